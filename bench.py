@@ -1,0 +1,277 @@
+#!/usr/bin/env python
+"""bench.py -- spin-flip attempts/s of the Metropolis sweep hot path.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--layout int8|bits]
+
+One "step" = one full checkerboard sweep of the workload (two kernel launches, one per colour).
+N = 1: BASELINE.json configs[1], a single 16384 x 16384 Ising lattice (2^28 sites) at kT = T_c.
+N > 1: one such lattice per GPU ("replicas only", weak scaling, no data-path collective) unless
+``--workload rx`` selects the replica-exchange workload (256 replicas of 1024^2 per GPU).
+Prints ONE JSON line on rank 0 (contract in the task statement / DESIGN.md section "Measurement").
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "spin-flip attempts/s"
+UNIT = "attempts/s"
+TC = 2.269185314213022
+SEED = 20260611
+
+
+def measured_peak_hbm():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons while the timed region runs."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.device = device
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, val in zip(names, f[4:8]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def dist_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU baseline: the reference's MCstep loop (oracle/cpu_port.py), one replica per host core
+# ------------------------------------------------------------------------------------------------
+def cpu_baseline(seconds_target=12.0):
+    from oracle import cpu_port
+    cores = os.cpu_count() or 1
+    rate1 = 2.5e5  # attempts/s/core, survey-time indication; only used to size the sample
+    ntrials = int(rate1 * seconds_target)
+    value, wall = cpu_port.time_all_cores(1024, -1.0, TC, ntrials, cores)
+    return {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": "%d single-site MCstep trials per core on a 1024x1024 float64 lattice at kT=Tc, one replica "
+                      "per core (%d cores, %.1f s); per-trial cost of the reference loop does not depend on "
+                      "lattice size" % (ntrials, cores, wall)}
+
+
+def run_reference(args):
+    rank, _, world = dist_env()
+    if rank != 0:
+        return
+    t_per_step = max(2.0, 20.0 / max(1, args.steps + args.warmup))
+    cb = None
+    vals = []
+    for i in range(args.warmup + args.steps):
+        c = cpu_baseline(seconds_target=t_per_step)
+        if i >= args.warmup:
+            vals.append(c["value"])
+            cb = c
+    value = sum(vals) / len(vals)
+    cb["value"] = value
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": None, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(args)}, "cpu_baseline": cb,
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def workload_name(args):
+    return "ising2d_%dx%d_single_replica_checkerboard_kT=Tc_J=-1" % (args.L, args.L)
+
+
+# ------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import numpy as np
+    rank, local_rank, world = dist_env()
+    from py_mc_b200 import _cabi
+    from py_mc_b200.ising2D import ising2D
+
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    L = args.L
+    layout = _cabi.LAYOUT_BITS if args.layout == "bits" else _cabi.LAYOUT_INT8
+    thr = ising2D(-1.0)._pmc_thresholds(TC)[None, :]
+    nsites = L * L
+
+    def make(lay):
+        lat = _cabi.Lattices(_cabi.MODEL_ISING, L, L, nreplicas=1, ntemps=1, seed=SEED, layout=lay,
+                             device=local_rank, replica_offset=rank, nreplicas_global=world)
+        lat.init_random()
+        lat.set_accept_tables(thr)
+        return lat
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+
+    def timed(lat, steps, warmup):
+        lat.sweep(warmup)
+        lat.synchronize()
+        barrier()
+        lat.timer_start()
+        lat.sweep(steps)
+        ms = lat.timer_stop()
+        barrier()
+        return ms
+
+    lat = make(layout)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ms = timed(lat, args.steps, args.warmup)
+    clocks = sampler.stop()
+    if dist is not None:
+        import torch
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    value = world * nsites * args.steps / (ms * 1e-3)
+
+    # end to end through the C ABI with HOST buffers: upload, sweeps, download, every step
+    host = lat.download(0)
+    e2e_sweeps = args.e2e_sweeps
+    reps = max(2, min(args.steps, 5))
+    lat.upload(0, host)
+    lat.sweep(1)
+    lat.synchronize()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        lat.upload(0, host)
+        lat.sweep(e2e_sweeps)
+        lat.download(0, out=host)
+        b, m = lat.tracked()
+    t_e2e = time.perf_counter() - t0
+    if dist is not None:
+        import torch
+        t = torch.tensor([t_e2e], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t_e2e = float(t.item())
+    e2e_value = world * nsites * e2e_sweeps * reps / t_e2e
+
+    bytes_per_site = 1.0 if layout == _cabi.LAYOUT_INT8 else 0.125
+    alg_bytes_per_launch = 2.0 * bytes_per_site * nsites / 2  # every site of one colour read + written once
+    launch_ms = ms / (2 * args.steps)
+    peak, peak_src = measured_peak_hbm()
+    achieved = alg_bytes_per_launch / (launch_ms * 1e-3) / 1e9
+
+    extra = {}
+    if args.also_bits and layout == _cabi.LAYOUT_INT8:
+        lat.close()
+        lat2 = make(_cabi.LAYOUT_BITS)
+        ms2 = timed(lat2, args.steps, args.warmup)
+        extra["bitpacked"] = {"value": world * nsites * args.steps / (ms2 * 1e-3), "unit": UNIT,
+                              "ms_per_step": ms2 / args.steps,
+                              "note": "same workload on the 1-bit/site layout (32 MiB, L2-resident: not HBM-bound)"}
+        lat2.close()
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8" if layout == _cabi.LAYOUT_INT8 else "u64 (1 bit/site)",
+            "data": "synthetic",
+            "config": {"workload": workload_name(args), "layout": args.layout, "sites_per_gpu": nsites,
+                       "step": "one full sweep = 2 colour passes", "seed": SEED,
+                       "l2": "working set %d MiB %s L2" % (int(nsites * bytes_per_site) >> 20,
+                                                           "exceeds" if nsites * bytes_per_site > 126e6 else "fits in"),
+                       "parallelism": "replicas only" if world > 1 else "single GPU"},
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": nsites, "d2h_bytes_per_step": nsites + 16,
+                    "sweeps_per_step": e2e_sweeps,
+                    "note": "C-ABI upload(host int8) + sweeps + download(host int8) + tracked observables per step"},
+            "gpu_launches": 2 * args.steps,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "kernel": "sweep_word_kernel", "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": alg_bytes_per_launch},
+        }
+        line.update(extra)
+        if world == 1 and not args.no_cpu:
+            line["cpu_baseline"] = cpu_baseline()
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--layout", default="int8", choices=["int8", "bits"])
+    ap.add_argument("--L", type=int, default=16384)
+    ap.add_argument("--e2e-sweeps", type=int, default=64)
+    ap.add_argument("--also-bits", action="store_true", default=True)
+    ap.add_argument("--no-also-bits", dest="also_bits", action="store_false")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

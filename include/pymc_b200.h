@@ -1,0 +1,140 @@
+/* pymc_b200.h -- C ABI of the B200-native Metropolis-sweep / replica-exchange engine.
+ *
+ * This is the drop-in boundary for py_mc's hot path.  The
+ * reference is pure Python and has no FFI of its own; each entry point below names
+ * the reference code whose work it takes over (paths relative to the reference tree).
+ * INTEGRATION.md shows the ctypes stub a py_mc maintainer would add.
+ *
+ * Conventions
+ *   - every function returns 0 on success and a negative pymc_status on failure;
+ *     pymc_last_error() returns a thread-local human-readable message.
+ *   - no exceptions, no C++/torch types: plain pointers and sizes only.
+ *   - host pointers are caller-owned; all device memory belongs to the handle.
+ *   - a handle is bound to one CUDA device and one stream; calls on one handle must be
+ *     serialised by the caller.  pymc_sweep / pymc_rx_* only enqueue work; functions that
+ *     return host data synchronise the handle's stream.
+ *   - there is no CPU fallback: unsupported shapes return PYMC_ERR_UNSUPPORTED.
+ */
+#ifndef PYMC_B200_H
+#define PYMC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PYMC_ABI_VERSION 1
+
+typedef enum {
+    PYMC_OK = 0,
+    PYMC_ERR_BADARG = -1,      /* null pointer, out-of-range index, wrong size */
+    PYMC_ERR_CUDA = -2,        /* a CUDA runtime call failed (message has the CUDA error) */
+    PYMC_ERR_UNSUPPORTED = -3, /* odd lattice edge, width not packable for the layout, ... */
+    PYMC_ERR_STATE = -4        /* call order problem, e.g. sweep before tables were set */
+} pymc_status;
+
+typedef enum {
+    PYMC_MODEL_ISING = 0,  /* spins +1/-1,   examples/ising2D.py:7-52   */
+    PYMC_MODEL_LATGAS = 1  /* occupancy 0/1, examples/latgas.py:7-57    */
+} pymc_model;
+
+typedef enum {
+    PYMC_LAYOUT_INT8 = 0, /* one byte per site, colour-split [replica][colour][lenX][lenY/2]        */
+    PYMC_LAYOUT_BITS = 1  /* one bit per site,  colour-split [replica][colour][lenX][lenY/128] u64; */
+                          /* needs lenY % 128 == 0                                                  */
+} pymc_layout;
+
+typedef enum {
+    PYMC_KERNEL_AUTO = 0,    /* fastest kernel that supports the shape                     */
+    PYMC_KERNEL_GENERIC = 1  /* the simple one-thread-per-word kernel (any even lenX, lenY) */
+} pymc_kernel;
+
+/* Number of acceptance-table entries per temperature: Ising 5 (index = number of aligned
+ * neighbours 0..4), lattice gas 10 (index = 5*c + number of occupied neighbours). */
+#define PYMC_NCLASS_ISING 5
+#define PYMC_NCLASS_LATGAS 10
+
+typedef struct {
+    int32_t abi_version;       /* PYMC_ABI_VERSION */
+    int32_t device;            /* CUDA device ordinal */
+    int32_t model;             /* pymc_model */
+    int32_t layout;            /* pymc_layout */
+    int32_t lenX, lenY;        /* lattice edges (config[x][y], y contiguous); both even */
+    int32_t nreplicas;         /* replicas held by this handle (this GPU) */
+    int32_t replica_offset;    /* global index of local replica 0 (multi-GPU partition) */
+    int32_t nreplicas_global;  /* replicas over all GPUs (== nreplicas on one GPU) */
+    int32_t ntemps;            /* rows of the acceptance table (temperatures / parameter sets) */
+    uint64_t seed;             /* Philox key; the same on every GPU of one run */
+    int32_t kernel;            /* pymc_kernel */
+    int32_t reserved;
+} pymc_params;
+
+typedef struct pymc_handle pymc_handle;
+
+/* ---- library ------------------------------------------------------------------- */
+int pymc_abi_version(void);
+const char *pymc_last_error(void);
+int pymc_device_count(int *count);
+
+/* ---- lifetime -------------------------------------------------------------------
+ * Replaces CanonicalMonteCarlo.__init__ (py_mc/mc.py:163-168) for a whole batch of
+ * replicas and ParallelMC.__init__'s one-engine-per-rank set-up (py_mc/mc_mpi.py:38-56). */
+int pymc_create(const pymc_params *params, pymc_handle **out);
+int pymc_destroy(pymc_handle *h);
+/* Run on a caller-provided CUDA stream (cudaStream_t cast to void*); NULL = the handle's own. */
+int pymc_set_stream(pymc_handle *h, void *cuda_stream);
+int pymc_synchronize(pymc_handle *h);
+
+/* ---- configurations ---------------------------------------------------------------
+ * Host format: int8 row-major [lenX][lenY], +1/-1 (Ising) or 0/1 (lattice gas): the
+ * integer image of the reference's float64 config array (examples/ising2D.py:56-70). */
+int pymc_upload_config(pymc_handle *h, int replica, const int8_t *host, size_t nsites);
+int pymc_download_config(pymc_handle *h, int replica, int8_t *host, size_t nsites);
+/* Hot start on the device, rule of ising2D_config.prepare_random (examples/ising2D.py:64-70)
+ * applied to stream domain 1 (see oracle/philox.py); all local replicas. */
+int pymc_init_random(pymc_handle *h);
+
+/* ---- acceptance tables --------------------------------------------------------------
+ * thr[t][c] = floor(exp(-dE_c/kT_t) * 2^32) clamped to 2^32-1, or 2^32-1 when dE_c < 0:
+ * the integer form of the Metropolis test of MCstep (py_mc/mc.py:175-184).  The caller
+ * computes it with the host libm so acceptance is bit-exact with the reference. */
+int pymc_set_accept_tables(pymc_handle *h, const uint32_t *thr, int ntemps, int nclass);
+/* replica -> table row.  Mirrors rank_to_T (py_mc/mc_mpi.py:79); n == nreplicas_global. */
+int pymc_set_replica_to_T(pymc_handle *h, const int32_t *map, int n);
+int pymc_get_replica_to_T(pymc_handle *h, int32_t *map, int n);
+
+/* ---- the hot path -----------------------------------------------------------------
+ * nsweeps full checkerboard sweeps of every local replica; one sweep = lenX*lenY
+ * Metropolis trials (= that many MCstep() calls of py_mc/mc.py:170-185 driven in
+ * checkerboard order).  Asynchronous. */
+int pymc_sweep(pymc_handle *h, int64_t nsweeps);
+int pymc_get_sweep_counter(pymc_handle *h, uint64_t *counter);
+int pymc_set_sweep_counter(pymc_handle *h, uint64_t counter);
+
+/* ---- observables --------------------------------------------------------------------
+ * Exact integers per local replica.  Ising: bond = sum s(i,j)(s(i-1,j)+s(i,j-1)) so that
+ * E = J*bond (examples/ising2D.py:15-22), second = sum s (ising2D.py:24-26).
+ * Lattice gas: bond = sum c(i,j)(c(i-1,j)+c(i,j-1)), second = sum c (latgas.py:17-29).
+ * pymc_reduce_observables recomputes them from the lattice (what model.energy(config)
+ * does at the top of run(), py_mc/mc.py:191) and re-bases the tracked values;
+ * pymc_get_tracked returns the incrementally tracked values (energy += dE, mc.py:177). */
+int pymc_reduce_observables(pymc_handle *h, int64_t *bond, int64_t *second);
+int pymc_get_tracked(pymc_handle *h, int64_t *bond, int64_t *second);
+
+/* ---- parity helper -------------------------------------------------------------------
+ * For n sites (x[i], y[i]) of one replica return the site value and the sum of its four
+ * neighbours: the integers from which trialstep's dE is formed (examples/ising2D.py:39-45,
+ * examples/latgas.py:42-50).  The configuration is left unchanged. */
+int pymc_propose(pymc_handle *h, int replica, const int32_t *x, const int32_t *y, int n,
+                 int32_t *site_out, int32_t *nnsum_out);
+
+/* ---- timing helper (CUDA events on the handle's stream) ------------------------------ */
+int pymc_timer_start(pymc_handle *h);
+int pymc_timer_stop(pymc_handle *h, float *elapsed_ms); /* synchronises */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PYMC_B200_H */

@@ -1,0 +1,213 @@
+"""ctypes binding of include/pymc_b200.h -- the only way Python reaches the kernels.
+
+There is no CPU fallback: if the shared library has not been built, importing this module
+raises, and so does every product class that needs it.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from ._build import LIBPATH
+
+ABI_VERSION = 1
+MODEL_ISING, MODEL_LATGAS = 0, 1
+LAYOUT_INT8, LAYOUT_BITS = 0, 1
+KERNEL_AUTO, KERNEL_GENERIC = 0, 1
+NCLASS = {MODEL_ISING: 5, MODEL_LATGAS: 10}
+
+# every symbol include/pymc_b200.h declares (tests check the library exports all of them)
+SYMBOLS = [
+    "pymc_abi_version", "pymc_last_error", "pymc_device_count", "pymc_create", "pymc_destroy",
+    "pymc_set_stream", "pymc_synchronize", "pymc_upload_config", "pymc_download_config",
+    "pymc_init_random", "pymc_set_accept_tables", "pymc_set_replica_to_T", "pymc_get_replica_to_T",
+    "pymc_sweep", "pymc_get_sweep_counter", "pymc_set_sweep_counter", "pymc_reduce_observables",
+    "pymc_get_tracked", "pymc_propose", "pymc_timer_start", "pymc_timer_stop",
+]
+
+
+class Params(C.Structure):
+    _fields_ = [
+        ("abi_version", C.c_int32), ("device", C.c_int32), ("model", C.c_int32), ("layout", C.c_int32),
+        ("lenX", C.c_int32), ("lenY", C.c_int32), ("nreplicas", C.c_int32), ("replica_offset", C.c_int32),
+        ("nreplicas_global", C.c_int32), ("ntemps", C.c_int32), ("seed", C.c_uint64),
+        ("kernel", C.c_int32), ("reserved", C.c_int32),
+    ]
+
+
+class PymcError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__("pymc_b200 error %d: %s" % (code, message))
+        self.code = code
+
+
+def _load():
+    if not os.path.exists(LIBPATH):
+        raise ImportError(
+            "py_mc_b200: %s is missing. Build it with `python -m py_mc_b200._build` "
+            "(needs nvcc; there is no CPU fallback)." % LIBPATH)
+    lib = C.CDLL(LIBPATH)
+    P, I, I64 = C.c_void_p, C.c_int, C.c_int64
+    lib.pymc_abi_version.restype = I
+    lib.pymc_last_error.restype = C.c_char_p
+    sigs = {
+        "pymc_device_count": [C.POINTER(I)],
+        "pymc_create": [C.POINTER(Params), C.POINTER(P)],
+        "pymc_destroy": [P],
+        "pymc_set_stream": [P, P],
+        "pymc_synchronize": [P],
+        "pymc_upload_config": [P, I, P, C.c_size_t],
+        "pymc_download_config": [P, I, P, C.c_size_t],
+        "pymc_init_random": [P],
+        "pymc_set_accept_tables": [P, P, I, I],
+        "pymc_set_replica_to_T": [P, P, I],
+        "pymc_get_replica_to_T": [P, P, I],
+        "pymc_sweep": [P, I64],
+        "pymc_get_sweep_counter": [P, C.POINTER(C.c_uint64)],
+        "pymc_set_sweep_counter": [P, C.c_uint64],
+        "pymc_reduce_observables": [P, P, P],
+        "pymc_get_tracked": [P, P, P],
+        "pymc_propose": [P, I, P, P, I, P, P],
+        "pymc_timer_start": [P],
+        "pymc_timer_stop": [P, C.POINTER(C.c_float)],
+    }
+    for name, argtypes in sigs.items():
+        fn = getattr(lib, name)
+        fn.argtypes = argtypes
+        fn.restype = I
+    if lib.pymc_abi_version() != ABI_VERSION:
+        raise ImportError("py_mc_b200: library ABI %d, binding expects %d; rebuild with "
+                          "`python -m py_mc_b200._build --force`" % (lib.pymc_abi_version(), ABI_VERSION))
+    return lib
+
+
+lib = _load()
+
+
+def check(rc):
+    if rc != 0:
+        raise PymcError(rc, lib.pymc_last_error().decode("utf-8", "replace"))
+
+
+def device_count():
+    n = C.c_int(0)
+    check(lib.pymc_device_count(C.byref(n)))
+    return n.value
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class Lattices:
+    """A batch of replicas of one lattice model on one GPU (thin owner of a pymc_handle)."""
+
+    def __init__(self, model, lenX, lenY, nreplicas=1, ntemps=1, seed=0, layout=LAYOUT_INT8, device=0,
+                 replica_offset=0, nreplicas_global=None, kernel=KERNEL_AUTO):
+        self._h = C.c_void_p()
+        self.model, self.lenX, self.lenY = int(model), int(lenX), int(lenY)
+        self.nreplicas, self.ntemps, self.layout = int(nreplicas), int(ntemps), int(layout)
+        self.replica_offset = int(replica_offset)
+        self.nreplicas_global = int(nreplicas if nreplicas_global is None else nreplicas_global)
+        self.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
+        self.device = int(device)
+        p = Params(ABI_VERSION, self.device, self.model, self.layout, self.lenX, self.lenY, self.nreplicas,
+                   self.replica_offset, self.nreplicas_global, self.ntemps, self.seed, int(kernel), 0)
+        check(lib.pymc_create(C.byref(p), C.byref(self._h)))
+
+    # -- lifetime
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            lib.pymc_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def nsites(self):
+        return self.lenX * self.lenY
+
+    def set_stream(self, cuda_stream_ptr):
+        check(lib.pymc_set_stream(self._h, C.c_void_p(cuda_stream_ptr or 0)))
+
+    def synchronize(self):
+        check(lib.pymc_synchronize(self._h))
+
+    # -- configurations
+    def upload(self, replica, config_int8):
+        a = np.ascontiguousarray(config_int8, dtype=np.int8)
+        if a.shape != (self.lenX, self.lenY):
+            raise ValueError("config shape %s, lattice is %dx%d" % (a.shape, self.lenX, self.lenY))
+        check(lib.pymc_upload_config(self._h, replica, _ptr(a), a.size))
+
+    def download(self, replica, out=None):
+        if out is None:
+            out = np.empty((self.lenX, self.lenY), dtype=np.int8)
+        assert out.dtype == np.int8 and out.flags.c_contiguous and out.size == self.nsites
+        check(lib.pymc_download_config(self._h, replica, _ptr(out), out.size))
+        return out
+
+    def init_random(self):
+        check(lib.pymc_init_random(self._h))
+
+    # -- tables
+    def set_accept_tables(self, thr):
+        t = np.ascontiguousarray(thr, dtype=np.uint32).reshape(self.ntemps, NCLASS[self.model])
+        check(lib.pymc_set_accept_tables(self._h, _ptr(t), t.shape[0], t.shape[1]))
+
+    def set_replica_to_T(self, mapping):
+        m = np.ascontiguousarray(mapping, dtype=np.int32)
+        check(lib.pymc_set_replica_to_T(self._h, _ptr(m), m.size))
+
+    def get_replica_to_T(self):
+        m = np.empty(self.nreplicas_global, dtype=np.int32)
+        check(lib.pymc_get_replica_to_T(self._h, _ptr(m), m.size))
+        return m
+
+    # -- hot path
+    def sweep(self, nsweeps=1):
+        check(lib.pymc_sweep(self._h, int(nsweeps)))
+
+    @property
+    def sweep_counter(self):
+        c = C.c_uint64(0)
+        check(lib.pymc_get_sweep_counter(self._h, C.byref(c)))
+        return c.value
+
+    @sweep_counter.setter
+    def sweep_counter(self, v):
+        check(lib.pymc_set_sweep_counter(self._h, int(v)))
+
+    # -- observables
+    def reduce_observables(self):
+        b = np.empty(self.nreplicas, dtype=np.int64)
+        s = np.empty(self.nreplicas, dtype=np.int64)
+        check(lib.pymc_reduce_observables(self._h, _ptr(b), _ptr(s)))
+        return b, s
+
+    def tracked(self):
+        b = np.empty(self.nreplicas, dtype=np.int64)
+        s = np.empty(self.nreplicas, dtype=np.int64)
+        check(lib.pymc_get_tracked(self._h, _ptr(b), _ptr(s)))
+        return b, s
+
+    def propose(self, replica, xs, ys):
+        xs = np.ascontiguousarray(xs, dtype=np.int32)
+        ys = np.ascontiguousarray(ys, dtype=np.int32)
+        site = np.empty(xs.size, dtype=np.int32)
+        nn = np.empty(xs.size, dtype=np.int32)
+        check(lib.pymc_propose(self._h, replica, _ptr(xs), _ptr(ys), xs.size, _ptr(site), _ptr(nn)))
+        return site, nn
+
+    # -- timing
+    def timer_start(self):
+        check(lib.pymc_timer_start(self._h))
+
+    def timer_stop(self):
+        ms = C.c_float(0)
+        check(lib.pymc_timer_stop(self._h, C.byref(ms)))
+        return ms.value

@@ -1,0 +1,127 @@
+// pmc_core.cuh -- the Metropolis test on one 64-site word, bit-sliced.
+//
+// What it replaces: model.trialstep + CanonicalMonteCarlo.MCstep for 64 same-colour sites at
+// once (examples/ising2D.py:28-52, examples/latgas.py:31-57, py_mc/mc.py:170-185).
+//
+// A word holds 64 sites of one checkerboard colour as bits (1 = spin +1 / occupied).  The four
+// neighbour words U, D (rows i-1, i+1), C (same row, same k) and Sd (same row, k-1 or k+1) belong
+// to the other colour and are read-only during the pass.  Each lane falls in one *class* that
+// fixes its dE (Ising: number of aligned neighbours 0..4; lattice gas: 5*c + occupied
+// neighbours), the caller supplies one 32-bit threshold per class
+// (thr = floor(exp(-dE/kT) 2^32), 2^32-1 = always accept), and a lane is accepted iff its
+// uniform x32 <= thr.  x32 is defined bit-serially by the Philox planes of pmc_stream.cuh, so the
+// comparison runs MSB-first on all 64 lanes in parallel and stops as soon as every lane of the
+// warp is decided (about log2(2048) + 1 planes instead of 32).
+#pragma once
+#include "pmc_stream.cuh"
+
+namespace pmc {
+
+constexpr uint32_t THR_ALWAYS = 0xFFFFFFFFu;
+
+enum : int { MODEL_ISING = 0, MODEL_LATGAS = 1 };
+
+template <int MODEL>
+struct ModelTraits;
+template <>
+struct ModelTraits<MODEL_ISING> {
+    static constexpr int NCLASS = 5;
+};
+template <>
+struct ModelTraits<MODEL_LATGAS> {
+    static constexpr int NCLASS = 10;
+};
+
+// bit-sliced sum of four one-bit operands: count = a0 + 2 a1 + 4 a2
+__device__ __forceinline__ void add4(uint64_t x1, uint64_t x2, uint64_t x3, uint64_t x4, uint64_t &a0, uint64_t &a1,
+                                     uint64_t &a2) {
+    uint64_t s01 = x1 ^ x2, c01 = x1 & x2;
+    uint64_t s23 = x3 ^ x4, c23 = x3 & x4;
+    a0 = s01 ^ s23;
+    uint64_t c0 = s01 & s23;
+    a1 = c01 ^ c23 ^ c0;
+    a2 = c01 & c23;
+}
+
+// One-hot class masks from a bit-sliced count 0..4.
+__device__ __forceinline__ void count_masks(uint64_t a0, uint64_t a1, uint64_t a2, uint64_t (&m)[5]) {
+    m[0] = ~(a0 | a1 | a2);
+    m[1] = a0 & ~a1;
+    m[2] = a1 & ~a0;
+    m[3] = a1 & a0;
+    m[4] = a2;
+}
+
+// Bit-serial x32 <= thr[class] for all lanes.  Every thread of the warp must call this together.
+template <int NCLASS>
+__device__ __forceinline__ uint64_t decide(const uint64_t (&m)[NCLASS], const uint32_t (&thr)[NCLASS], uint64_t valid,
+                                           uint32_t word_idx, uint32_t replica, uint64_t step, uint32_t domain,
+                                           PhiloxKey key) {
+    uint64_t always = 0, needed = 0;
+#pragma unroll
+    for (int c = 0; c < NCLASS; ++c) {
+        if (thr[c] == THR_ALWAYS)
+            always |= m[c];
+        else
+            needed |= m[c];
+    }
+    uint64_t und = needed & valid;  // lanes whose x32 still equals thr on all planes seen so far
+    uint64_t lt = 0;                // lanes already known to have x32 < thr
+#pragma unroll 1
+    for (uint32_t call = 0; call < 16; ++call) {
+        if (!__any_sync(0xFFFFFFFFu, und != 0)) break;
+        uint64_t pe, po;
+        word_planes(word_idx, replica, step, domain, call, key, pe, po);
+        uint64_t te = 0, to = 0;
+        const int be = 31 - 2 * (int)call, bo = be - 1;
+#pragma unroll
+        for (int c = 0; c < NCLASS; ++c) {
+            if ((thr[c] >> be) & 1u) te |= m[c];
+            if ((thr[c] >> bo) & 1u) to |= m[c];
+        }
+        lt |= und & te & ~pe;
+        und &= ~(te ^ pe);
+        lt |= und & to & ~po;
+        und &= ~(to ^ po);
+    }
+    // und != 0 here only after all 32 planes: x32 == thr, which the reference accepts (u <= p).
+    return ((always & valid) | lt | und);
+}
+
+// Full update of one word.  Returns the new word; dB / dS are the exact integer changes of the
+// bond sum and of the second observable (magnetisation or particle number) caused by this word.
+template <int MODEL>
+__device__ __forceinline__ uint64_t update_word(uint64_t S, uint64_t U, uint64_t D, uint64_t C, uint64_t Sd,
+                                                uint64_t valid, const uint32_t (&thr)[ModelTraits<MODEL>::NCLASS],
+                                                uint32_t word_idx, uint32_t replica, uint64_t step, PhiloxKey key,
+                                                int &dB, int &dS) {
+    if constexpr (MODEL == MODEL_ISING) {
+        uint64_t a0, a1, a2, m[5];
+        add4(~(S ^ U), ~(S ^ D), ~(S ^ C), ~(S ^ Sd), a0, a1, a2);  // aligned neighbours
+        count_masks(a0, a1, a2, m);
+        uint64_t acc = decide<5>(m, thr, valid, word_idx, replica, step, DOMAIN_SWEEP, key);
+        // flipping a spin with a aligned neighbours changes the bond sum by 8 - 4a, M by -2s
+        int na = __popcll(acc);
+        dB = 8 * na - 4 * (__popcll(acc & a0) + 2 * __popcll(acc & a1) + 4 * __popcll(acc & a2));
+        dS = -2 * (2 * __popcll(acc & S) - na);
+        return S ^ acc;
+    } else {
+        uint64_t n0, n1, n2, cnt[5], m[10];
+        add4(U, D, C, Sd, n0, n1, n2);  // occupied neighbours
+        count_masks(n0, n1, n2, cnt);
+#pragma unroll
+        for (int n = 0; n < 5; ++n) {
+            m[n] = cnt[n] & ~S;
+            m[5 + n] = cnt[n] & S;
+        }
+        uint64_t acc = decide<10>(m, thr, valid, word_idx, replica, step, DOMAIN_SWEEP, key);
+        // toggling c -> 1-c with nn occupied neighbours changes the bond count by (1-2c) nn, N by (1-2c)
+        uint64_t add = acc & ~S, rem = acc & S;
+        dB = (__popcll(add & n0) + 2 * __popcll(add & n1) + 4 * __popcll(add & n2)) -
+             (__popcll(rem & n0) + 2 * __popcll(rem & n1) + 4 * __popcll(rem & n2));
+        dS = __popcll(add) - __popcll(rem);
+        return S ^ acc;
+    }
+}
+
+}  // namespace pmc

@@ -1,0 +1,68 @@
+// pmc_stream.cuh -- Philox4x32-10 in registers and the "pmc stream v1" counter layout.
+//
+// The reference draws from CPython's MT19937 (py_mc/mc.py:2,182; examples/ising2D.py:32-33);
+// a sweep kernel needs a counter-based generator instead.  The layout below is the single
+// definition shared by every kernel; oracle/philox.py restates it for the CPU checker.
+//
+//   key     = (seed_lo, seed_hi)
+//   counter = (idx, replica, step_lo, domain<<28 | call<<24 | step_hi[23:0])
+//
+// Domain 0 (sweeps): idx = word index (row*nwords_per_row + wcol) of a 64-site word of one
+// colour, step = 2*sweep + colour, call m in 0..15 yields bit planes 2m (o0 | o1<<32) and
+// 2m+1 (o2 | o3<<32).  Lane l's 32-bit uniform is x32 = sum_j bit_l(plane_j) << (31-j).
+#pragma once
+#include <stdint.h>
+
+namespace pmc {
+
+constexpr uint32_t PHILOX_M0 = 0xD2511F53u;
+constexpr uint32_t PHILOX_M1 = 0xCD9E8D57u;
+constexpr uint32_t PHILOX_W0 = 0x9E3779B9u;
+constexpr uint32_t PHILOX_W1 = 0xBB67AE85u;
+
+enum : uint32_t { DOMAIN_SWEEP = 0, DOMAIN_INIT = 1, DOMAIN_RX = 2, DOMAIN_PAIR = 3, DOMAIN_DISC = 4 };
+
+struct PhiloxKey {
+    uint32_t k0, k1;
+};
+
+__host__ __device__ __forceinline__ PhiloxKey make_key(uint64_t seed) {
+    PhiloxKey k;
+    k.k0 = (uint32_t)seed;
+    k.k1 = (uint32_t)(seed >> 32);
+    return k;
+}
+
+__host__ __device__ __forceinline__ uint32_t ctr3(uint32_t domain, uint32_t call, uint64_t step) {
+    return (domain << 28) | (call << 24) | ((uint32_t)(step >> 32) & 0xFFFFFFu);
+}
+
+// One Philox4x32-10 block.  The round keys depend only on the (uniform) seed, so the
+// compiler folds the key schedule into immediates/uniform registers.
+__device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, PhiloxKey key) {
+    uint32_t k0 = key.k0, k1 = key.k1;
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        uint32_t hi0 = __umulhi(PHILOX_M0, c0), lo0 = PHILOX_M0 * c0;
+        uint32_t hi1 = __umulhi(PHILOX_M1, c2), lo1 = PHILOX_M1 * c2;
+        uint32_t n0 = hi1 ^ c1 ^ k0;
+        uint32_t n2 = hi0 ^ c3 ^ k1;
+        c0 = n0;
+        c1 = lo1;
+        c2 = n2;
+        c3 = lo0;
+        k0 += PHILOX_W0;
+        k1 += PHILOX_W1;
+    }
+    return make_uint4(c0, c1, c2, c3);
+}
+
+// Two bit planes (2*call, 2*call+1) of one word.
+__device__ __forceinline__ void word_planes(uint32_t word_idx, uint32_t replica, uint64_t step, uint32_t domain,
+                                            uint32_t call, PhiloxKey key, uint64_t &even, uint64_t &odd) {
+    uint4 o = philox4x32_10(word_idx, replica, (uint32_t)step, ctr3(domain, call, step), key);
+    even = (uint64_t)o.x | ((uint64_t)o.y << 32);
+    odd = (uint64_t)o.z | ((uint64_t)o.w << 32);
+}
+
+}  // namespace pmc

@@ -1,0 +1,739 @@
+// pymc_b200.cu -- kernels and C ABI of the B200-native Metropolis sweep engine (sm_100a).
+//
+// Data layout in HBM (per handle = per GPU):
+//   int8 layout : spins[replica][colour][lenX][nk]   int8,  nk = lenY/2
+//   bits layout : bits [replica][colour][lenX][nw]   u64,   nw = nk/64
+// colour = (x + y) & 1; within a row the sites of one colour are numbered k = y >> 1, and 64
+// consecutive k form a *word* (the unit of the random stream, pmc_stream.cuh).
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+#include "../../include/pymc_b200.h"
+#include "pmc_core.cuh"
+
+using namespace pmc;
+
+// ------------------------------------------------------------------------------------------
+// error plumbing
+// ------------------------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+
+static int fail(int code, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define CUDA_TRY(expr)                                                                                  \
+    do {                                                                                                \
+        cudaError_t _e = (expr);                                                                        \
+        if (_e != cudaSuccess)                                                                          \
+            return fail(PYMC_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, \
+                        __LINE__);                                                                      \
+    } while (0)
+
+#define REQUIRE(cond, code, ...) \
+    do {                         \
+        if (!(cond)) return fail(code, __VA_ARGS__); \
+    } while (0)
+
+// ------------------------------------------------------------------------------------------
+// lattice descriptor passed by value to kernels
+// ------------------------------------------------------------------------------------------
+struct Lat {
+    int8_t *i8;
+    uint64_t *bits;
+    int lenX, lenY, nk, nw;
+    int nrep, rep_offset;
+    const uint32_t *thr;       // [ntemps][nclass]
+    const int32_t *rep_to_T;   // [nrep_global]
+    unsigned long long *tracked;  // [nrep][2]
+    PhiloxKey key;
+};
+
+template <int LAYOUT>
+struct Loader;
+
+// one byte per site
+template <>
+struct Loader<PYMC_LAYOUT_INT8> {
+    static __device__ __forceinline__ const int8_t *row(const Lat &L, int rep, int colour, int i) {
+        return L.i8 + ((size_t)(rep * 2 + colour) * L.lenX + i) * L.nk;
+    }
+    static __device__ __forceinline__ uint64_t word(const Lat &L, int rep, int colour, int i, int w) {
+        const int8_t *p = row(L, rep, colour, i) + 64 * w;
+        int n = min(64, L.nk - 64 * w);
+        uint64_t m = 0;
+        for (int l = 0; l < n; ++l) m |= (uint64_t)(p[l] > 0) << l;
+        return m;
+    }
+    static __device__ __forceinline__ int site(const Lat &L, int rep, int colour, int i, int k) {
+        return row(L, rep, colour, i)[k] > 0;
+    }
+};
+
+// one bit per site
+template <>
+struct Loader<PYMC_LAYOUT_BITS> {
+    static __device__ __forceinline__ uint64_t word(const Lat &L, int rep, int colour, int i, int w) {
+        return L.bits[((size_t)(rep * 2 + colour) * L.lenX + i) * L.nw + w];
+    }
+    static __device__ __forceinline__ int site(const Lat &L, int rep, int colour, int i, int k) {
+        return (int)((word(L, rep, colour, i, k >> 6) >> (k & 63)) & 1u);
+    }
+};
+
+// Neighbour words of word (colour, i, w): U, D, C and the two shifted same-row words
+// Lf (site k-1) and Rt (site k+1) of the other colour, periodic in both directions.
+template <int LAYOUT>
+__device__ __forceinline__ void load_neighbours(const Lat &L, int rep, int colour, int i, int w, int nvalid,
+                                                bool needLf, bool needRt, uint64_t &U, uint64_t &D, uint64_t &C,
+                                                uint64_t &Lf, uint64_t &Rt) {
+    const int oc = colour ^ 1;
+    const int im = (i == 0) ? L.lenX - 1 : i - 1;
+    const int ip = (i == L.lenX - 1) ? 0 : i + 1;
+    U = Loader<LAYOUT>::word(L, rep, oc, im, w);
+    D = Loader<LAYOUT>::word(L, rep, oc, ip, w);
+    C = Loader<LAYOUT>::word(L, rep, oc, i, w);
+    Lf = Rt = 0;
+    if (needLf) {
+        int kprev = 64 * w - 1;
+        if (kprev < 0) kprev = L.nk - 1;
+        Lf = (C << 1) | (uint64_t)Loader<LAYOUT>::site(L, rep, oc, i, kprev);
+    }
+    if (needRt) {
+        int knext = 64 * w + nvalid;
+        if (knext >= L.nk) knext = 0;
+        Rt = (C >> 1) | ((uint64_t)Loader<LAYOUT>::site(L, rep, oc, i, knext) << (nvalid - 1));
+    }
+}
+
+__device__ __forceinline__ int warp_sum(int v) { return __reduce_add_sync(0xFFFFFFFFu, v); }
+
+// Block-level sum of two ints, one 64-bit atomic pair per block.
+__device__ __forceinline__ void block_accumulate(int a, int b, unsigned long long *dst) {
+    __shared__ int sa[32], sb[32];
+    a = warp_sum(a);
+    b = warp_sum(b);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (lane == 0) {
+        sa[wid] = a;
+        sb[wid] = b;
+    }
+    __syncthreads();
+    if (wid == 0) {
+        const int nwarp = (blockDim.x + 31) >> 5;
+        a = lane < nwarp ? sa[lane] : 0;
+        b = lane < nwarp ? sb[lane] : 0;
+        a = warp_sum(a);
+        b = warp_sum(b);
+        if (lane == 0) {
+            if (a) atomicAdd(dst, (unsigned long long)(long long)a);
+            if (b) atomicAdd(dst + 1, (unsigned long long)(long long)b);
+        }
+    }
+}
+
+template <int MODEL>
+__device__ __forceinline__ void load_thr(const Lat &L, int rep, uint32_t (&thr)[ModelTraits<MODEL>::NCLASS]) {
+    const int t = L.rep_to_T[L.rep_offset + rep];
+    const uint32_t *row = L.thr + (size_t)t * ModelTraits<MODEL>::NCLASS;
+#pragma unroll
+    for (int c = 0; c < ModelTraits<MODEL>::NCLASS; ++c) thr[c] = __ldg(row + c);
+}
+
+// ------------------------------------------------------------------------------------------
+// K1/K2 (first form): one thread per word, any even lenX/lenY (int8) or lenY % 128 == 0 (bits).
+// grid = (ceil(lenX*nw / block), nrep)
+// ------------------------------------------------------------------------------------------
+template <int LAYOUT, int MODEL>
+__global__ void __launch_bounds__(128) sweep_word_kernel(Lat L, int colour, uint64_t step) {
+    constexpr int NCLASS = ModelTraits<MODEL>::NCLASS;
+    const int rep = blockIdx.y;
+    const int word = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool active = word < L.lenX * L.nw;
+    uint32_t thr[NCLASS];
+    load_thr<MODEL>(L, rep, thr);
+
+    int i = 0, w = 0, nvalid = 0;
+    uint64_t S = 0, U = 0, D = 0, C = 0, Lf = 0, Rt = 0, valid = 0;
+    bool q = false;
+    if (active) {
+        i = word / L.nw;
+        w = word - i * L.nw;
+        nvalid = min(64, L.nk - 64 * w);
+        valid = nvalid == 64 ? ~0ull : ((1ull << nvalid) - 1);
+        q = (i + colour) & 1;  // first column of this colour in row i
+        S = Loader<LAYOUT>::word(L, rep, colour, i, w);
+        load_neighbours<LAYOUT>(L, rep, colour, i, w, nvalid, !q, q, U, D, C, Lf, Rt);
+    }
+    int dB = 0, dS = 0;
+    uint64_t Snew = update_word<MODEL>(S, U, D, C, q ? Rt : Lf, valid, thr, (uint32_t)word,
+                                       (uint32_t)(L.rep_offset + rep), step, L.key, dB, dS);
+    if (active) {
+        uint64_t flip = (S ^ Snew) & valid;
+        if (LAYOUT == PYMC_LAYOUT_BITS) {
+            if (flip) L.bits[((size_t)(rep * 2 + colour) * L.lenX + i) * L.nw + w] = Snew;
+        } else {
+            int8_t *p = L.i8 + ((size_t)(rep * 2 + colour) * L.lenX + i) * L.nk + 64 * w;
+            while (flip) {
+                int l = __ffsll((long long)flip) - 1;
+                flip &= flip - 1;
+                p[l] = (MODEL == MODEL_ISING) ? (int8_t)-p[l] : (int8_t)(1 - p[l]);
+            }
+        }
+    } else {
+        dB = dS = 0;
+    }
+    block_accumulate(dB, dS, L.tracked + 2 * (size_t)rep);
+}
+
+// ------------------------------------------------------------------------------------------
+// K3: exact integer observables per replica (bond sum and magnetisation / particle number).
+// Each word of either colour contributes its bonds to the row above and to the site on its left.
+// grid = (ceil(2*lenX*nw / block), nrep)
+// ------------------------------------------------------------------------------------------
+template <int LAYOUT, int MODEL>
+__global__ void __launch_bounds__(256) reduce_kernel(Lat L, unsigned long long *out) {
+    const int rep = blockIdx.y;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int per_colour = L.lenX * L.nw;
+    int dB = 0, dS = 0;
+    if (idx < 2 * per_colour) {
+        const int colour = idx / per_colour;
+        const int word = idx - colour * per_colour;
+        const int i = word / L.nw, w = word - i * L.nw;
+        const int nvalid = min(64, L.nk - 64 * w);
+        const uint64_t valid = nvalid == 64 ? ~0ull : ((1ull << nvalid) - 1);
+        const bool q = (i + colour) & 1;
+        uint64_t S = Loader<LAYOUT>::word(L, rep, colour, i, w), U, D, C, Lf, Rt;
+        load_neighbours<LAYOUT>(L, rep, colour, i, w, nvalid, !q, false, U, D, C, Lf, Rt);
+        const uint64_t Lw = q ? C : Lf;  // the site at column y-1
+        if (MODEL == MODEL_ISING) {
+            dB = 2 * nvalid - 2 * (__popcll((S ^ U) & valid) + __popcll((S ^ Lw) & valid));
+            dS = 2 * __popcll(S & valid) - nvalid;
+        } else {
+            dB = __popcll(S & U & valid) + __popcll(S & Lw & valid);
+            dS = __popcll(S & valid);
+        }
+    }
+    block_accumulate(dB, dS, out + 2 * (size_t)rep);
+}
+
+// ------------------------------------------------------------------------------------------
+// layout conversion: natural int8 [lenX][lenY]  <->  colour-split storage of one replica
+// ------------------------------------------------------------------------------------------
+template <int LAYOUT>
+__global__ void pack_kernel(Lat L, int rep, const int8_t *natural) {
+    const int word = blockIdx.x * blockDim.x + threadIdx.x;
+    const int colour = blockIdx.y;
+    if (word >= L.lenX * L.nw) return;
+    const int i = word / L.nw, w = word - i * L.nw;
+    const int nvalid = min(64, L.nk - 64 * w);
+    const int q = (i + colour) & 1;
+    const int8_t *src = natural + (size_t)i * L.lenY + 2 * (64 * w) + q;
+    if (LAYOUT == PYMC_LAYOUT_BITS) {
+        uint64_t m = 0;
+        for (int l = 0; l < nvalid; ++l) m |= (uint64_t)(src[2 * l] > 0) << l;
+        L.bits[((size_t)(rep * 2 + colour) * L.lenX + i) * L.nw + w] = m;
+    } else {
+        int8_t *dst = L.i8 + ((size_t)(rep * 2 + colour) * L.lenX + i) * L.nk + 64 * w;
+        for (int l = 0; l < nvalid; ++l) dst[l] = src[2 * l];
+    }
+}
+
+template <int LAYOUT, int MODEL>
+__global__ void unpack_kernel(Lat L, int rep, int8_t *natural) {
+    const int word = blockIdx.x * blockDim.x + threadIdx.x;
+    const int colour = blockIdx.y;
+    if (word >= L.lenX * L.nw) return;
+    const int i = word / L.nw, w = word - i * L.nw;
+    const int nvalid = min(64, L.nk - 64 * w);
+    const int q = (i + colour) & 1;
+    int8_t *dst = natural + (size_t)i * L.lenY + 2 * (64 * w) + q;
+    if (LAYOUT == PYMC_LAYOUT_BITS) {
+        uint64_t m = L.bits[((size_t)(rep * 2 + colour) * L.lenX + i) * L.nw + w];
+        for (int l = 0; l < nvalid; ++l) {
+            int b = (int)((m >> l) & 1u);
+            dst[2 * l] = (MODEL == MODEL_ISING) ? (int8_t)(2 * b - 1) : (int8_t)b;
+        }
+    } else {
+        const int8_t *src = L.i8 + ((size_t)(rep * 2 + colour) * L.lenX + i) * L.nk + 64 * w;
+        for (int l = 0; l < nvalid; ++l) dst[2 * l] = src[l];
+    }
+}
+
+// Hot start from stream domain 1: thread per Philox call = 4 consecutive natural sites.
+template <int LAYOUT, int MODEL>
+__global__ void init_kernel(Lat L) {
+    const int rep = blockIdx.y;
+    const size_t call = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t nsites = (size_t)L.lenX * L.lenY;
+    if (call * 4 >= nsites) return;
+    uint4 o = philox4x32_10((uint32_t)call, (uint32_t)(L.rep_offset + rep), 0u, ctr3(DOMAIN_INIT, 0, 0), L.key);
+    const uint32_t x[4] = {o.x, o.y, o.z, o.w};
+    for (int e = 0; e < 4; ++e) {
+        const size_t site = call * 4 + e;
+        if (site >= nsites) break;
+        const int i = (int)(site / L.lenY), j = (int)(site - (size_t)i * L.lenY);
+        const int colour = (i + j) & 1, k = j >> 1;
+        const int up = x[e] >= 0x80000000u;
+        if (LAYOUT == PYMC_LAYOUT_BITS) {
+            uint64_t *p = L.bits + ((size_t)(rep * 2 + colour) * L.lenX + i) * L.nw + (k >> 6);
+            if (up)
+                atomicOr((unsigned long long *)p, 1ull << (k & 63));
+        } else {
+            L.i8[((size_t)(rep * 2 + colour) * L.lenX + i) * L.nk + k] =
+                (MODEL == MODEL_ISING) ? (int8_t)(2 * up - 1) : (int8_t)up;
+        }
+    }
+}
+
+// K7: site value and neighbour sum for a list of sites (parity helper for trialstep's dE).
+template <int LAYOUT, int MODEL>
+__global__ void propose_kernel(Lat L, int rep, const int32_t *xs, const int32_t *ys, int n, int32_t *site_out,
+                               int32_t *nn_out) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    const int x = xs[t], y = ys[t];
+    auto val = [&](int i, int j) {
+        int b = Loader<LAYOUT>::site(L, rep, (i + j) & 1, i, j >> 1);
+        return (MODEL == MODEL_ISING) ? 2 * b - 1 : b;
+    };
+    const int xm = x == 0 ? L.lenX - 1 : x - 1, xp = x == L.lenX - 1 ? 0 : x + 1;
+    const int ym = y == 0 ? L.lenY - 1 : y - 1, yp = y == L.lenY - 1 ? 0 : y + 1;
+    site_out[t] = val(x, y);
+    nn_out[t] = val(xm, y) + val(xp, y) + val(x, ym) + val(x, yp);
+}
+
+// ------------------------------------------------------------------------------------------
+// handle
+// ------------------------------------------------------------------------------------------
+struct pymc_handle {
+    pymc_params p;
+    int nk, nw, nclass;
+    cudaStream_t own_stream, stream;
+    cudaEvent_t ev0, ev1;
+    int8_t *i8;
+    uint64_t *bits;
+    uint32_t *thr;
+    int32_t *rep_to_T;
+    unsigned long long *tracked;   // [nrep][2]
+    unsigned long long *reduced;   // [nrep][2] output of reduce_kernel
+    int8_t *staging;               // natural int8 image of one replica (upload/download)
+    int32_t *qbuf;                 // propose scratch: x, y, site, nn
+    int qcap;
+    bool tables_set;
+    bool dirty;                    // configurations changed since the tracked observables were based
+    uint64_t sweep_counter;
+};
+
+static Lat make_lat(const pymc_handle *h) {
+    Lat L;
+    L.i8 = h->i8;
+    L.bits = h->bits;
+    L.lenX = h->p.lenX;
+    L.lenY = h->p.lenY;
+    L.nk = h->nk;
+    L.nw = h->nw;
+    L.nrep = h->p.nreplicas;
+    L.rep_offset = h->p.replica_offset;
+    L.thr = h->thr;
+    L.rep_to_T = h->rep_to_T;
+    L.tracked = h->tracked;
+    L.key = make_key(h->p.seed);
+    return L;
+}
+
+struct DeviceGuard {
+    int prev;
+    bool ok;
+    explicit DeviceGuard(int dev) : prev(-1), ok(false) {
+        if (cudaGetDevice(&prev) != cudaSuccess) return;
+        ok = cudaSetDevice(dev) == cudaSuccess;
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+#define ENTER(h)                                                         \
+    REQUIRE((h) != nullptr, PYMC_ERR_BADARG, "%s: null handle", __func__); \
+    DeviceGuard _guard((h)->p.device);                                   \
+    REQUIRE(_guard.ok, PYMC_ERR_CUDA, "%s: cannot select device %d", __func__, (h)->p.device)
+
+// dispatch on (layout, model)
+#define DISPATCH(h, CALL)                                                                            \
+    do {                                                                                             \
+        if ((h)->p.layout == PYMC_LAYOUT_INT8 && (h)->p.model == PYMC_MODEL_ISING) {                 \
+            CALL(PYMC_LAYOUT_INT8, MODEL_ISING);                                                     \
+        } else if ((h)->p.layout == PYMC_LAYOUT_INT8 && (h)->p.model == PYMC_MODEL_LATGAS) {         \
+            CALL(PYMC_LAYOUT_INT8, MODEL_LATGAS);                                                    \
+        } else if ((h)->p.layout == PYMC_LAYOUT_BITS && (h)->p.model == PYMC_MODEL_ISING) {          \
+            CALL(PYMC_LAYOUT_BITS, MODEL_ISING);                                                     \
+        } else {                                                                                     \
+            CALL(PYMC_LAYOUT_BITS, MODEL_LATGAS);                                                    \
+        }                                                                                            \
+    } while (0)
+
+extern "C" {
+
+int pymc_abi_version(void) { return PYMC_ABI_VERSION; }
+
+const char *pymc_last_error(void) { return g_err; }
+
+int pymc_device_count(int *count) {
+    REQUIRE(count, PYMC_ERR_BADARG, "pymc_device_count: null pointer");
+    CUDA_TRY(cudaGetDeviceCount(count));
+    return PYMC_OK;
+}
+
+int pymc_destroy(pymc_handle *h) {
+    if (!h) return PYMC_OK;
+    DeviceGuard guard(h->p.device);
+    if (guard.ok) {
+        if (h->own_stream) cudaStreamSynchronize(h->own_stream);
+        cudaFree(h->i8);
+        cudaFree(h->bits);
+        cudaFree(h->thr);
+        cudaFree(h->rep_to_T);
+        cudaFree(h->tracked);
+        cudaFree(h->reduced);
+        cudaFree(h->staging);
+        cudaFree(h->qbuf);
+        if (h->ev0) cudaEventDestroy(h->ev0);
+        if (h->ev1) cudaEventDestroy(h->ev1);
+        if (h->own_stream) cudaStreamDestroy(h->own_stream);
+    }
+    delete h;
+    return PYMC_OK;
+}
+
+int pymc_create(const pymc_params *p, pymc_handle **out) {
+    REQUIRE(p && out, PYMC_ERR_BADARG, "pymc_create: null pointer");
+    *out = nullptr;
+    REQUIRE(p->abi_version == PYMC_ABI_VERSION, PYMC_ERR_BADARG, "pymc_create: ABI version %d, library has %d",
+            p->abi_version, PYMC_ABI_VERSION);
+    REQUIRE(p->model == PYMC_MODEL_ISING || p->model == PYMC_MODEL_LATGAS, PYMC_ERR_BADARG, "pymc_create: model %d",
+            p->model);
+    REQUIRE(p->layout == PYMC_LAYOUT_INT8 || p->layout == PYMC_LAYOUT_BITS, PYMC_ERR_BADARG,
+            "pymc_create: layout %d", p->layout);
+    REQUIRE(p->lenX >= 2 && p->lenY >= 2, PYMC_ERR_BADARG, "pymc_create: lattice %dx%d too small", p->lenX, p->lenY);
+    REQUIRE(p->lenX % 2 == 0 && p->lenY % 2 == 0, PYMC_ERR_UNSUPPORTED,
+            "pymc_create: checkerboard sweeps need even lenX and lenY (got %dx%d); there is no CPU fallback",
+            p->lenX, p->lenY);
+    REQUIRE(p->layout != PYMC_LAYOUT_BITS || p->lenY % 128 == 0, PYMC_ERR_UNSUPPORTED,
+            "pymc_create: the bit-packed layout needs lenY %% 128 == 0 (got %d)", p->lenY);
+    REQUIRE(p->nreplicas >= 1 && p->nreplicas <= 65535, PYMC_ERR_BADARG, "pymc_create: nreplicas %d not in 1..65535",
+            p->nreplicas);
+    REQUIRE(p->nreplicas_global >= p->nreplicas && p->replica_offset >= 0 &&
+                p->replica_offset + p->nreplicas <= p->nreplicas_global,
+            PYMC_ERR_BADARG, "pymc_create: replica partition [%d,+%d) outside 0..%d", p->replica_offset, p->nreplicas,
+            p->nreplicas_global);
+    REQUIRE(p->ntemps >= 1, PYMC_ERR_BADARG, "pymc_create: ntemps %d", p->ntemps);
+    int ndev = 0;
+    CUDA_TRY(cudaGetDeviceCount(&ndev));
+    REQUIRE(p->device >= 0 && p->device < ndev, PYMC_ERR_BADARG, "pymc_create: device %d of %d", p->device, ndev);
+
+    pymc_handle *h = new (std::nothrow) pymc_handle();
+    REQUIRE(h, PYMC_ERR_BADARG, "pymc_create: out of host memory");
+    memset(h, 0, sizeof(*h));
+    h->p = *p;
+    h->nk = p->lenY / 2;
+    h->nw = (h->nk + 63) / 64;
+    h->nclass = p->model == PYMC_MODEL_ISING ? PYMC_NCLASS_ISING : PYMC_NCLASS_LATGAS;
+    REQUIRE((uint64_t)p->lenX * h->nw < (1ull << 31), PYMC_ERR_UNSUPPORTED, "pymc_create: lattice too large");
+
+    DeviceGuard guard(p->device);
+    int rc = PYMC_OK;
+    auto check = [&](cudaError_t e, const char *what) {
+        if (e != cudaSuccess && rc == PYMC_OK)
+            rc = fail(PYMC_ERR_CUDA, "pymc_create: %s failed: %s", what, cudaGetErrorString(e));
+    };
+    if (!guard.ok) rc = fail(PYMC_ERR_CUDA, "pymc_create: cannot select device %d", p->device);
+    if (rc == PYMC_OK) {
+        check(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking), "cudaStreamCreate");
+        h->stream = h->own_stream;
+        check(cudaEventCreate(&h->ev0), "cudaEventCreate");
+        check(cudaEventCreate(&h->ev1), "cudaEventCreate");
+        const size_t nrep = p->nreplicas;
+        if (p->layout == PYMC_LAYOUT_INT8) {
+            check(cudaMalloc(&h->i8, nrep * 2 * p->lenX * (size_t)h->nk), "cudaMalloc(spins)");
+        } else {
+            check(cudaMalloc(&h->bits, nrep * 2 * p->lenX * (size_t)h->nw * 8), "cudaMalloc(bits)");
+        }
+        check(cudaMalloc(&h->thr, (size_t)p->ntemps * h->nclass * 4), "cudaMalloc(thr)");
+        check(cudaMalloc(&h->rep_to_T, (size_t)p->nreplicas_global * 4), "cudaMalloc(rep_to_T)");
+        check(cudaMalloc(&h->tracked, nrep * 16), "cudaMalloc(tracked)");
+        check(cudaMalloc(&h->reduced, nrep * 16), "cudaMalloc(reduced)");
+    }
+    if (rc == PYMC_OK) {
+        if (h->i8) check(cudaMemsetAsync(h->i8, 0, (size_t)p->nreplicas * 2 * p->lenX * h->nk, h->stream), "memset");
+        if (h->bits)
+            check(cudaMemsetAsync(h->bits, 0, (size_t)p->nreplicas * 2 * p->lenX * h->nw * 8, h->stream), "memset");
+        check(cudaMemsetAsync(h->tracked, 0, (size_t)p->nreplicas * 16, h->stream), "memset");
+        // default map: replica r -> row r (or row 0 when there is a single temperature)
+        int32_t *map = new int32_t[p->nreplicas_global];
+        for (int r = 0; r < p->nreplicas_global; ++r) map[r] = p->ntemps == p->nreplicas_global ? r : 0;
+        check(cudaMemcpyAsync(h->rep_to_T, map, (size_t)p->nreplicas_global * 4, cudaMemcpyHostToDevice, h->stream),
+              "memcpy(rep_to_T)");
+        check(cudaStreamSynchronize(h->stream), "cudaStreamSynchronize");
+        delete[] map;
+    }
+    if (rc != PYMC_OK) {
+        char keep[sizeof(g_err)];
+        memcpy(keep, g_err, sizeof(keep));
+        pymc_destroy(h);
+        memcpy(g_err, keep, sizeof(keep));
+        return rc;
+    }
+    *out = h;
+    return PYMC_OK;
+}
+
+int pymc_set_stream(pymc_handle *h, void *cuda_stream) {
+    ENTER(h);
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    h->stream = cuda_stream ? (cudaStream_t)cuda_stream : h->own_stream;
+    return PYMC_OK;
+}
+
+int pymc_synchronize(pymc_handle *h) {
+    ENTER(h);
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return PYMC_OK;
+}
+
+static int ensure_staging(pymc_handle *h) {
+    if (!h->staging) CUDA_TRY(cudaMalloc(&h->staging, (size_t)h->p.lenX * h->p.lenY));
+    return PYMC_OK;
+}
+
+int pymc_upload_config(pymc_handle *h, int replica, const int8_t *host, size_t nsites) {
+    ENTER(h);
+    REQUIRE(host, PYMC_ERR_BADARG, "pymc_upload_config: null host pointer");
+    REQUIRE(replica >= 0 && replica < h->p.nreplicas, PYMC_ERR_BADARG, "pymc_upload_config: replica %d of %d", replica,
+            h->p.nreplicas);
+    REQUIRE(nsites == (size_t)h->p.lenX * h->p.lenY, PYMC_ERR_BADARG, "pymc_upload_config: %zu sites, lattice has %zu",
+            nsites, (size_t)h->p.lenX * h->p.lenY);
+    int rc = ensure_staging(h);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemcpyAsync(h->staging, host, nsites, cudaMemcpyHostToDevice, h->stream));
+    Lat L = make_lat(h);
+    dim3 grid((h->p.lenX * h->nw + 127) / 128, 2);
+    if (h->p.layout == PYMC_LAYOUT_BITS)
+        pack_kernel<PYMC_LAYOUT_BITS><<<grid, 128, 0, h->stream>>>(L, replica, h->staging);
+    else
+        pack_kernel<PYMC_LAYOUT_INT8><<<grid, 128, 0, h->stream>>>(L, replica, h->staging);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaStreamSynchronize(h->stream));  // the host buffer may be reused on return
+    h->dirty = true;
+    return PYMC_OK;
+}
+
+int pymc_download_config(pymc_handle *h, int replica, int8_t *host, size_t nsites) {
+    ENTER(h);
+    REQUIRE(host, PYMC_ERR_BADARG, "pymc_download_config: null host pointer");
+    REQUIRE(replica >= 0 && replica < h->p.nreplicas, PYMC_ERR_BADARG, "pymc_download_config: replica %d of %d",
+            replica, h->p.nreplicas);
+    REQUIRE(nsites == (size_t)h->p.lenX * h->p.lenY, PYMC_ERR_BADARG,
+            "pymc_download_config: %zu sites, lattice has %zu", nsites, (size_t)h->p.lenX * h->p.lenY);
+    int rc = ensure_staging(h);
+    if (rc) return rc;
+    Lat L = make_lat(h);
+    dim3 grid((h->p.lenX * h->nw + 127) / 128, 2);
+#define CALL_UNPACK(LAY, MOD) unpack_kernel<LAY, MOD><<<grid, 128, 0, h->stream>>>(L, replica, h->staging)
+    DISPATCH(h, CALL_UNPACK);
+#undef CALL_UNPACK
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpyAsync(host, h->staging, nsites, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return PYMC_OK;
+}
+
+static int rebase_tracked(pymc_handle *h);
+
+int pymc_init_random(pymc_handle *h) {
+    ENTER(h);
+    Lat L = make_lat(h);
+    if (h->bits) CUDA_TRY(cudaMemsetAsync(h->bits, 0, (size_t)h->p.nreplicas * 2 * h->p.lenX * h->nw * 8, h->stream));
+    const size_t ncalls = ((size_t)h->p.lenX * h->p.lenY + 3) / 4;
+    dim3 grid((unsigned)((ncalls + 255) / 256), h->p.nreplicas);
+#define CALL_INIT(LAY, MOD) init_kernel<LAY, MOD><<<grid, 256, 0, h->stream>>>(L)
+    DISPATCH(h, CALL_INIT);
+#undef CALL_INIT
+    CUDA_TRY(cudaGetLastError());
+    return rebase_tracked(h);
+}
+
+int pymc_set_accept_tables(pymc_handle *h, const uint32_t *thr, int ntemps, int nclass) {
+    ENTER(h);
+    REQUIRE(thr, PYMC_ERR_BADARG, "pymc_set_accept_tables: null pointer");
+    REQUIRE(ntemps == h->p.ntemps && nclass == h->nclass, PYMC_ERR_BADARG,
+            "pymc_set_accept_tables: got %d x %d, handle expects %d x %d", ntemps, nclass, h->p.ntemps, h->nclass);
+    CUDA_TRY(cudaMemcpyAsync(h->thr, thr, (size_t)ntemps * nclass * 4, cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    h->tables_set = true;
+    return PYMC_OK;
+}
+
+int pymc_set_replica_to_T(pymc_handle *h, const int32_t *map, int n) {
+    ENTER(h);
+    REQUIRE(map && n == h->p.nreplicas_global, PYMC_ERR_BADARG, "pymc_set_replica_to_T: need %d entries, got %d",
+            h->p.nreplicas_global, n);
+    for (int r = 0; r < n; ++r)
+        REQUIRE(map[r] >= 0 && map[r] < h->p.ntemps, PYMC_ERR_BADARG, "pymc_set_replica_to_T: map[%d] = %d not in 0..%d",
+                r, map[r], h->p.ntemps - 1);
+    CUDA_TRY(cudaMemcpyAsync(h->rep_to_T, map, (size_t)n * 4, cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return PYMC_OK;
+}
+
+int pymc_get_replica_to_T(pymc_handle *h, int32_t *map, int n) {
+    ENTER(h);
+    REQUIRE(map && n == h->p.nreplicas_global, PYMC_ERR_BADARG, "pymc_get_replica_to_T: need %d entries, got %d",
+            h->p.nreplicas_global, n);
+    CUDA_TRY(cudaMemcpyAsync(map, h->rep_to_T, (size_t)n * 4, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return PYMC_OK;
+}
+
+int pymc_sweep(pymc_handle *h, int64_t nsweeps) {
+    ENTER(h);
+    REQUIRE(nsweeps >= 0, PYMC_ERR_BADARG, "pymc_sweep: nsweeps %lld", (long long)nsweeps);
+    REQUIRE(h->tables_set, PYMC_ERR_STATE, "pymc_sweep: call pymc_set_accept_tables first");
+    if (h->dirty) {
+        int rc = rebase_tracked(h);
+        if (rc) return rc;
+    }
+    Lat L = make_lat(h);
+    dim3 grid((h->p.lenX * h->nw + 127) / 128, h->p.nreplicas);
+    for (int64_t s = 0; s < nsweeps; ++s) {
+        for (int colour = 0; colour < 2; ++colour) {
+            const uint64_t step = 2 * h->sweep_counter + colour;
+#define CALL_SWEEP(LAY, MOD) sweep_word_kernel<LAY, MOD><<<grid, 128, 0, h->stream>>>(L, colour, step)
+            DISPATCH(h, CALL_SWEEP);
+#undef CALL_SWEEP
+        }
+        h->sweep_counter++;
+    }
+    CUDA_TRY(cudaGetLastError());
+    return PYMC_OK;
+}
+
+int pymc_get_sweep_counter(pymc_handle *h, uint64_t *counter) {
+    REQUIRE(h && counter, PYMC_ERR_BADARG, "pymc_get_sweep_counter: null pointer");
+    *counter = h->sweep_counter;
+    return PYMC_OK;
+}
+
+int pymc_set_sweep_counter(pymc_handle *h, uint64_t counter) {
+    REQUIRE(h, PYMC_ERR_BADARG, "pymc_set_sweep_counter: null handle");
+    REQUIRE(counter < (1ull << 55), PYMC_ERR_BADARG, "pymc_set_sweep_counter: counter too large");
+    h->sweep_counter = counter;
+    return PYMC_OK;
+}
+
+// recompute bond/second into h->reduced and copy them over the tracked values (all async)
+static int rebase_tracked(pymc_handle *h) {
+    Lat L = make_lat(h);
+    CUDA_TRY(cudaMemsetAsync(h->reduced, 0, (size_t)h->p.nreplicas * 16, h->stream));
+    dim3 grid((2 * h->p.lenX * h->nw + 255) / 256, h->p.nreplicas);
+#define CALL_REDUCE(LAY, MOD) reduce_kernel<LAY, MOD><<<grid, 256, 0, h->stream>>>(L, h->reduced)
+    DISPATCH(h, CALL_REDUCE);
+#undef CALL_REDUCE
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpyAsync(h->tracked, h->reduced, (size_t)h->p.nreplicas * 16, cudaMemcpyDeviceToDevice, h->stream));
+    h->dirty = false;
+    return PYMC_OK;
+}
+
+static int fetch_pairs(pymc_handle *h, const unsigned long long *dev, int64_t *bond, int64_t *second) {
+    const int n = h->p.nreplicas;
+    long long *tmp = new (std::nothrow) long long[2 * (size_t)n];
+    REQUIRE(tmp, PYMC_ERR_BADARG, "out of host memory");
+    cudaError_t e = cudaMemcpyAsync(tmp, dev, (size_t)n * 16, cudaMemcpyDeviceToHost, h->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    if (e != cudaSuccess) {
+        delete[] tmp;
+        return fail(PYMC_ERR_CUDA, "observable copy failed: %s", cudaGetErrorString(e));
+    }
+    for (int r = 0; r < n; ++r) {
+        if (bond) bond[r] = tmp[2 * r];
+        if (second) second[r] = tmp[2 * r + 1];
+    }
+    delete[] tmp;
+    return PYMC_OK;
+}
+
+int pymc_reduce_observables(pymc_handle *h, int64_t *bond, int64_t *second) {
+    ENTER(h);
+    int rc = rebase_tracked(h);
+    if (rc) return rc;
+    return fetch_pairs(h, h->reduced, bond, second);
+}
+
+int pymc_get_tracked(pymc_handle *h, int64_t *bond, int64_t *second) {
+    ENTER(h);
+    if (h->dirty) {
+        int rc = rebase_tracked(h);
+        if (rc) return rc;
+    }
+    return fetch_pairs(h, h->tracked, bond, second);
+}
+
+int pymc_propose(pymc_handle *h, int replica, const int32_t *x, const int32_t *y, int n, int32_t *site_out,
+                 int32_t *nnsum_out) {
+    ENTER(h);
+    REQUIRE(x && y && site_out && nnsum_out, PYMC_ERR_BADARG, "pymc_propose: null pointer");
+    REQUIRE(replica >= 0 && replica < h->p.nreplicas, PYMC_ERR_BADARG, "pymc_propose: replica %d of %d", replica,
+            h->p.nreplicas);
+    REQUIRE(n >= 0, PYMC_ERR_BADARG, "pymc_propose: n = %d", n);
+    if (n == 0) return PYMC_OK;
+    for (int t = 0; t < n; ++t)
+        REQUIRE(x[t] >= 0 && x[t] < h->p.lenX && y[t] >= 0 && y[t] < h->p.lenY, PYMC_ERR_BADARG,
+                "pymc_propose: site %d = (%d,%d) outside %dx%d", t, x[t], y[t], h->p.lenX, h->p.lenY);
+    if (n > h->qcap) {
+        cudaFree(h->qbuf);
+        h->qbuf = nullptr;
+        h->qcap = 0;
+        CUDA_TRY(cudaMalloc(&h->qbuf, (size_t)n * 16));
+        h->qcap = n;
+    }
+    int32_t *dx = h->qbuf, *dy = dx + n, *ds = dy + n, *dn = ds + n;
+    CUDA_TRY(cudaMemcpyAsync(dx, x, (size_t)n * 4, cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(cudaMemcpyAsync(dy, y, (size_t)n * 4, cudaMemcpyHostToDevice, h->stream));
+    Lat L = make_lat(h);
+#define CALL_PROPOSE(LAY, MOD) \
+    propose_kernel<LAY, MOD><<<(n + 127) / 128, 128, 0, h->stream>>>(L, replica, dx, dy, n, ds, dn)
+    DISPATCH(h, CALL_PROPOSE);
+#undef CALL_PROPOSE
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpyAsync(site_out, ds, (size_t)n * 4, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaMemcpyAsync(nnsum_out, dn, (size_t)n * 4, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return PYMC_OK;
+}
+
+int pymc_timer_start(pymc_handle *h) {
+    ENTER(h);
+    CUDA_TRY(cudaEventRecord(h->ev0, h->stream));
+    return PYMC_OK;
+}
+
+int pymc_timer_stop(pymc_handle *h, float *elapsed_ms) {
+    ENTER(h);
+    REQUIRE(elapsed_ms, PYMC_ERR_BADARG, "pymc_timer_stop: null pointer");
+    CUDA_TRY(cudaEventRecord(h->ev1, h->stream));
+    CUDA_TRY(cudaEventSynchronize(h->ev1));
+    CUDA_TRY(cudaEventElapsedTime(elapsed_ms, h->ev0, h->ev1));
+    return PYMC_OK;
+}
+
+}  // extern "C"

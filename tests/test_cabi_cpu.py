@@ -1,0 +1,61 @@
+"""CPU: the C-ABI library builds, loads and exports every symbol include/pymc_b200.h declares.
+No compute calls here (there is no GPU in the build container)."""
+import ctypes
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    text = open(os.path.join(ROOT, "include", "pymc_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(pymc_[A-Za-z0-9_]+)\s*\(", text)))
+
+
+def test_library_builds_and_exports_all_declared_symbols():
+    from py_mc_b200 import _build
+    path = _build.build()
+    assert os.path.exists(path)
+    lib = ctypes.CDLL(path)
+    declared = _declared_symbols()
+    assert len(declared) >= 20
+    for name in declared:
+        assert hasattr(lib, name), "library does not export %s" % name
+
+
+def test_binding_covers_header():
+    from py_mc_b200 import _cabi
+    assert sorted(_cabi.SYMBOLS) == _declared_symbols()
+    assert _cabi.lib.pymc_abi_version() == _cabi.ABI_VERSION
+
+
+def test_params_struct_matches_header_layout():
+    from py_mc_b200 import _cabi
+    # 10 x int32, uint64 (8-aligned at offset 40), 2 x int32
+    assert _cabi.Params.seed.offset == 40
+    assert ctypes.sizeof(_cabi.Params) == 56
+
+
+def test_errors_are_reported_not_swallowed():
+    from py_mc_b200 import _cabi
+    # null params -> BADARG with a message, no crash, no GPU needed
+    rc = _cabi.lib.pymc_create(None, None)
+    assert rc == -1
+    assert b"null" in _cabi.lib.pymc_last_error()
+    with pytest.raises(_cabi.PymcError):
+        _cabi.check(rc)
+
+
+def test_sass_has_no_local_memory_spills_in_sweep_kernels():
+    # cheap static check that stays valid without a GPU: the hot kernels must not spill
+    import subprocess
+    from py_mc_b200 import _build
+    out = subprocess.run(["cuobjdump", "-res-usage", _build.build()], capture_output=True, text=True).stdout
+    blocks = re.findall(r"Function (\S*sweep\S*):\s*\n\s*(.*)", out)
+    assert blocks, out[:400]
+    for name, usage in blocks:
+        m = re.search(r"STACK:(\d+)", usage)
+        assert m and int(m.group(1)) == 0, (name, usage)
