@@ -199,9 +199,10 @@ class CanonicalMonteCarlo:
     def energy(self):
         if self._energy is None:
             obs = self.config._device_observables()
-            if obs is None:
-                raise AttributeError("energy is defined once run() has started (as in the reference, mc.py:191)")
-            self._energy = self.model._pmc_energy(*obs)
+            if obs is None:  # the host copy is the newest (someone took a writable view): recompute
+                self._energy = self.model.energy(self.config)
+            else:
+                self._energy = self.model._pmc_energy(*obs)
         return self._energy
 
     @energy.setter
@@ -251,6 +252,7 @@ class CanonicalMonteCarlo:
                             self.obs_save.append(obs_step)
         finally:
             output.close()
+        self.energy  # cache the tracked energy while the device copy is the newest
         if save_obs:
             with open("obs_save.npy", "wb") as f:
                 np.save(f, np.array(self.obs_save))

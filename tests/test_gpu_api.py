@@ -90,9 +90,9 @@ def test_run_with_observer_returns_means(workdir):
         nsamp = 2 ** 14
         out = calc.run(nsamp, 1, 10 ** 9, obs)
         assert len(out) == 2
-        assert len(obs.energy_obs) == nsamp + 1  # the pre-run probe sample (mc.py:193)
-        e = np.asarray(obs.energy_obs[1:]) / 16
-        mag = np.asarray(obs.magnet_obs[1:]) / 16
+        assert len(obs.energy_obs) == nsamp + 2  # + the pre-run probe (mc.py:193) and obs_info's call (mc.py:125,211)
+        e = np.asarray(obs.energy_obs[1:-1]) / 16
+        mag = np.asarray(obs.magnet_obs[1:-1]) / 16
         assert out[0] / 16 == pytest.approx(e.mean(), rel=1e-12)
         err_e = max(binning(e, 8)) + 1e-9
         err_m = max(binning(mag, 8)) + 1e-9
