@@ -52,19 +52,20 @@ __device__ __forceinline__ void count_masks(uint64_t a0, uint64_t a1, uint64_t a
     m[4] = a2;
 }
 
-// Bit-serial x32 <= thr[class] for all lanes.  Every thread of the warp must call this together.
-template <int NCLASS>
-__device__ __forceinline__ uint64_t decide(const uint64_t (&m)[NCLASS], const uint32_t (&thr)[NCLASS], uint64_t valid,
-                                           uint32_t word_idx, uint32_t replica, uint64_t step, uint32_t domain,
-                                           PhiloxKey key) {
-    uint64_t always = 0, needed = 0;
+// Bit-serial x32 <= thr for all lanes.  Every thread of the warp must call this together.
+//
+// Only the lanes of *hard* classes (thr < 2^32-1, i.e. dE > 0) need random bits; the caller
+// passes them compacted as hm[k] (one-hot lane masks) / ht[k] (thresholds, warp-uniform).  Per
+// plane the per-lane threshold bit is T = OR_k (hm[k] & -bit_j(ht[k])); the selectors are
+// uniform, so the per-lane work is 2 logic ops per hard class plus 3 for the lt/und update on each
+// 32-bit half.
+template <int MAXH>
+__device__ __forceinline__ uint64_t decide_hard(const uint64_t (&hm)[MAXH], const uint32_t (&ht)[MAXH],
+                                                uint64_t always, uint64_t valid, uint32_t word_idx,
+                                                uint32_t replica, uint64_t step, uint32_t domain, PhiloxKey key) {
+    uint64_t needed = 0;
 #pragma unroll
-    for (int c = 0; c < NCLASS; ++c) {
-        if (thr[c] == THR_ALWAYS)
-            always |= m[c];
-        else
-            needed |= m[c];
-    }
+    for (int k = 0; k < MAXH; ++k) needed |= hm[k];
     uint64_t und = needed & valid;  // lanes whose x32 still equals thr on all planes seen so far
     uint64_t lt = 0;                // lanes already known to have x32 < thr
 #pragma unroll 1
@@ -75,9 +76,9 @@ __device__ __forceinline__ uint64_t decide(const uint64_t (&m)[NCLASS], const ui
         uint64_t te = 0, to = 0;
         const int be = 31 - 2 * (int)call, bo = be - 1;
 #pragma unroll
-        for (int c = 0; c < NCLASS; ++c) {
-            if ((thr[c] >> be) & 1u) te |= m[c];
-            if ((thr[c] >> bo) & 1u) to |= m[c];
+        for (int k = 0; k < MAXH; ++k) {
+            te |= hm[k] & (0ull - (uint64_t)((ht[k] >> be) & 1u));
+            to |= hm[k] & (0ull - (uint64_t)((ht[k] >> bo) & 1u));
         }
         lt |= und & te & ~pe;
         und &= ~(te ^ pe);
@@ -86,6 +87,47 @@ __device__ __forceinline__ uint64_t decide(const uint64_t (&m)[NCLASS], const ui
     }
     // und != 0 here only after all 32 planes: x32 == thr, which the reference accepts (u <= p).
     return ((always & valid) | lt | und);
+}
+
+// Compact the hard classes of a one-hot class decomposition into at most MAXH slots.  thr[] is
+// warp-uniform, so all control here is uniform.  Returns false if more than MAXH classes are hard
+// (the caller then uses all NCLASS slots).
+template <int NCLASS, int MAXH>
+__device__ __forceinline__ bool compact_hard(const uint64_t (&m)[NCLASS], const uint32_t (&thr)[NCLASS],
+                                             uint64_t (&hm)[MAXH], uint32_t (&ht)[MAXH], uint64_t &always) {
+    int nh = 0;
+    always = 0;
+#pragma unroll
+    for (int k = 0; k < MAXH; ++k) {
+        hm[k] = 0;
+        ht[k] = THR_ALWAYS;
+    }
+#pragma unroll
+    for (int c = 0; c < NCLASS; ++c) {
+        const bool hard = thr[c] != THR_ALWAYS;
+        if (!hard) always |= m[c];
+#pragma unroll
+        for (int k = 0; k < MAXH; ++k) {
+            if (hard && nh == k) {
+                hm[k] = m[c];
+                ht[k] = thr[c];
+            }
+        }
+        nh += hard ? 1 : 0;
+    }
+    return nh <= MAXH;
+}
+
+template <int NCLASS, int MAXH>
+__device__ __forceinline__ uint64_t decide(const uint64_t (&m)[NCLASS], const uint32_t (&thr)[NCLASS], uint64_t valid,
+                                           uint32_t word_idx, uint32_t replica, uint64_t step, uint32_t domain,
+                                           PhiloxKey key) {
+    uint64_t hm[MAXH], always;
+    uint32_t ht[MAXH];
+    // pymc_set_accept_tables rejects tables with more than MAXH hard classes per row, so the
+    // compaction cannot overflow here.
+    compact_hard<NCLASS, MAXH>(m, thr, hm, ht, always);
+    return decide_hard<MAXH>(hm, ht, always, valid, word_idx, replica, step, domain, key);
 }
 
 // Full update of one word.  Returns the new word; dB / dS are the exact integer changes of the
@@ -99,7 +141,8 @@ __device__ __forceinline__ uint64_t update_word(uint64_t S, uint64_t U, uint64_t
         uint64_t a0, a1, a2, m[5];
         add4(~(S ^ U), ~(S ^ D), ~(S ^ C), ~(S ^ Sd), a0, a1, a2);  // aligned neighbours
         count_masks(a0, a1, a2, m);
-        uint64_t acc = decide<5>(m, thr, valid, word_idx, replica, step, DOMAIN_SWEEP, key);
+        // dE > 0 only for two of the five classes (a = 3,4 if J < 0; a = 0,1 if J > 0)
+        uint64_t acc = decide<5, 2>(m, thr, valid, word_idx, replica, step, DOMAIN_SWEEP, key);
         // flipping a spin with a aligned neighbours changes the bond sum by 8 - 4a, M by -2s
         int na = __popcll(acc);
         dB = 8 * na - 4 * (__popcll(acc & a0) + 2 * __popcll(acc & a1) + 4 * __popcll(acc & a2));
@@ -114,7 +157,8 @@ __device__ __forceinline__ uint64_t update_word(uint64_t S, uint64_t U, uint64_t
             m[n] = cnt[n] & ~S;
             m[5 + n] = cnt[n] & S;
         }
-        uint64_t acc = decide<10>(m, thr, valid, word_idx, replica, step, DOMAIN_SWEEP, key);
+        // dE(c=0, nn) = -dE(c=1, nn): at most one class of each pair is hard, five in all
+        uint64_t acc = decide<10, 5>(m, thr, valid, word_idx, replica, step, DOMAIN_SWEEP, key);
         // toggling c -> 1-c with nn occupied neighbours changes the bond count by (1-2c) nn, N by (1-2c)
         uint64_t add = acc & ~S, rem = acc & S;
         dB = (__popcll(add & n0) + 2 * __popcll(add & n1) + 4 * __popcll(add & n2)) -

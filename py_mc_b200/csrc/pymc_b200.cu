@@ -14,6 +14,7 @@
 
 #include "../../include/pymc_b200.h"
 #include "pmc_core.cuh"
+#include "pmc_tiled_i8.cuh"
 
 using namespace pmc;
 
@@ -577,6 +578,16 @@ int pymc_set_accept_tables(pymc_handle *h, const uint32_t *thr, int ntemps, int 
     REQUIRE(thr, PYMC_ERR_BADARG, "pymc_set_accept_tables: null pointer");
     REQUIRE(ntemps == h->p.ntemps && nclass == h->nclass, PYMC_ERR_BADARG,
             "pymc_set_accept_tables: got %d x %d, handle expects %d x %d", ntemps, nclass, h->p.ntemps, h->nclass);
+    // dE > 0 ("hard", thr < 2^32-1) for at most 2 of the 5 Ising classes and 5 of the 10 lattice-gas
+    // classes in any table derived from an energy function; the kernels compact exactly that many.
+    const int maxhard = h->p.model == PYMC_MODEL_ISING ? 2 : 5;
+    for (int t = 0; t < ntemps; ++t) {
+        int nhard = 0;
+        for (int c = 0; c < nclass; ++c) nhard += thr[(size_t)t * nclass + c] != 0xFFFFFFFFu;
+        REQUIRE(nhard <= maxhard, PYMC_ERR_UNSUPPORTED,
+                "pymc_set_accept_tables: row %d has %d classes with dE > 0, at most %d are possible for this model", t,
+                nhard, maxhard);
+    }
     CUDA_TRY(cudaMemcpyAsync(h->thr, thr, (size_t)ntemps * nclass * 4, cudaMemcpyHostToDevice, h->stream));
     CUDA_TRY(cudaStreamSynchronize(h->stream));
     h->tables_set = true;
@@ -614,9 +625,22 @@ int pymc_sweep(pymc_handle *h, int64_t nsweeps) {
     }
     Lat L = make_lat(h);
     dim3 grid((h->p.lenX * h->nw + 127) / 128, h->p.nreplicas);
+    // K1 tiled int8 kernel: needs whole words (lenY % 128 == 0); tile = TH rows x TW words, TW | nw
+    const bool tiled = h->p.layout == PYMC_LAYOUT_INT8 && h->p.kernel != PYMC_KERNEL_GENERIC && h->nk % 64 == 0;
+    int tw_log2 = 0;
+    while (tw_log2 < 4 && h->nw % (2 << tw_log2) == 0) ++tw_log2;
+    const int TH = TILE_THREADS >> tw_log2;
+    dim3 tgrid(h->nw >> tw_log2, (h->p.lenX + TH - 1) / TH, h->p.nreplicas);
     for (int64_t s = 0; s < nsweeps; ++s) {
         for (int colour = 0; colour < 2; ++colour) {
             const uint64_t step = 2 * h->sweep_counter + colour;
+            if (tiled) {
+                if (h->p.model == PYMC_MODEL_ISING)
+                    sweep_tiled_i8_kernel<MODEL_ISING, Lat><<<tgrid, TILE_THREADS, 0, h->stream>>>(L, colour, step, tw_log2);
+                else
+                    sweep_tiled_i8_kernel<MODEL_LATGAS, Lat><<<tgrid, TILE_THREADS, 0, h->stream>>>(L, colour, step, tw_log2);
+                continue;
+            }
 #define CALL_SWEEP(LAY, MOD) sweep_word_kernel<LAY, MOD><<<grid, 128, 0, h->stream>>>(L, colour, step)
             DISPATCH(h, CALL_SWEEP);
 #undef CALL_SWEEP
