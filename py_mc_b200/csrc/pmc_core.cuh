@@ -89,78 +89,83 @@ __device__ __forceinline__ uint64_t decide_hard(const uint64_t (&hm)[MAXH], cons
     return ((always & valid) | lt | und);
 }
 
-// Compact the hard classes of a one-hot class decomposition into at most MAXH slots.  thr[] is
-// warp-uniform, so all control here is uniform.  Returns false if more than MAXH classes are hard
-// (the caller then uses all NCLASS slots).
-template <int NCLASS, int MAXH>
-__device__ __forceinline__ bool compact_hard(const uint64_t (&m)[NCLASS], const uint32_t (&thr)[NCLASS],
-                                             uint64_t (&hm)[MAXH], uint32_t (&ht)[MAXH], uint64_t &always) {
-    int nh = 0;
-    always = 0;
-#pragma unroll
-    for (int k = 0; k < MAXH; ++k) {
-        hm[k] = 0;
-        ht[k] = THR_ALWAYS;
-    }
-#pragma unroll
-    for (int c = 0; c < NCLASS; ++c) {
-        const bool hard = thr[c] != THR_ALWAYS;
-        if (!hard) always |= m[c];
-#pragma unroll
-        for (int k = 0; k < MAXH; ++k) {
-            if (hard && nh == k) {
-                hm[k] = m[c];
-                ht[k] = thr[c];
-            }
-        }
-        nh += hard ? 1 : 0;
-    }
-    return nh <= MAXH;
-}
+// ------------------------------------------------------------------------------------------
+// Per-temperature plans: everything that depends only on the (warp-uniform) threshold row is
+// worked out once per thread, outside the per-word path.
+// ------------------------------------------------------------------------------------------
+template <int MODEL>
+struct Plan;
 
-template <int NCLASS, int MAXH>
-__device__ __forceinline__ uint64_t decide(const uint64_t (&m)[NCLASS], const uint32_t (&thr)[NCLASS], uint64_t valid,
-                                           uint32_t word_idx, uint32_t replica, uint64_t step, uint32_t domain,
-                                           PhiloxKey key) {
-    uint64_t hm[MAXH], always;
-    uint32_t ht[MAXH];
-    // pymc_set_accept_tables rejects tables with more than MAXH hard classes per row, so the
-    // compaction cannot overflow here.
-    compact_hard<NCLASS, MAXH>(m, thr, hm, ht, always);
-    return decide_hard<MAXH>(hm, ht, always, valid, word_idx, replica, step, domain, key);
-}
+// Ising.  dE = -2J(2a-4) with a = aligned neighbours, so dE > 0 for a in {3,4} when J < 0 and for
+// a in {0,1} when J > 0 (pymc_set_accept_tables rejects anything else).  Counting *anti*-aligned
+// neighbours in the second case maps it onto the first: the hard classes are always count 3 and 4.
+template <>
+struct Plan<MODEL_ISING> {
+    uint64_t notmask;  // ~0: count aligned neighbours; 0: count anti-aligned neighbours
+    uint64_t en3, en4;  // ~0 where the class needs a draw
+    uint32_t ht[2];
+    int sign;           // +1 / -1: orientation of the bond-sum change
+    __device__ __forceinline__ void init(const uint32_t *__restrict__ thr) {
+        const uint32_t t0 = __ldg(thr + 0), t1 = __ldg(thr + 1), t3 = __ldg(thr + 3), t4 = __ldg(thr + 4);
+        const bool low = (t0 != THR_ALWAYS) || (t1 != THR_ALWAYS);
+        notmask = low ? 0ull : ~0ull;
+        sign = low ? -1 : 1;
+        ht[0] = low ? t1 : t3;
+        ht[1] = low ? t0 : t4;
+        en3 = ht[0] != THR_ALWAYS ? ~0ull : 0ull;
+        en4 = ht[1] != THR_ALWAYS ? ~0ull : 0ull;
+    }
+};
+
+// Lattice gas.  Class = 5c + nn; dE(c=0,nn) = -dE(c=1,nn), so for each nn at most one of the two
+// occupancies needs a draw.
+template <>
+struct Plan<MODEL_LATGAS> {
+    uint64_t sel[5];  // XOR-ed with S: result 1 = lane is in the hard occupancy for this nn
+    uint64_t en[5];   // ~0 if that nn has a hard class at all
+    uint32_t ht[5];
+    __device__ __forceinline__ void init(const uint32_t *__restrict__ thr) {
+#pragma unroll
+        for (int n = 0; n < 5; ++n) {
+            const uint32_t te = __ldg(thr + n), to = __ldg(thr + 5 + n);  // empty / occupied site
+            const bool hard_occ = to != THR_ALWAYS;
+            sel[n] = hard_occ ? 0ull : ~0ull;
+            ht[n] = hard_occ ? to : te;
+            en[n] = ht[n] != THR_ALWAYS ? ~0ull : 0ull;
+        }
+    }
+};
 
 // Full update of one word.  Returns the new word; dB / dS are the exact integer changes of the
 // bond sum and of the second observable (magnetisation or particle number) caused by this word.
 template <int MODEL>
 __device__ __forceinline__ uint64_t update_word(uint64_t S, uint64_t U, uint64_t D, uint64_t C, uint64_t Sd,
-                                                uint64_t valid, const uint32_t (&thr)[ModelTraits<MODEL>::NCLASS],
-                                                uint32_t word_idx, uint32_t replica, uint64_t step, PhiloxKey key,
-                                                int &dB, int &dS) {
+                                                uint64_t valid, const Plan<MODEL> &plan, uint32_t word_idx,
+                                                uint32_t replica, uint64_t step, PhiloxKey key, int &dB, int &dS) {
     if constexpr (MODEL == MODEL_ISING) {
-        uint64_t a0, a1, a2, m[5];
-        add4(~(S ^ U), ~(S ^ D), ~(S ^ C), ~(S ^ Sd), a0, a1, a2);  // aligned neighbours
-        count_masks(a0, a1, a2, m);
-        // dE > 0 only for two of the five classes (a = 3,4 if J < 0; a = 0,1 if J > 0)
-        uint64_t acc = decide<5, 2>(m, thr, valid, word_idx, replica, step, DOMAIN_SWEEP, key);
+        uint64_t c0, c1, c2;
+        const uint64_t nm = plan.notmask;
+        add4(S ^ U ^ nm, S ^ D ^ nm, S ^ C ^ nm, S ^ Sd ^ nm, c0, c1, c2);
+        uint64_t hm[2] = {c1 & c0 & plan.en3, c2 & plan.en4};
+        const uint64_t acc = decide_hard<2>(hm, plan.ht, ~(hm[0] | hm[1]), valid, word_idx, replica, step,
+                                            DOMAIN_SWEEP, key);
         // flipping a spin with a aligned neighbours changes the bond sum by 8 - 4a, M by -2s
-        int na = __popcll(acc);
-        dB = 8 * na - 4 * (__popcll(acc & a0) + 2 * __popcll(acc & a1) + 4 * __popcll(acc & a2));
+        const int na = __popcll(acc);
+        dB = plan.sign * (8 * na - 4 * (__popcll(acc & c0) + 2 * __popcll(acc & c1) + 4 * __popcll(acc & c2)));
         dS = -2 * (2 * __popcll(acc & S) - na);
         return S ^ acc;
     } else {
-        uint64_t n0, n1, n2, cnt[5], m[10];
+        uint64_t n0, n1, n2, cnt[5], hm[5], needed = 0;
         add4(U, D, C, Sd, n0, n1, n2);  // occupied neighbours
         count_masks(n0, n1, n2, cnt);
 #pragma unroll
         for (int n = 0; n < 5; ++n) {
-            m[n] = cnt[n] & ~S;
-            m[5 + n] = cnt[n] & S;
+            hm[n] = cnt[n] & (S ^ plan.sel[n]) & plan.en[n];
+            needed |= hm[n];
         }
-        // dE(c=0, nn) = -dE(c=1, nn): at most one class of each pair is hard, five in all
-        uint64_t acc = decide<10, 5>(m, thr, valid, word_idx, replica, step, DOMAIN_SWEEP, key);
+        const uint64_t acc = decide_hard<5>(hm, plan.ht, ~needed, valid, word_idx, replica, step, DOMAIN_SWEEP, key);
         // toggling c -> 1-c with nn occupied neighbours changes the bond count by (1-2c) nn, N by (1-2c)
-        uint64_t add = acc & ~S, rem = acc & S;
+        const uint64_t add = acc & ~S, rem = acc & S;
         dB = (__popcll(add & n0) + 2 * __popcll(add & n1) + 4 * __popcll(add & n2)) -
              (__popcll(rem & n0) + 2 * __popcll(rem & n1) + 4 * __popcll(rem & n2));
         dS = __popcll(add) - __popcll(rem);

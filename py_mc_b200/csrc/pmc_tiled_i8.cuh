@@ -75,13 +75,8 @@ __global__ void __launch_bounds__(TILE_THREADS) sweep_tiled_i8_kernel(LatT L, in
     const int chunks_per_row = TW * 4;     // 16-byte chunks per tile row
     const int cpr_log2 = tw_log2 + 2;
 
-    uint32_t thr[NCLASS];
-    {
-        const int tt = L.rep_to_T[L.rep_offset + rep];
-        const uint32_t *row = L.thr + (size_t)tt * NCLASS;
-#pragma unroll
-        for (int c = 0; c < NCLASS; ++c) thr[c] = __ldg(row + c);
-    }
+    Plan<MODEL> plan;
+    plan.init(L.thr + (size_t)L.rep_to_T[L.rep_offset + rep] * NCLASS);
 
     const int8_t *tgt = L.i8 + (size_t)(rep * 2 + colour) * L.lenX * L.nk;
     const int8_t *oth = L.i8 + (size_t)(rep * 2 + oc) * L.lenX * L.nk;
@@ -152,7 +147,7 @@ __global__ void __launch_bounds__(TILE_THREADS) sweep_tiled_i8_kernel(LatT L, in
     }
     int dB = 0, dS = 0;
     const uint32_t word_idx = (uint32_t)(i * L.nw + w0 + w);
-    const uint64_t Snew = update_word<MODEL>(S, U, D, C, Sd, active ? ~0ull : 0ull, thr, word_idx,
+    const uint64_t Snew = update_word<MODEL>(S, U, D, C, Sd, active ? ~0ull : 0ull, plan, word_idx,
                                              (uint32_t)(L.rep_offset + rep), step, L.key, dB, dS);
     s_words[t] = Snew;  // each thread overwrites only the word it read itself
     __syncthreads();

@@ -142,11 +142,9 @@ __device__ __forceinline__ void block_accumulate(int a, int b, unsigned long lon
 }
 
 template <int MODEL>
-__device__ __forceinline__ void load_thr(const Lat &L, int rep, uint32_t (&thr)[ModelTraits<MODEL>::NCLASS]) {
+__device__ __forceinline__ void load_plan(const Lat &L, int rep, Plan<MODEL> &plan) {
     const int t = L.rep_to_T[L.rep_offset + rep];
-    const uint32_t *row = L.thr + (size_t)t * ModelTraits<MODEL>::NCLASS;
-#pragma unroll
-    for (int c = 0; c < ModelTraits<MODEL>::NCLASS; ++c) thr[c] = __ldg(row + c);
+    plan.init(L.thr + (size_t)t * ModelTraits<MODEL>::NCLASS);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -155,12 +153,11 @@ __device__ __forceinline__ void load_thr(const Lat &L, int rep, uint32_t (&thr)[
 // ------------------------------------------------------------------------------------------
 template <int LAYOUT, int MODEL>
 __global__ void __launch_bounds__(128) sweep_word_kernel(Lat L, int colour, uint64_t step) {
-    constexpr int NCLASS = ModelTraits<MODEL>::NCLASS;
     const int rep = blockIdx.y;
     const int word = blockIdx.x * blockDim.x + threadIdx.x;
     const bool active = word < L.lenX * L.nw;
-    uint32_t thr[NCLASS];
-    load_thr<MODEL>(L, rep, thr);
+    Plan<MODEL> plan;
+    load_plan<MODEL>(L, rep, plan);
 
     int i = 0, w = 0, nvalid = 0;
     uint64_t S = 0, U = 0, D = 0, C = 0, Lf = 0, Rt = 0, valid = 0;
@@ -175,7 +172,7 @@ __global__ void __launch_bounds__(128) sweep_word_kernel(Lat L, int colour, uint
         load_neighbours<LAYOUT>(L, rep, colour, i, w, nvalid, !q, q, U, D, C, Lf, Rt);
     }
     int dB = 0, dS = 0;
-    uint64_t Snew = update_word<MODEL>(S, U, D, C, q ? Rt : Lf, valid, thr, (uint32_t)word,
+    uint64_t Snew = update_word<MODEL>(S, U, D, C, q ? Rt : Lf, valid, plan, (uint32_t)word,
                                        (uint32_t)(L.rep_offset + rep), step, L.key, dB, dS);
     if (active) {
         uint64_t flip = (S ^ Snew) & valid;
@@ -193,6 +190,59 @@ __global__ void __launch_bounds__(128) sweep_word_kernel(Lat L, int colour, uint
         dB = dS = 0;
     }
     block_accumulate(dB, dS, L.tracked + 2 * (size_t)rep);
+}
+
+// ------------------------------------------------------------------------------------------
+// K2: bit-packed layout, one thread walks RPT consecutive rows of one word column so that the
+// neighbour rows are loaded once and the per-thread set-up (plan, index arithmetic) is shared.
+// All loads of a thread are issued before the first update.  grid = (ceil(lenX/RPT*nw / block), nrep)
+// ------------------------------------------------------------------------------------------
+template <int MODEL, int RPT>
+__global__ void __launch_bounds__(128) sweep_bits_rows_kernel(Lat L, int colour, uint64_t step) {
+    const int rep = blockIdx.y;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int ngroups = L.lenX / RPT;
+    const bool active = idx < ngroups * L.nw;
+    Plan<MODEL> plan;
+    load_plan<MODEL>(L, rep, plan);
+    const int g = active ? idx / L.nw : 0;
+    const int w = active ? idx - g * L.nw : 0;
+    const int i0 = g * RPT;
+    const int wl = w == 0 ? L.nw - 1 : w - 1, wr = w == L.nw - 1 ? 0 : w + 1;
+    uint64_t *tgt = L.bits + (size_t)(rep * 2 + colour) * L.lenX * L.nw;
+    const uint64_t *oth = L.bits + (size_t)(rep * 2 + (colour ^ 1)) * L.lenX * L.nw;
+
+    uint64_t S[RPT], O[RPT + 2], A[RPT];
+    {
+        const int im = i0 == 0 ? L.lenX - 1 : i0 - 1;
+        O[0] = oth[(size_t)im * L.nw + w];
+#pragma unroll
+        for (int r = 0; r < RPT; ++r) {
+            const int i = i0 + r;
+            const bool q = (i + colour) & 1;
+            O[r + 1] = oth[(size_t)i * L.nw + w];
+            A[r] = oth[(size_t)i * L.nw + (q ? wr : wl)];
+            S[r] = tgt[(size_t)i * L.nw + w];
+        }
+        const int ip = i0 + RPT == L.lenX ? 0 : i0 + RPT;
+        O[RPT + 1] = oth[(size_t)ip * L.nw + w];
+    }
+    int dB = 0, dS = 0;
+#pragma unroll
+    for (int r = 0; r < RPT; ++r) {
+        const int i = i0 + r;
+        const bool q = (i + colour) & 1;
+        const uint64_t C = O[r + 1];
+        const uint64_t Sd = q ? ((C >> 1) | (A[r] << 63)) : ((C << 1) | (A[r] >> 63));
+        int b, s2;
+        const uint64_t Snew = update_word<MODEL>(S[r], O[r], O[r + 2], C, Sd, active ? ~0ull : 0ull, plan,
+                                                 (uint32_t)(i * L.nw + w), (uint32_t)(L.rep_offset + rep), step, L.key,
+                                                 b, s2);
+        if (active && Snew != S[r]) tgt[(size_t)i * L.nw + w] = Snew;
+        dB += b;
+        dS += s2;
+    }
+    block_accumulate(active ? dB : 0, active ? dS : 0, L.tracked + 2 * (size_t)rep);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -578,15 +628,21 @@ int pymc_set_accept_tables(pymc_handle *h, const uint32_t *thr, int ntemps, int 
     REQUIRE(thr, PYMC_ERR_BADARG, "pymc_set_accept_tables: null pointer");
     REQUIRE(ntemps == h->p.ntemps && nclass == h->nclass, PYMC_ERR_BADARG,
             "pymc_set_accept_tables: got %d x %d, handle expects %d x %d", ntemps, nclass, h->p.ntemps, h->nclass);
-    // dE > 0 ("hard", thr < 2^32-1) for at most 2 of the 5 Ising classes and 5 of the 10 lattice-gas
-    // classes in any table derived from an energy function; the kernels compact exactly that many.
-    const int maxhard = h->p.model == PYMC_MODEL_ISING ? 2 : 5;
+    // dE > 0 ("hard", thr < 2^32-1) comes from dE = -2J(2a-4) (Ising) or dE = -(2c-1)(J nn + Eads - mu),
+    // so a consistent table has them only at one end of the Ising class range (a in {3,4} or {0,1})
+    // and in at most one occupancy per neighbour count of the lattice gas.  The kernels rely on it.
     for (int t = 0; t < ntemps; ++t) {
-        int nhard = 0;
-        for (int c = 0; c < nclass; ++c) nhard += thr[(size_t)t * nclass + c] != 0xFFFFFFFFu;
-        REQUIRE(nhard <= maxhard, PYMC_ERR_UNSUPPORTED,
-                "pymc_set_accept_tables: row %d has %d classes with dE > 0, at most %d are possible for this model", t,
-                nhard, maxhard);
+        const uint32_t *row = thr + (size_t)t * nclass;
+        auto hard = [&](int c) { return row[c] != 0xFFFFFFFFu; };
+        if (h->p.model == PYMC_MODEL_ISING) {
+            const bool lo = hard(0) || hard(1), hi = hard(3) || hard(4);
+            REQUIRE(!hard(2) && !(lo && hi), PYMC_ERR_UNSUPPORTED,
+                    "pymc_set_accept_tables: row %d is not an Ising table (dE > 0 at both ends or at dE = 0)", t);
+        } else {
+            for (int n = 0; n < 5; ++n)
+                REQUIRE(!(hard(n) && hard(5 + n)), PYMC_ERR_UNSUPPORTED,
+                        "pymc_set_accept_tables: row %d has dE > 0 for both occupancies at %d neighbours", t, n);
+        }
     }
     CUDA_TRY(cudaMemcpyAsync(h->thr, thr, (size_t)ntemps * nclass * 4, cudaMemcpyHostToDevice, h->stream));
     CUDA_TRY(cudaStreamSynchronize(h->stream));
@@ -627,6 +683,8 @@ int pymc_sweep(pymc_handle *h, int64_t nsweeps) {
     dim3 grid((h->p.lenX * h->nw + 127) / 128, h->p.nreplicas);
     // K1 tiled int8 kernel: needs whole words (lenY % 128 == 0); tile = TH rows x TW words, TW | nw
     const bool tiled = h->p.layout == PYMC_LAYOUT_INT8 && h->p.kernel != PYMC_KERNEL_GENERIC && h->nk % 64 == 0;
+    const bool bitrows = h->p.layout == PYMC_LAYOUT_BITS && h->p.kernel != PYMC_KERNEL_GENERIC;
+    const int rpt = h->p.lenX % 4 == 0 ? 4 : 2;
     int tw_log2 = 0;
     while (tw_log2 < 4 && h->nw % (2 << tw_log2) == 0) ++tw_log2;
     const int TH = TILE_THREADS >> tw_log2;
@@ -634,6 +692,17 @@ int pymc_sweep(pymc_handle *h, int64_t nsweeps) {
     for (int64_t s = 0; s < nsweeps; ++s) {
         for (int colour = 0; colour < 2; ++colour) {
             const uint64_t step = 2 * h->sweep_counter + colour;
+            if (bitrows) {
+                dim3 bgrid(((h->p.lenX / rpt) * h->nw + 127) / 128, h->p.nreplicas);
+                if (h->p.model == PYMC_MODEL_ISING) {
+                    if (rpt == 4) sweep_bits_rows_kernel<MODEL_ISING, 4><<<bgrid, 128, 0, h->stream>>>(L, colour, step);
+                    else sweep_bits_rows_kernel<MODEL_ISING, 2><<<bgrid, 128, 0, h->stream>>>(L, colour, step);
+                } else {
+                    if (rpt == 4) sweep_bits_rows_kernel<MODEL_LATGAS, 4><<<bgrid, 128, 0, h->stream>>>(L, colour, step);
+                    else sweep_bits_rows_kernel<MODEL_LATGAS, 2><<<bgrid, 128, 0, h->stream>>>(L, colour, step);
+                }
+                continue;
+            }
             if (tiled) {
                 if (h->p.model == PYMC_MODEL_ISING)
                     sweep_tiled_i8_kernel<MODEL_ISING, Lat><<<tgrid, TILE_THREADS, 0, h->stream>>>(L, colour, step, tw_log2);

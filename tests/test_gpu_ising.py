@@ -109,7 +109,8 @@ def test_trajectories_match_reference(golden_ising):
             lat.close()
 
 
-@pytest.mark.parametrize("shape,kT", [((64, 256), 2.269185314213022), ((128, 1024), 2.0), ((30, 44), 3.0)])
+@pytest.mark.parametrize("shape,kT", [((64, 256), 2.269185314213022), ((128, 1024), 2.0), ((30, 44), 3.0),
+                                      ((6, 256), 2.5), ((258, 128), 1.5), ((40, 4096), 2.3)])
 def test_sweeps_match_oracle_medium(shape, kT):
     c = _cabi()
     seed, nsweeps, J = 2026, 4, -1.0
