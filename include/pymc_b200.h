@@ -130,6 +130,32 @@ int pymc_get_tracked(pymc_handle *h, int64_t *bond, int64_t *second);
 int pymc_propose(pymc_handle *h, int replica, const int32_t *x, const int32_t *y, int n,
                  int32_t *site_out, int32_t *nnsum_out);
 
+/* ---- replica exchange -----------------------------------------------------------------
+ * Replaces TemperatureRX_MPI (py_mc/mc_mpi.py:75-209).  Needs ntemps == nreplicas_global
+ * (the reference's own requirement, mc_mpi.py:47-52).
+ * pymc_rx_setup      betas = 1/kTs (mc_mpi.py:78); energy = c_bond*bond + c_second*second
+ *                    (J*B for Ising; J*B + (Eads-mu)*N for the lattice gas).
+ * pymc_rx_energies   writes the energies of the local replicas into the shared energies[R] array
+ *                    at [replica_offset, +nreplicas)  (mycalc.energy, mc_mpi.py:117,135).
+ * pymc_rx_buffers    device pointers of energies[R] (float64) and replica_to_T[R] (int32): with
+ *                    several GPUs the caller all-gathers energies in place (NCCL) between
+ *                    pymc_rx_energies and pymc_rx_exchange; this replaces the Send/Recv of one
+ *                    double per pair and the Allgather of the rank->T map (mc_mpi.py:106-138).
+ * pymc_rx_exchange   Xtrial(XCscheme) (mc_mpi.py:102-140) for every pair at once, on the device;
+ *                    identical on every GPU because it reads only all-gathered data.
+ * pymc_rx_cycle      single-GPU loop [sweeps, energies, exchange] x ncycles with alternating
+ *                    scheme (mc_mpi.py:165-169), no host synchronisation inside. */
+int pymc_rx_setup(pymc_handle *h, const double *betas, int ntemps, double c_bond, double c_second);
+int pymc_rx_energies(pymc_handle *h);
+int pymc_rx_buffers(pymc_handle *h, void **energies_all, void **replica_to_T);
+int pymc_rx_exchange(pymc_handle *h, int xcscheme);
+int pymc_rx_cycle(pymc_handle *h, int64_t ncycles, int64_t sweeps_per_exchange, int first_scheme);
+int pymc_rx_get_energies(pymc_handle *h, double *energies, int n);
+/* attempts / acceptances per temperature pair, indexed by the lower temperature index */
+int pymc_rx_get_stats(pymc_handle *h, uint64_t *tried, uint64_t *accepted, int n);
+int pymc_rx_get_round(pymc_handle *h, uint64_t *round);
+int pymc_rx_set_round(pymc_handle *h, uint64_t round);
+
 /* ---- timing helper (CUDA events on the handle's stream) ------------------------------ */
 int pymc_timer_start(pymc_handle *h);
 int pymc_timer_stop(pymc_handle *h, float *elapsed_ms); /* synchronises */

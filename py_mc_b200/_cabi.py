@@ -23,6 +23,8 @@ SYMBOLS = [
     "pymc_init_random", "pymc_set_accept_tables", "pymc_set_replica_to_T", "pymc_get_replica_to_T",
     "pymc_sweep", "pymc_get_sweep_counter", "pymc_set_sweep_counter", "pymc_reduce_observables",
     "pymc_get_tracked", "pymc_propose", "pymc_timer_start", "pymc_timer_stop",
+    "pymc_rx_setup", "pymc_rx_energies", "pymc_rx_buffers", "pymc_rx_exchange", "pymc_rx_cycle",
+    "pymc_rx_get_energies", "pymc_rx_get_stats", "pymc_rx_get_round", "pymc_rx_set_round",
 ]
 
 
@@ -68,6 +70,15 @@ def _load():
         "pymc_reduce_observables": [P, P, P],
         "pymc_get_tracked": [P, P, P],
         "pymc_propose": [P, I, P, P, I, P, P],
+        "pymc_rx_setup": [P, P, I, C.c_double, C.c_double],
+        "pymc_rx_energies": [P],
+        "pymc_rx_buffers": [P, C.POINTER(P), C.POINTER(P)],
+        "pymc_rx_exchange": [P, I],
+        "pymc_rx_cycle": [P, I64, I64, I],
+        "pymc_rx_get_energies": [P, P, I],
+        "pymc_rx_get_stats": [P, P, P, I],
+        "pymc_rx_get_round": [P, C.POINTER(C.c_uint64)],
+        "pymc_rx_set_round": [P, C.c_uint64],
         "pymc_timer_start": [P],
         "pymc_timer_stop": [P, C.POINTER(C.c_float)],
     }
@@ -202,6 +213,47 @@ class Lattices:
         nn = np.empty(xs.size, dtype=np.int32)
         check(lib.pymc_propose(self._h, replica, _ptr(xs), _ptr(ys), xs.size, _ptr(site), _ptr(nn)))
         return site, nn
+
+    # -- replica exchange
+    def rx_setup(self, betas, c_bond, c_second=0.0):
+        b = np.ascontiguousarray(betas, dtype=np.float64)
+        check(lib.pymc_rx_setup(self._h, _ptr(b), b.size, float(c_bond), float(c_second)))
+
+    def rx_energies(self):
+        check(lib.pymc_rx_energies(self._h))
+
+    def rx_buffers(self):
+        """Device pointers (ints) of energies[R] (float64) and replica_to_T[R] (int32)."""
+        e, m = C.c_void_p(), C.c_void_p()
+        check(lib.pymc_rx_buffers(self._h, C.byref(e), C.byref(m)))
+        return e.value, m.value
+
+    def rx_exchange(self, xcscheme):
+        check(lib.pymc_rx_exchange(self._h, int(xcscheme)))
+
+    def rx_cycle(self, ncycles, sweeps_per_exchange, first_scheme=0):
+        check(lib.pymc_rx_cycle(self._h, int(ncycles), int(sweeps_per_exchange), int(first_scheme)))
+
+    def rx_get_energies(self):
+        e = np.empty(self.nreplicas_global, dtype=np.float64)
+        check(lib.pymc_rx_get_energies(self._h, _ptr(e), e.size))
+        return e
+
+    def rx_stats(self):
+        t = np.empty(self.ntemps, dtype=np.uint64)
+        a = np.empty(self.ntemps, dtype=np.uint64)
+        check(lib.pymc_rx_get_stats(self._h, _ptr(t), _ptr(a), t.size))
+        return t, a
+
+    @property
+    def rx_round(self):
+        c = C.c_uint64(0)
+        check(lib.pymc_rx_get_round(self._h, C.byref(c)))
+        return c.value
+
+    @rx_round.setter
+    def rx_round(self, v):
+        check(lib.pymc_rx_set_round(self._h, int(v)))
 
     # -- timing
     def timer_start(self):

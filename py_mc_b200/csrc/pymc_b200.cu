@@ -15,6 +15,7 @@
 #include "../../include/pymc_b200.h"
 #include "pmc_core.cuh"
 #include "pmc_tiled_i8.cuh"
+#include "pmc_rx.cuh"
 
 using namespace pmc;
 
@@ -380,6 +381,14 @@ struct pymc_handle {
     int8_t *staging;               // natural int8 image of one replica (upload/download)
     int32_t *qbuf;                 // propose scratch: x, y, site, nn
     int qcap;
+    // replica exchange (allocated by pymc_rx_setup)
+    double *betas;                 // [ntemps]
+    double *energies;              // [nrep_global]  all-gathered energies, indexed by global replica
+    int32_t *T_to_rep;             // [ntemps]
+    unsigned long long *rx_tried, *rx_accepted;  // [ntemps] per lower temperature index of a pair
+    double c_bond, c_second;
+    bool rx_ready;
+    uint64_t rx_round;
     bool tables_set;
     bool dirty;                    // configurations changed since the tracked observables were based
     uint64_t sweep_counter;
@@ -458,6 +467,11 @@ int pymc_destroy(pymc_handle *h) {
         cudaFree(h->reduced);
         cudaFree(h->staging);
         cudaFree(h->qbuf);
+        cudaFree(h->betas);
+        cudaFree(h->energies);
+        cudaFree(h->T_to_rep);
+        cudaFree(h->rx_tried);
+        cudaFree(h->rx_accepted);
         if (h->ev0) cudaEventDestroy(h->ev0);
         if (h->ev1) cudaEventDestroy(h->ev1);
         if (h->own_stream) cudaStreamDestroy(h->own_stream);
@@ -657,7 +671,21 @@ int pymc_set_replica_to_T(pymc_handle *h, const int32_t *map, int n) {
     for (int r = 0; r < n; ++r)
         REQUIRE(map[r] >= 0 && map[r] < h->p.ntemps, PYMC_ERR_BADARG, "pymc_set_replica_to_T: map[%d] = %d not in 0..%d",
                 r, map[r], h->p.ntemps - 1);
+    if (h->rx_ready) {
+        bool *seen = new bool[h->p.ntemps]();
+        bool perm = n == h->p.ntemps;
+        for (int r = 0; r < n && perm; ++r) {
+            perm = !seen[map[r]];
+            seen[map[r]] = true;
+        }
+        delete[] seen;
+        REQUIRE(perm, PYMC_ERR_BADARG, "pymc_set_replica_to_T: replica exchange needs a permutation of 0..%d", n - 1);
+    }
     CUDA_TRY(cudaMemcpyAsync(h->rep_to_T, map, (size_t)n * 4, cudaMemcpyHostToDevice, h->stream));
+    if (h->rx_ready) {
+        rx_invert_map_kernel<<<(n + 255) / 256, 256, 0, h->stream>>>(h->rep_to_T, h->T_to_rep, n);
+        CUDA_TRY(cudaGetLastError());
+    }
     CUDA_TRY(cudaStreamSynchronize(h->stream));
     return PYMC_OK;
 }
@@ -811,6 +839,128 @@ int pymc_propose(pymc_handle *h, int replica, const int32_t *x, const int32_t *y
     CUDA_TRY(cudaMemcpyAsync(site_out, ds, (size_t)n * 4, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(cudaMemcpyAsync(nnsum_out, dn, (size_t)n * 4, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return PYMC_OK;
+}
+
+
+// ------------------------------------------------------------------------------------------
+// replica exchange
+// ------------------------------------------------------------------------------------------
+int pymc_rx_setup(pymc_handle *h, const double *betas, int ntemps, double c_bond, double c_second) {
+    ENTER(h);
+    REQUIRE(betas, PYMC_ERR_BADARG, "pymc_rx_setup: null pointer");
+    REQUIRE(ntemps == h->p.ntemps && ntemps == h->p.nreplicas_global, PYMC_ERR_BADARG,
+            "pymc_rx_setup: replica exchange needs ntemps == nreplicas_global (got %d temperatures, handle has %d "
+            "temperatures and %d replicas)", ntemps, h->p.ntemps, h->p.nreplicas_global);
+    if (!h->betas) {
+        CUDA_TRY(cudaMalloc(&h->betas, (size_t)ntemps * 8));
+        CUDA_TRY(cudaMalloc(&h->energies, (size_t)ntemps * 8));
+        CUDA_TRY(cudaMalloc(&h->T_to_rep, (size_t)ntemps * 4));
+        CUDA_TRY(cudaMalloc(&h->rx_tried, (size_t)ntemps * 8));
+        CUDA_TRY(cudaMalloc(&h->rx_accepted, (size_t)ntemps * 8));
+    }
+    CUDA_TRY(cudaMemcpyAsync(h->betas, betas, (size_t)ntemps * 8, cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(cudaMemsetAsync(h->energies, 0, (size_t)ntemps * 8, h->stream));
+    CUDA_TRY(cudaMemsetAsync(h->rx_tried, 0, (size_t)ntemps * 8, h->stream));
+    CUDA_TRY(cudaMemsetAsync(h->rx_accepted, 0, (size_t)ntemps * 8, h->stream));
+    rx_invert_map_kernel<<<(ntemps + 255) / 256, 256, 0, h->stream>>>(h->rep_to_T, h->T_to_rep, ntemps);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    h->c_bond = c_bond;
+    h->c_second = c_second;
+    h->rx_ready = true;
+    return PYMC_OK;
+}
+
+int pymc_rx_energies(pymc_handle *h) {
+    ENTER(h);
+    REQUIRE(h->rx_ready, PYMC_ERR_STATE, "pymc_rx_energies: call pymc_rx_setup first");
+    if (h->dirty) {
+        int rc = rebase_tracked(h);
+        if (rc) return rc;
+    }
+    rx_energy_kernel<<<(h->p.nreplicas + 127) / 128, 128, 0, h->stream>>>(h->tracked, h->p.nreplicas, h->p.replica_offset,
+                                                                        h->c_bond, h->c_second, h->energies);
+    CUDA_TRY(cudaGetLastError());
+    return PYMC_OK;
+}
+
+int pymc_rx_buffers(pymc_handle *h, void **energies_all, void **replica_to_T) {
+    REQUIRE(h, PYMC_ERR_BADARG, "pymc_rx_buffers: null handle");
+    REQUIRE(h->rx_ready, PYMC_ERR_STATE, "pymc_rx_buffers: call pymc_rx_setup first");
+    if (energies_all) *energies_all = h->energies;
+    if (replica_to_T) *replica_to_T = h->rep_to_T;
+    return PYMC_OK;
+}
+
+static int rx_exchange_async(pymc_handle *h, int xcscheme) {
+    const int npairs = (h->p.ntemps + 1) / 2;
+    rx_decide_kernel<<<(npairs + 127) / 128, 128, 0, h->stream>>>(h->energies, h->betas, h->rep_to_T, h->T_to_rep,
+                                                                 h->p.ntemps, xcscheme, h->rx_round,
+                                                                 make_key(h->p.seed), h->rx_tried, h->rx_accepted);
+    h->rx_round++;
+    return PYMC_OK;
+}
+
+int pymc_rx_exchange(pymc_handle *h, int xcscheme) {
+    ENTER(h);
+    REQUIRE(h->rx_ready, PYMC_ERR_STATE, "pymc_rx_exchange: call pymc_rx_setup first");
+    REQUIRE(xcscheme == 0 || xcscheme == 1, PYMC_ERR_BADARG, "pymc_rx_exchange: scheme %d", xcscheme);
+    rx_exchange_async(h, xcscheme);
+    CUDA_TRY(cudaGetLastError());
+    return PYMC_OK;
+}
+
+int pymc_rx_cycle(pymc_handle *h, int64_t ncycles, int64_t sweeps_per_exchange, int first_scheme) {
+    ENTER(h);
+    REQUIRE(h->rx_ready, PYMC_ERR_STATE, "pymc_rx_cycle: call pymc_rx_setup first");
+    REQUIRE(h->p.nreplicas == h->p.nreplicas_global, PYMC_ERR_STATE,
+            "pymc_rx_cycle: this handle holds %d of %d replicas; with several GPUs the caller all-gathers the "
+            "energies between pymc_rx_energies and pymc_rx_exchange", h->p.nreplicas, h->p.nreplicas_global);
+    REQUIRE(ncycles >= 0 && sweeps_per_exchange >= 1 && (first_scheme == 0 || first_scheme == 1), PYMC_ERR_BADARG,
+            "pymc_rx_cycle: bad arguments");
+    int scheme = first_scheme;
+    for (int64_t c = 0; c < ncycles; ++c) {
+        int rc = pymc_sweep(h, sweeps_per_exchange);
+        if (rc) return rc;
+        rc = pymc_rx_energies(h);
+        if (rc) return rc;
+        rx_exchange_async(h, scheme);
+        scheme ^= 1;
+    }
+    CUDA_TRY(cudaGetLastError());
+    return PYMC_OK;
+}
+
+int pymc_rx_get_energies(pymc_handle *h, double *energies, int n) {
+    ENTER(h);
+    REQUIRE(h->rx_ready, PYMC_ERR_STATE, "pymc_rx_get_energies: call pymc_rx_setup first");
+    REQUIRE(energies && n == h->p.nreplicas_global, PYMC_ERR_BADARG, "pymc_rx_get_energies: need %d entries",
+            h->p.nreplicas_global);
+    CUDA_TRY(cudaMemcpyAsync(energies, h->energies, (size_t)n * 8, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return PYMC_OK;
+}
+
+int pymc_rx_get_stats(pymc_handle *h, uint64_t *tried, uint64_t *accepted, int n) {
+    ENTER(h);
+    REQUIRE(h->rx_ready, PYMC_ERR_STATE, "pymc_rx_get_stats: call pymc_rx_setup first");
+    REQUIRE(tried && accepted && n == h->p.ntemps, PYMC_ERR_BADARG, "pymc_rx_get_stats: need %d entries", h->p.ntemps);
+    CUDA_TRY(cudaMemcpyAsync(tried, h->rx_tried, (size_t)n * 8, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaMemcpyAsync(accepted, h->rx_accepted, (size_t)n * 8, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return PYMC_OK;
+}
+
+int pymc_rx_get_round(pymc_handle *h, uint64_t *round) {
+    REQUIRE(h && round, PYMC_ERR_BADARG, "pymc_rx_get_round: null pointer");
+    *round = h->rx_round;
+    return PYMC_OK;
+}
+
+int pymc_rx_set_round(pymc_handle *h, uint64_t round) {
+    REQUIRE(h, PYMC_ERR_BADARG, "pymc_rx_set_round: null handle");
+    h->rx_round = round;
     return PYMC_OK;
 }
 

@@ -30,3 +30,8 @@ def golden_ising():
 @pytest.fixture(scope="session")
 def golden_ising_de():
     return load_golden("ising_de")
+
+
+@pytest.fixture(scope="session")
+def golden_rx():
+    return load_golden("rx")

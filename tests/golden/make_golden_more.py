@@ -1,0 +1,142 @@
+"""More golden-fixture generators (replica exchange, lattice gas, hard discs); see make_golden.py."""
+import json
+import os
+import sys
+import tempfile
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, HERE)
+
+from oracle import philox, ising as o_ising  # noqa: E402
+
+RX_CASES = [
+    dict(name="rx4_8x8", R=4, lenX=8, lenY=8, J=-1.0, kT_lo=1.5, kT_hi=3.5, seed=777, nsweeps=40, rx_every=2),
+    dict(name="rx6_6x10", R=6, lenX=6, lenY=10, J=-1.0, kT_lo=2.0, kT_hi=2.6, seed=4242, nsweeps=30, rx_every=1),
+]
+
+
+class RXInjector:
+    """Per-rank injector: checkerboard site order + per-site uniforms for MCstep, and the
+    (round, pair) uniform for Xtrial (read from the caller's frame: myTrank in Xtrial, i in run)."""
+
+    def __init__(self, case, rank):
+        self.case, self.rank = case, rank
+        self.N = case["lenX"] * case["lenY"]
+        self.n = -1
+        self.phase = 0
+        self.sweep_loaded = -1
+        self.base_sweep = 0
+        self.base_round = 0
+        self.exchange_draws = 0
+
+    def _load(self, sweep):
+        c = self.case
+        self.sites, self.us = [], []
+        for colour in (0, 1):
+            u = philox.x32_to_uniform(o_ising.site_x32(c["seed"], self.rank, sweep, colour, c["lenX"], c["lenY"]))
+            for i in range(c["lenX"]):
+                q = (i + colour) & 1
+                for k in range(c["lenY"] // 2):
+                    self.sites.append((i, 2 * k + q))
+                    self.us.append(u[i, k])
+        self.sweep_loaded = sweep
+
+    def randrange(self, n):
+        if self.phase == 0:
+            self.n += 1
+            sweep = self.base_sweep + self.n // self.N
+            if sweep != self.sweep_loaded:
+                self._load(sweep)
+            self.phase = 1
+            return int(self.sites[self.n % self.N][0])
+        self.phase = 0
+        return int(self.sites[self.n % self.N][1])
+
+    def random_metropolis(self):
+        return float(self.us[self.n % self.N])
+
+    def random_exchange(self):
+        f = sys._getframe(1)
+        assert f.f_code.co_name == "Xtrial"
+        t = int(f.f_locals["myTrank"])
+        run = f.f_back
+        assert run.f_code.co_name == "run"
+        rnd = self.base_round + run.f_locals["i"] // run.f_locals["RXtrial_frequency"] - 1
+        self.exchange_draws += 1
+        return float(philox.x32_to_uniform(philox.rx_x32(self.case["seed"], rnd, t)))
+
+
+def _rx_rank_main(comm, case, workdir, ref_root):
+    import fake_mpi
+    np.int = int      # removed from numpy >= 1.24; py_mc/mc_mpi.py:79-81 still uses them
+    np.float = float
+    fake_mpi.install(comm)
+    sys.path.insert(0, ref_root)
+    sys.path.insert(0, os.path.join(ref_root, "examples"))
+    import py_mc.mc as refmc
+    import py_mc.mc_mpi as refmpi
+    import ising2D as ref_ising
+
+    rank = comm.Get_rank()
+    inj = RXInjector(case, rank)
+    ref_ising.rand = inj
+    refmc.random = inj.random_metropolis
+    refmpi.random = inj.random_exchange
+    os.chdir(workdir)
+    R, N = case["R"], case["lenX"] * case["lenY"]
+    kTs = np.linspace(case["kT_lo"], case["kT_hi"], R)
+    configs = []
+    for r in range(R):
+        cfg = ref_ising.ising2D_config(case["lenX"], case["lenY"])
+        cfg.config[:, :] = o_ising.init_config(case["seed"], r, case["lenX"], case["lenY"])
+        configs.append(cfg)
+    model = ref_ising.ising2D(case["J"])
+    rx = refmpi.TemperatureRX_MPI(comm, refmc.CanonicalMonteCarlo, model, configs, kTs)
+    obs = ref_ising.observer()
+    out = rx.run(case["nsweeps"] * N, case["rx_every"] * N, N, 10 ** 12, obs, True, True)
+    res = dict(
+        rank_to_T=np.array(rx.rank_to_T, dtype=np.int64),
+        config=rx.mycalc.config.config.astype(np.int8),
+        obs_save=np.load(os.path.join(workdir, str(rank), "obs_save.npy")),
+        Trank_hist=np.load(os.path.join(workdir, str(rank), "Trank_hist.npy")),
+        kT_hist=np.load(os.path.join(workdir, str(rank), "kT_hist.npy")),
+        energy=float(rx.mycalc.energy),
+        exchange_draws=inj.exchange_draws,
+        obs_list=np.array(out, dtype=np.float64) if rank == 0 else None,
+        files=sorted(os.listdir(os.path.join(workdir, str(rank)))),
+        top_files=sorted(f for f in os.listdir(workdir) if not f.isdigit()) if rank == 0 else None,
+    )
+    return res
+
+
+def gen_rx(out):
+    import fake_mpi
+    ref_root = os.environ.get("PYMC_REFERENCE", "/root/reference")
+    meta = []
+    for case in RX_CASES:
+        workdir = tempfile.mkdtemp()
+        res = fake_mpi.run_ranks(case["R"], _rx_rank_main, (case, workdir, ref_root))
+        n = case["name"]
+        out[n + "_rank_to_T"] = res[0]["rank_to_T"]
+        for r in range(case["R"]):
+            assert np.array_equal(res[r]["rank_to_T"], res[0]["rank_to_T"])
+        out[n + "_configs"] = np.array([r["config"] for r in res])
+        out[n + "_obs_save"] = np.array([r["obs_save"] for r in res])      # [rank, sample, (E, |M|)]
+        out[n + "_Trank_hist"] = np.array([r["Trank_hist"] for r in res])  # [rank, sample]
+        out[n + "_kT_hist"] = np.array([r["kT_hist"] for r in res])
+        out[n + "_energy"] = np.array([r["energy"] for r in res])
+        out[n + "_obs_list"] = res[0]["obs_list"]                          # [T, (E, |M|)] means
+        c = dict(case)
+        c["files"] = res[0]["files"]
+        c["top_files"] = res[0]["top_files"]
+        c["exchange_draws"] = int(sum(r["exchange_draws"] for r in res))
+        meta.append(c)
+        print("rx", n, "final rank_to_T", res[0]["rank_to_T"], "draws", c["exchange_draws"], "files", c["files"],
+              c["top_files"])
+        print("   mean obs per T:", np.round(res[0]["obs_list"], 3).tolist())
+    out["meta"] = np.array(json.dumps(meta))
+
+
+MORE = {"rx": gen_rx}
