@@ -125,6 +125,7 @@ class Lattices:
         p = Params(ABI_VERSION, self.device, self.model, self.layout, self.lenX, self.lenY, self.nreplicas,
                    self.replica_offset, self.nreplicas_global, self.ntemps, self.seed, int(kernel), 0)
         check(lib.pymc_create(C.byref(p), C.byref(self._h)))
+        self._tracked_cache = None  # (bond, second) valid until the configurations change
 
     # -- lifetime
     def close(self):
@@ -153,6 +154,7 @@ class Lattices:
         a = np.ascontiguousarray(config_int8, dtype=np.int8)
         if a.shape != (self.lenX, self.lenY):
             raise ValueError("config shape %s, lattice is %dx%d" % (a.shape, self.lenX, self.lenY))
+        self._tracked_cache = None
         check(lib.pymc_upload_config(self._h, replica, _ptr(a), a.size))
 
     def download(self, replica, out=None):
@@ -163,6 +165,7 @@ class Lattices:
         return out
 
     def init_random(self):
+        self._tracked_cache = None
         check(lib.pymc_init_random(self._h))
 
     # -- tables
@@ -181,6 +184,7 @@ class Lattices:
 
     # -- hot path
     def sweep(self, nsweeps=1):
+        self._tracked_cache = None
         check(lib.pymc_sweep(self._h, int(nsweeps)))
 
     @property
@@ -198,13 +202,16 @@ class Lattices:
         b = np.empty(self.nreplicas, dtype=np.int64)
         s = np.empty(self.nreplicas, dtype=np.int64)
         check(lib.pymc_reduce_observables(self._h, _ptr(b), _ptr(s)))
+        self._tracked_cache = (b, s)
         return b, s
 
     def tracked(self):
-        b = np.empty(self.nreplicas, dtype=np.int64)
-        s = np.empty(self.nreplicas, dtype=np.int64)
-        check(lib.pymc_get_tracked(self._h, _ptr(b), _ptr(s)))
-        return b, s
+        if self._tracked_cache is None:
+            b = np.empty(self.nreplicas, dtype=np.int64)
+            s = np.empty(self.nreplicas, dtype=np.int64)
+            check(lib.pymc_get_tracked(self._h, _ptr(b), _ptr(s)))
+            self._tracked_cache = (b, s)
+        return self._tracked_cache
 
     def propose(self, replica, xs, ys):
         xs = np.ascontiguousarray(xs, dtype=np.int32)
@@ -232,6 +239,7 @@ class Lattices:
         check(lib.pymc_rx_exchange(self._h, int(xcscheme)))
 
     def rx_cycle(self, ncycles, sweeps_per_exchange, first_scheme=0):
+        self._tracked_cache = None
         check(lib.pymc_rx_cycle(self._h, int(ncycles), int(sweeps_per_exchange), int(first_scheme)))
 
     def rx_get_energies(self):

@@ -39,7 +39,9 @@ class LatticeConfig:
         self._host = np.empty([self.lenX, self.lenY], dtype=dtype)
         self._host_valid = True
         self._dev_valid = False
-        self._lat = None        # _cabi.Lattices with one replica
+        self._lat = None        # _cabi.Lattices holding this configuration ...
+        self._rep = 0           # ... as local replica number _rep
+        self._lat_shared = False  # True when the lattice batch belongs to a replica-exchange engine
         self._lat_key = None
 
     # -- host side ---------------------------------------------------------------------
@@ -64,7 +66,7 @@ class LatticeConfig:
 
     def _pull(self):
         if not self._host_valid:
-            img = self._lat.download(0)
+            img = self._lat.download(self._rep)
             self._host[...] = self._from_int8(img)
             self._host_valid = True
 
@@ -83,13 +85,16 @@ class LatticeConfig:
         if self._lat is None or self._lat_key != key:
             if self._lat is not None:
                 self._pull()
-                self._lat.close()
+                if not self._lat_shared:
+                    self._lat.close()
                 self._dev_valid = False
+                self._lat_shared = False
+                self._rep = 0
             self._lat = _cabi.Lattices(model_code, self.lenX, self.lenY, nreplicas=1, ntemps=1, seed=get_seed(),
                                        layout=layout, device=self.device)
             self._lat_key = key
         if not self._dev_valid:
-            self._lat.upload(0, self._to_int8(self._host))
+            self._lat.upload(self._rep, self._to_int8(self._host))
             self._dev_valid = True
         return self._lat
 
@@ -101,14 +106,27 @@ class LatticeConfig:
         """(bond, second) exact integers from the device if it holds the newest copy, else None."""
         if self._lat is not None and self._dev_valid:
             b, s = self._lat.tracked()
-            return int(b[0]), int(s[0])
+            return int(b[self._rep]), int(s[self._rep])
         return None
+
+    def _bind(self, lat, rep, model_code):
+        """Make this config local replica ``rep`` of a shared batch (replica exchange); uploads it."""
+        if self._lat is not None and not self._lat_shared and self._lat is not lat:
+            self._pull()
+            self._lat.close()
+        self._pull()
+        self._lat, self._rep, self._lat_shared = lat, rep, True
+        self._lat_key = (model_code, lat.layout)
+        lat.upload(rep, self._to_int8(self._host))
+        self._dev_valid = True
 
     # -- pickling (TemperatureRX_MPI / ParallelMC pickle configs, py_mc/mc_mpi.py:67,179) -------
     def __getstate__(self):
         self._pull()
         st = dict(self.__dict__)
         st["_lat"] = None
+        st["_rep"] = 0
+        st["_lat_shared"] = False
         st["_lat_key"] = None
         st["_dev_valid"] = False
         st["_host_valid"] = True

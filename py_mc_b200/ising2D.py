@@ -48,25 +48,29 @@ class ising2D(model):
     def _pmc_energy(self, bond, second):
         return self.J * float(bond)
 
+    def _pmc_energy_coeffs(self):
+        """(c_bond, c_second) with E = c_bond*bond + c_second*second, for the on-device exchange test."""
+        return float(self.J), 0.0
+
     # -- reference API -------------------------------------------------------------------
     def energy(self, ising2D_config):
         lat = ising2D_config._attach(self._pmc_model)
         bond, _ = lat.reduce_observables()
-        return self._pmc_energy(int(bond[0]), 0)
+        return self._pmc_energy(int(bond[ising2D_config._rep]), 0)
 
     def magnetization(self, ising2D_config):
         obs = ising2D_config._device_observables()
         if obs is None:
             lat = ising2D_config._attach(self._pmc_model)
             _, m = lat.reduce_observables()
-            return float(m[0])
+            return float(m[ising2D_config._rep])
         return float(obs[1])
 
     def trialstep(self, ising2D_config, energy):
         x = rand.randrange(ising2D_config.lenX)
         y = rand.randrange(ising2D_config.lenY)
         lat = ising2D_config._attach(self._pmc_model)
-        s, nn = lat.propose(0, [x], [y])
+        s, nn = lat.propose(ising2D_config._rep, [x], [y])
         return [x, y], self._pmc_dE(s[0], nn[0])
 
     def newconfig(self, ising2D_config, dconfig):
