@@ -131,14 +131,150 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
-def workload_name(args):
+def pick_workload(args, world):
+    if args.workload != "auto":
+        return args.workload
+    return "ising16k" if world == 1 else "rx"
+
+
+def workload_name(args, world=None):
+    world = args.gpus if world is None else world
+    if pick_workload(args, world) == "rx":
+        return ("ising2d_replica_exchange_%d_replicas_of_%dx%d_per_gpu_kT=%.2f..%.2f_exchange_every_%d_sweeps"
+                % (args.rx_replicas, args.rx_L, args.rx_L, args.rx_kT_lo, args.rx_kT_hi, args.rx_every))
     return "ising2d_%dx%d_single_replica_checkerboard_kT=Tc_J=-1" % (args.L, args.L)
 
 
 # ------------------------------------------------------------------------------------------------
+def run_rx(args):
+    """Replica exchange, weak scaling: every GPU holds rx_replicas lattices of rx_L^2; the ladder spans all
+    replicas of all GPUs; energies are all-gathered with NCCL (in place, on the kernels' stream) and the
+    exchange is decided on every GPU by the same kernel.  No host synchronisation in the timed region."""
+    import numpy as np
+    import torch
+    rank, local_rank, world = dist_env()
+    from py_mc_b200 import _cabi
+    from py_mc_b200.ising2D import ising2D
+    from py_mc_b200.mc_mpi import _DeviceArray
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    L, nloc = args.rx_L, args.rx_replicas
+    R = nloc * world
+    layout = _cabi.LAYOUT_BITS if args.layout == "bits" else _cabi.LAYOUT_INT8
+    kTs = np.linspace(args.rx_kT_lo, args.rx_kT_hi, R)
+    model = ising2D(-1.0)
+    lat = _cabi.Lattices(_cabi.MODEL_ISING, L, L, nreplicas=nloc, ntemps=R, seed=SEED, layout=layout,
+                         device=local_rank, replica_offset=rank * nloc, nreplicas_global=R)
+    stream = torch.cuda.current_stream()
+    lat.set_stream(stream.cuda_stream)
+    lat.init_random()
+    lat.set_accept_tables(np.array([model._pmc_thresholds(kT) for kT in kTs]))
+    lat.rx_setup(1.0 / kTs, -1.0)
+    eptr, _ = lat.rx_buffers()
+    e_all = torch.as_tensor(_DeviceArray(eptr, R, "<f8"), device="cuda")
+    e_mine = e_all[rank * nloc:(rank + 1) * nloc]
+    state = {"scheme": 0, "done": 0, "exchanges": 0}
+
+    def steps(n):
+        for _ in range(n):
+            lat.sweep(1)
+            state["done"] += 1
+            if state["done"] % args.rx_every == 0:
+                lat.rx_energies()
+                if dist is not None:
+                    dist.all_gather_into_tensor(e_all, e_mine)
+                lat.rx_exchange(state["scheme"])
+                state["scheme"] ^= 1
+                state["exchanges"] += 1
+
+    steps(args.warmup)
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ex0 = state["exchanges"]
+    ev0.record(stream)
+    steps(args.steps)
+    ev1.record(stream)
+    torch.cuda.synchronize()
+    ms = ev0.elapsed_time(ev1)
+    clocks = sampler.stop()
+    if dist is not None:
+        dist.barrier()
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    nsites = nloc * L * L
+    value = world * nsites * args.steps / (ms * 1e-3)
+    nex = state["exchanges"] - ex0
+
+    # end to end: host configurations in, sweeps + exchanges, observables and the map out, every step
+    host = [lat.download(r) for r in range(min(nloc, 4))]
+    img = np.stack([lat.download(r) for r in range(nloc)]) if args.e2e_full else None
+    reps = 3
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        for r in range(nloc):
+            lat.upload(r, img[r] if img is not None else host[r % len(host)])
+        steps(args.e2e_sweeps)
+        b, m = lat.tracked()
+        mp = lat.get_replica_to_T()
+    t_e2e = time.perf_counter() - t0
+    if dist is not None:
+        t = torch.tensor([t_e2e], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t_e2e = float(t.item())
+    e2e_value = world * nsites * args.e2e_sweeps * reps / t_e2e
+    tried, acc = lat.rx_stats()
+
+    bytes_per_site = 1.0 if layout == _cabi.LAYOUT_INT8 else 0.125
+    alg = 2.0 * bytes_per_site * nsites / 2
+    launch_ms = ms / (2 * args.steps)  # exchange kernels are ~microseconds; stated in config
+    peak, peak_src = measured_peak_hbm()
+    achieved = alg / (launch_ms * 1e-3) / 1e9
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8" if layout == _cabi.LAYOUT_INT8 else "u64 (1 bit/site)",
+            "data": "synthetic",
+            "config": {"workload": workload_name(args, world), "layout": args.layout, "sites_per_gpu": nsites,
+                       "replicas_per_gpu": nloc, "replicas_total": R, "lattice": [L, L],
+                       "step": "one sweep of every replica (2 colour passes) + exchange when due",
+                       "exchanges_in_timed_region": nex, "seed": SEED,
+                       "rx_sweeps_per_s": world * nloc * args.steps / (ms * 1e-3),
+                       "exchange_acceptance": float(acc.sum()) / max(1.0, float(tried.sum())),
+                       "l2": "working set %d MiB per GPU %s L2" % (int(nsites * bytes_per_site) >> 20,
+                                                                  "exceeds" if nsites * bytes_per_site > 126e6 else "fits in"),
+                       "parallelism": "replicas block-partitioned over %d GPU(s); NCCL all-gather of %d energies per "
+                                      "exchange" % (world, R)},
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": nsites,
+                    "d2h_bytes_per_step": 16 * nloc + 4 * R, "sweeps_per_step": args.e2e_sweeps,
+                    "note": "C-ABI: upload every replica from host int8, sweeps+exchanges, read back tracked "
+                            "observables and the replica->T map"},
+            "gpu_launches": 2 * args.steps + 2 * nex,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "kernel": "sweep (colour pass)", "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": alg},
+        }
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
 def run_ours(args):
     import numpy as np
     rank, local_rank, world = dist_env()
+    if pick_workload(args, world) == "rx":
+        return run_rx(args)
     from py_mc_b200 import _cabi
     from py_mc_b200.ising2D import ising2D
 
@@ -265,6 +401,13 @@ def main():
     ap.add_argument("--also-bits", action="store_true", default=True)
     ap.add_argument("--no-also-bits", dest="also_bits", action="store_false")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--workload", default="auto", choices=["auto", "ising16k", "rx"])
+    ap.add_argument("--rx-replicas", type=int, default=256, help="replicas per GPU (weak scaling)")
+    ap.add_argument("--rx-L", type=int, default=1024)
+    ap.add_argument("--rx-every", type=int, default=10, help="sweeps between exchanges")
+    ap.add_argument("--rx-kT-lo", type=float, default=2.0)
+    ap.add_argument("--rx-kT-hi", type=float, default=2.6)
+    ap.add_argument("--e2e-full", action="store_true", help="rx e2e uploads a distinct host image per replica")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

@@ -83,8 +83,11 @@ int pymc_device_count(int *count);
  * replicas and ParallelMC.__init__'s one-engine-per-rank set-up (py_mc/mc_mpi.py:38-56). */
 int pymc_create(const pymc_params *params, pymc_handle **out);
 int pymc_destroy(pymc_handle *h);
-/* Run on a caller-provided CUDA stream (cudaStream_t cast to void*); NULL = the handle's own. */
+/* Run on a caller-provided CUDA stream (cudaStream_t cast to void*; NULL = CUDA's legacy default
+ * stream) so that the caller's own work on that stream -- e.g. an NCCL all-gather -- is ordered
+ * with the kernels.  pymc_reset_stream goes back to the handle's private non-blocking stream. */
 int pymc_set_stream(pymc_handle *h, void *cuda_stream);
+int pymc_reset_stream(pymc_handle *h);
 int pymc_synchronize(pymc_handle *h);
 
 /* ---- configurations ---------------------------------------------------------------

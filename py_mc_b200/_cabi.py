@@ -19,7 +19,7 @@ NCLASS = {MODEL_ISING: 5, MODEL_LATGAS: 10}
 # every symbol include/pymc_b200.h declares (tests check the library exports all of them)
 SYMBOLS = [
     "pymc_abi_version", "pymc_last_error", "pymc_device_count", "pymc_create", "pymc_destroy",
-    "pymc_set_stream", "pymc_synchronize", "pymc_upload_config", "pymc_download_config",
+    "pymc_set_stream", "pymc_reset_stream", "pymc_synchronize", "pymc_upload_config", "pymc_download_config",
     "pymc_init_random", "pymc_set_accept_tables", "pymc_set_replica_to_T", "pymc_get_replica_to_T",
     "pymc_sweep", "pymc_get_sweep_counter", "pymc_set_sweep_counter", "pymc_reduce_observables",
     "pymc_get_tracked", "pymc_propose", "pymc_timer_start", "pymc_timer_stop",
@@ -57,6 +57,7 @@ def _load():
         "pymc_create": [C.POINTER(Params), C.POINTER(P)],
         "pymc_destroy": [P],
         "pymc_set_stream": [P, P],
+        "pymc_reset_stream": [P],
         "pymc_synchronize": [P],
         "pymc_upload_config": [P, I, P, C.c_size_t],
         "pymc_download_config": [P, I, P, C.c_size_t],
@@ -144,7 +145,11 @@ class Lattices:
         return self.lenX * self.lenY
 
     def set_stream(self, cuda_stream_ptr):
-        check(lib.pymc_set_stream(self._h, C.c_void_p(cuda_stream_ptr or 0)))
+        """Run on the given cudaStream_t (an int; 0 = the legacy default stream)."""
+        check(lib.pymc_set_stream(self._h, C.c_void_p(int(cuda_stream_ptr))))
+
+    def reset_stream(self):
+        check(lib.pymc_reset_stream(self._h))
 
     def synchronize(self):
         check(lib.pymc_synchronize(self._h))

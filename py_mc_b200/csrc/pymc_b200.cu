@@ -565,7 +565,14 @@ int pymc_create(const pymc_params *p, pymc_handle **out) {
 int pymc_set_stream(pymc_handle *h, void *cuda_stream) {
     ENTER(h);
     CUDA_TRY(cudaStreamSynchronize(h->stream));
-    h->stream = cuda_stream ? (cudaStream_t)cuda_stream : h->own_stream;
+    h->stream = (cudaStream_t)cuda_stream;  // NULL is CUDA's legacy default stream, a valid choice
+    return PYMC_OK;
+}
+
+int pymc_reset_stream(pymc_handle *h) {
+    ENTER(h);
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    h->stream = h->own_stream;
     return PYMC_OK;
 }
 
