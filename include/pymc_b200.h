@@ -159,6 +159,12 @@ int pymc_rx_get_stats(pymc_handle *h, uint64_t *tried, uint64_t *accepted, int n
 int pymc_rx_get_round(pymc_handle *h, uint64_t *round);
 int pymc_rx_set_round(pymc_handle *h, uint64_t round);
 
+/* ---- pinned host memory ----------------------------------------------------------------
+ * Page-locked buffers for upload/download at full PCIe speed (the reference keeps its arrays in
+ * ordinary numpy memory, examples/ising2D.py:62; pageable buffers work too, only slower). */
+int pymc_host_alloc(size_t bytes, void **out);
+int pymc_host_free(void *ptr);
+
 /* ---- timing helper (CUDA events on the handle's stream) ------------------------------ */
 int pymc_timer_start(pymc_handle *h);
 int pymc_timer_stop(pymc_handle *h, float *elapsed_ms); /* synchronises */

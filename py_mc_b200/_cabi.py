@@ -25,6 +25,7 @@ SYMBOLS = [
     "pymc_get_tracked", "pymc_propose", "pymc_timer_start", "pymc_timer_stop",
     "pymc_rx_setup", "pymc_rx_energies", "pymc_rx_buffers", "pymc_rx_exchange", "pymc_rx_cycle",
     "pymc_rx_get_energies", "pymc_rx_get_stats", "pymc_rx_get_round", "pymc_rx_set_round",
+    "pymc_host_alloc", "pymc_host_free",
 ]
 
 
@@ -80,6 +81,8 @@ def _load():
         "pymc_rx_get_stats": [P, P, P, I],
         "pymc_rx_get_round": [P, C.POINTER(C.c_uint64)],
         "pymc_rx_set_round": [P, C.c_uint64],
+        "pymc_host_alloc": [C.c_size_t, C.POINTER(P)],
+        "pymc_host_free": [P],
         "pymc_timer_start": [P],
         "pymc_timer_stop": [P, C.POINTER(C.c_float)],
     }
@@ -109,6 +112,29 @@ def device_count():
 
 def _ptr(a):
     return a.ctypes.data_as(C.c_void_p)
+
+
+class _PinnedOwner:
+    def __init__(self, ptr):
+        self.ptr = ptr
+
+    def __del__(self):
+        try:
+            lib.pymc_host_free(C.c_void_p(self.ptr))
+        except Exception:
+            pass
+
+
+def pinned_empty(shape, dtype=np.int8):
+    """numpy array in page-locked host memory (freed when the array and its views are gone)."""
+    dtype = np.dtype(dtype)
+    n = int(np.prod(shape)) * dtype.itemsize
+    p = C.c_void_p()
+    check(lib.pymc_host_alloc(n, C.byref(p)))
+    owner = _PinnedOwner(p.value)
+    buf = (C.c_char * max(n, 1)).from_address(p.value)
+    buf._owner = owner  # keeps the allocation alive as long as the ctypes buffer (hence the array) lives
+    return np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
 
 
 class Lattices:

@@ -71,6 +71,8 @@ class LatticeConfig:
             self._host_valid = True
 
     def _to_int8(self, a):
+        if getattr(a, "dtype", None) == np.int8:
+            return a
         lo, hi = self._pmc_values
         return np.where(np.asarray(a) > (lo + hi) / 2.0, hi, lo).astype(np.int8)
 

@@ -16,6 +16,7 @@
 #include "pmc_core.cuh"
 #include "pmc_tiled_i8.cuh"
 #include "pmc_rx.cuh"
+#include "pmc_layout.cuh"
 
 using namespace pmc;
 
@@ -70,6 +71,25 @@ struct Loader<PYMC_LAYOUT_INT8> {
     }
     static __device__ __forceinline__ uint64_t word(const Lat &L, int rep, int colour, int i, int w) {
         const int8_t *p = row(L, rep, colour, i) + 64 * w;
+        if ((L.nk & 63) == 0) {  // whole words, 16-byte aligned: four 128-bit loads, multiply-gather packing
+            const uint4 *q = reinterpret_cast<const uint4 *>(p);
+            uint64_t m = 0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint4 v = __ldg(q + j);
+                // sign bit set <=> -1 (Ising); 0/1 bytes of the lattice gas have bit 0 set <=> occupied.
+                // "p[l] > 0" for both models: byte is 0x01.
+                const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+                uint32_t r = 0;
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const uint32_t pos = w4[e] & ~(w4[e] >> 7) & 0x01010101u;  // bit 0 set and sign clear
+                    r |= ((pos * 0x10204080u) >> 28) << (4 * e);
+                }
+                m |= (uint64_t)r << (16 * j);
+            }
+            return m;
+        }
         int n = min(64, L.nk - 64 * w);
         uint64_t m = 0;
         for (int l = 0; l < n; ++l) m |= (uint64_t)(p[l] > 0) << l;
@@ -599,7 +619,13 @@ int pymc_upload_config(pymc_handle *h, int replica, const int8_t *host, size_t n
     CUDA_TRY(cudaMemcpyAsync(h->staging, host, nsites, cudaMemcpyHostToDevice, h->stream));
     Lat L = make_lat(h);
     dim3 grid((h->p.lenX * h->nw + 127) / 128, 2);
-    if (h->p.layout == PYMC_LAYOUT_BITS)
+    const bool fast = h->p.lenY % 16 == 0 && (h->p.layout == PYMC_LAYOUT_INT8 || h->p.lenY % 128 == 0);
+    if (fast) {
+        const int nchunks = h->p.lenX * (h->p.lenY / 16);
+#define CALL_PACKF(LAY, MOD) pack_fast_kernel<LAY, MOD, Lat><<<(nchunks + 255) / 256, 256, 0, h->stream>>>(L, replica, h->staging)
+        DISPATCH(h, CALL_PACKF);
+#undef CALL_PACKF
+    } else if (h->p.layout == PYMC_LAYOUT_BITS)
         pack_kernel<PYMC_LAYOUT_BITS><<<grid, 128, 0, h->stream>>>(L, replica, h->staging);
     else
         pack_kernel<PYMC_LAYOUT_INT8><<<grid, 128, 0, h->stream>>>(L, replica, h->staging);
@@ -620,7 +646,11 @@ int pymc_download_config(pymc_handle *h, int replica, int8_t *host, size_t nsite
     if (rc) return rc;
     Lat L = make_lat(h);
     dim3 grid((h->p.lenX * h->nw + 127) / 128, 2);
-#define CALL_UNPACK(LAY, MOD) unpack_kernel<LAY, MOD><<<grid, 128, 0, h->stream>>>(L, replica, h->staging)
+    const bool fast = h->p.lenY % 16 == 0 && (h->p.layout == PYMC_LAYOUT_INT8 || h->p.lenY % 128 == 0);
+    const int nchunks = h->p.lenX * (h->p.lenY / 16);
+#define CALL_UNPACK(LAY, MOD)                                                                                     \
+    if (fast) unpack_fast_kernel<LAY, MOD, Lat><<<(nchunks + 255) / 256, 256, 0, h->stream>>>(L, replica, h->staging); \
+    else unpack_kernel<LAY, MOD><<<grid, 128, 0, h->stream>>>(L, replica, h->staging)
     DISPATCH(h, CALL_UNPACK);
 #undef CALL_UNPACK
     CUDA_TRY(cudaGetLastError());
@@ -968,6 +998,18 @@ int pymc_rx_get_round(pymc_handle *h, uint64_t *round) {
 int pymc_rx_set_round(pymc_handle *h, uint64_t round) {
     REQUIRE(h, PYMC_ERR_BADARG, "pymc_rx_set_round: null handle");
     h->rx_round = round;
+    return PYMC_OK;
+}
+
+int pymc_host_alloc(size_t bytes, void **out) {
+    REQUIRE(out, PYMC_ERR_BADARG, "pymc_host_alloc: null pointer");
+    *out = nullptr;
+    CUDA_TRY(cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault));
+    return PYMC_OK;
+}
+
+int pymc_host_free(void *ptr) {
+    if (ptr) CUDA_TRY(cudaFreeHost(ptr));
     return PYMC_OK;
 }
 
