@@ -126,6 +126,22 @@ int pymc_set_sweep_counter(pymc_handle *h, uint64_t counter);
 int pymc_reduce_observables(pymc_handle *h, int64_t *bond, int64_t *second);
 int pymc_get_tracked(pymc_handle *h, int64_t *bond, int64_t *second);
 
+/* No counterpart in the reference (it has no device memory to manage).  Same results and same
+ * side effect as pymc_reduce_observables, for callers that must not allocate while running: a
+ * process that has given all device memory to another allocator or works under a fixed memory
+ * budget (a late cudaMalloc can fail there), or a loop that cannot take the device-wide
+ * synchronisation cudaMalloc/cudaFree imply.  It calls no cudaMalloc, cudaFree or other
+ * allocating routine, host or device: the kernel's accumulators sit in a static 64 KiB device
+ * array that each GPU holds from library load to process exit.
+ * Limits and rules:
+ *   - at most 4096 replicas per handle; more returns PYMC_ERR_UNSUPPORTED with a message.
+ *   - the first call on each device looks up the array's device address (one
+ *     cudaGetSymbolAddress); make that first call before any stream capture begins.
+ *   - all handles on a GPU share the array.  The call clears the part it uses, so earlier contents
+ *     never leak into a result, but two such calls whose GPU work overlaps (different streams or
+ *     threads) race on it: run them one after the other. */
+int pymc_reduce_observables_static(pymc_handle *h, int64_t *bond, int64_t *second);
+
 /* ---- parity helper -------------------------------------------------------------------
  * For n sites (x[i], y[i]) of one replica return the site value and the sum of its four
  * neighbours: the integers from which trialstep's dE is formed (examples/ising2D.py:39-45,

@@ -25,7 +25,7 @@ SYMBOLS = [
     "pymc_get_tracked", "pymc_propose", "pymc_timer_start", "pymc_timer_stop",
     "pymc_rx_setup", "pymc_rx_energies", "pymc_rx_buffers", "pymc_rx_exchange", "pymc_rx_cycle",
     "pymc_rx_get_energies", "pymc_rx_get_stats", "pymc_rx_get_round", "pymc_rx_set_round",
-    "pymc_host_alloc", "pymc_host_free",
+    "pymc_host_alloc", "pymc_host_free", "pymc_reduce_observables_static",
 ]
 
 
@@ -71,6 +71,7 @@ def _load():
         "pymc_set_sweep_counter": [P, C.c_uint64],
         "pymc_reduce_observables": [P, P, P],
         "pymc_get_tracked": [P, P, P],
+        "pymc_reduce_observables_static": [P, P, P],
         "pymc_propose": [P, I, P, P, I, P, P],
         "pymc_rx_setup": [P, P, I, C.c_double, C.c_double],
         "pymc_rx_energies": [P],
@@ -233,6 +234,16 @@ class Lattices:
         b = np.empty(self.nreplicas, dtype=np.int64)
         s = np.empty(self.nreplicas, dtype=np.int64)
         check(lib.pymc_reduce_observables(self._h, _ptr(b), _ptr(s)))
+        self._tracked_cache = (b, s)
+        return b, s
+
+    def reduce_observables_static(self):
+        """Same as ``reduce_observables`` through the entry point that allocates nothing (for hosts that
+        may not call cudaMalloc while running); at most 4096 replicas, shares one static device array
+        per GPU, so do not overlap two such calls on one GPU."""
+        b = np.empty(self.nreplicas, dtype=np.int64)
+        s = np.empty(self.nreplicas, dtype=np.int64)
+        check(lib.pymc_reduce_observables_static(self._h, _ptr(b), _ptr(s)))
         self._tracked_cache = (b, s)
         return b, s
 

@@ -1029,3 +1029,69 @@ int pymc_timer_stop(pymc_handle *h, float *elapsed_ms) {
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------
+// Observables without any allocation.
+//
+// Who this is for: a host program that must not allocate once it is running.  Typical cases are a
+// process whose device memory has been handed over in full to another allocator (a framework's
+// caching pool, a fixed per-client memory budget), so that a later cudaMalloc may simply fail, and a
+// latency-sensitive loop that cannot accept the implicit device-wide synchronisation a cudaMalloc
+// or cudaFree brings with it.  pymc_reduce_observables itself keeps its accumulators in memory
+// that pymc_create obtained with cudaMalloc and stages the result through a host array from new[];
+// this variant needs neither.
+//
+// The accumulators of reduce_kernel live in the file-scope array below instead: 16 bytes per replica,
+// PYMC_STATIC_MAX_REPLICAS replicas, 64 KiB that every GPU which loads this library holds until the
+// process exits.  In host code the name g_static_obs is only a stand-in for the device object, not
+// a device address, so the address is looked up with cudaGetSymbolAddress -- once per device, with
+// that device current -- and cached.
+// ------------------------------------------------------------------------------------------
+#define PYMC_STATIC_MAX_REPLICAS 4096
+#define PYMC_STATIC_MAX_DEVICES 64
+static __device__ __align__(256) unsigned long long g_static_obs[2 * PYMC_STATIC_MAX_REPLICAS];
+static unsigned long long *g_static_obs_addr[PYMC_STATIC_MAX_DEVICES];  // per device, null = not looked up yet
+
+// Device address of g_static_obs on `device`, which must be the current device.
+static int static_obs_address(int device, unsigned long long **out) {
+    REQUIRE(device >= 0 && device < PYMC_STATIC_MAX_DEVICES, PYMC_ERR_UNSUPPORTED,
+            "static scratch supports device ordinals below %d (got %d)", PYMC_STATIC_MAX_DEVICES, device);
+    if (!g_static_obs_addr[device]) {
+        unsigned long long *ptr = nullptr;
+        CUDA_TRY(cudaGetSymbolAddress((void **)&ptr, g_static_obs));
+        REQUIRE(ptr != nullptr, PYMC_ERR_CUDA, "cudaGetSymbolAddress returned a null address for the static scratch");
+        g_static_obs_addr[device] = ptr;
+    }
+    *out = g_static_obs_addr[device];
+    return PYMC_OK;
+}
+
+extern "C" int pymc_reduce_observables_static(pymc_handle *h, int64_t *bond, int64_t *second) {
+    ENTER(h);
+    REQUIRE(bond && second, PYMC_ERR_BADARG, "pymc_reduce_observables_static: null output pointer");
+    REQUIRE(h->p.nreplicas <= PYMC_STATIC_MAX_REPLICAS, PYMC_ERR_UNSUPPORTED,
+            "pymc_reduce_observables_static: %d replicas exceed the static scratch (at most %d replicas per call); "
+            "use pymc_reduce_observables",
+            h->p.nreplicas, PYMC_STATIC_MAX_REPLICAS);
+    unsigned long long *acc = nullptr;
+    int rc = static_obs_address(h->p.device, &acc);
+    if (rc) return rc;
+    const size_t nrep = (size_t)h->p.nreplicas;
+    // The array still holds whatever the previous call (of any handle on this GPU) left in it, and the
+    // kernel adds into it: the part used now has to start from zero.
+    CUDA_TRY(cudaMemsetAsync(acc, 0, nrep * 16, h->stream));
+    Lat L = make_lat(h);
+    dim3 grid((2 * h->p.lenX * h->nw + 255) / 256, h->p.nreplicas);
+#define CALL_REDUCE_STATIC(LAY, MOD) reduce_kernel<LAY, MOD><<<grid, 256, 0, h->stream>>>(L, acc)
+    DISPATCH(h, CALL_REDUCE_STATIC);
+#undef CALL_REDUCE_STATIC
+    CUDA_TRY(cudaGetLastError());
+    // same side effect as pymc_reduce_observables: the tracked values are re-based on the fresh sums
+    CUDA_TRY(cudaMemcpyAsync(h->tracked, acc, nrep * 16, cudaMemcpyDeviceToDevice, h->stream));
+    h->dirty = false;
+    // pairs (bond, second) are interleaved on the device; copy each column straight into the caller's array
+    CUDA_TRY(cudaMemcpy2DAsync(bond, 8, acc, 16, 8, nrep, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaMemcpy2DAsync(second, 8, acc + 1, 16, 8, nrep, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return PYMC_OK;
+}
