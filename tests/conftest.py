@@ -35,3 +35,8 @@ def golden_ising_de():
 @pytest.fixture(scope="session")
 def golden_rx():
     return load_golden("rx")
+
+
+@pytest.fixture(scope="session")
+def golden_latgas():
+    return load_golden("latgas")

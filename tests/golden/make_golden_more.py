@@ -139,4 +139,68 @@ def gen_rx(out):
     out["meta"] = np.array(json.dumps(meta))
 
 
-MORE = {"rx": gen_rx}
+LATGAS_CASES = [
+    # name, lenX, lenY, J, Eads, mu, kT, seed, replica, nsweeps
+    ("lg_5x... shipped-like J=0", 6, 6, 0.0, -0.4, -0.1, 0.25, 11, 0, 8),
+    ("lg_attract", 8, 10, -1.0, -0.5, 0.25, 1.0, 12, 1, 10),
+    ("lg_repulse", 8, 8, 1.0, -2.0, 0.0, 0.5, 13, 2, 10),
+    ("lg_word_6x128", 6, 128, -0.5, 0.25, -0.75, 0.75, 14, 0, 5),
+    ("lg_partial_4x132", 4, 132, 0.25, -0.5, 0.0, 0.3, 15, 3, 5),
+]
+
+
+def gen_latgas(out):
+    """Flip moves of examples/latgas.py driven in checkerboard order with injected uniforms."""
+    ref_root = os.environ.get("PYMC_REFERENCE", "/root/reference")
+    sys.path.insert(0, ref_root)
+    sys.path.insert(0, os.path.join(ref_root, "examples"))
+    import py_mc.mc as refmc
+    import latgas as ref_latgas
+    from make_golden import SiteInjector, checkerboard_schedule
+    from oracle import latgas as o_latgas
+    inj = SiteInjector()
+    ref_latgas.rand = inj
+    refmc.random = inj.random
+    meta = []
+    cwd = os.getcwd()
+    os.chdir(tempfile.mkdtemp())
+    try:
+        for n, (name, lenX, lenY, J, Eads, mu, kT, seed, replica, nsweeps) in enumerate(LATGAS_CASES):
+            name = "lg%d" % n
+            cfg = ref_latgas.latgas_config(lenX, lenY)
+            init = o_latgas.init_config(seed, replica, lenX, lenY)
+            cfg.config[:, :] = init
+            model = ref_latgas.latticegas(Eads=Eads, J=J, mu=mu)
+            calc = refmc.CanonicalMonteCarlo(model, kT, cfg)
+            # dE for every site of the initial configuration, straight from trialstep
+            sites = [(x, y) for x in range(lenX) for y in range(lenY)]
+            inj.load(sites, [0.0] * len(sites))
+            dEs = np.zeros((lenX, lenY))
+            for (x, y) in sites:
+                dconfig, dE = model.trialstep(cfg, 0.0)
+                assert dconfig == [x, y]
+                dEs[x, y] = dE
+            e0 = model.energy(cfg)
+            energies, dens, configs = [], [], []
+            for sw in range(nsweeps):
+                s2, us = checkerboard_schedule(seed, replica, sw, lenX, lenY)
+                inj.load(s2, us)
+                calc.run(lenX * lenY)
+                energies.append(calc.energy)
+                dens.append(model.density(cfg))
+                configs.append(cfg.config.astype(np.int8).copy())
+            out[name + "_init"] = init
+            out[name + "_dE"] = dEs
+            out[name + "_e0"] = np.float64(e0)
+            out[name + "_energy"] = np.array(energies, dtype=np.float64)
+            out[name + "_density"] = np.array(dens, dtype=np.float64)
+            out[name + "_configs"] = np.array(configs, dtype=np.int8)
+            meta.append(dict(name=name, lenX=lenX, lenY=lenY, J=J, Eads=Eads, mu=mu, kT=kT, seed=seed,
+                             replica=replica, nsweeps=nsweeps))
+            print("latgas", name, "E0", e0, "E_end", energies[-1], "N_end", dens[-1])
+    finally:
+        os.chdir(cwd)
+    out["meta"] = np.array(json.dumps(meta))
+
+
+MORE = {"rx": gen_rx, "latgas": gen_latgas}
