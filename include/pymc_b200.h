@@ -48,7 +48,8 @@ typedef enum {
 
 typedef enum {
     PYMC_KERNEL_AUTO = 0,    /* fastest kernel that supports the shape                     */
-    PYMC_KERNEL_GENERIC = 1  /* the simple one-thread-per-word kernel (any even lenX, lenY) */
+    PYMC_KERNEL_GENERIC = 1, /* the simple one-thread-per-word kernel (any even lenX, lenY) */
+    PYMC_KERNEL_TWO_PASS = 2 /* one launch per colour even where the fused int8 sweep kernel applies */
 } pymc_kernel;
 
 /* Number of acceptance-table entries per temperature: Ising 5 (index = number of aligned
@@ -113,6 +114,9 @@ int pymc_get_replica_to_T(pymc_handle *h, int32_t *map, int n);
  * Metropolis trials (= that many MCstep() calls of py_mc/mc.py:170-185 driven in
  * checkerboard order).  Asynchronous. */
 int pymc_sweep(pymc_handle *h, int64_t nsweeps);
+/* Which kernel pymc_sweep uses for this handle and how many launches one sweep takes (1 for the
+ * fused two-colour int8 kernel, otherwise 2); for benchmarks and logs. */
+int pymc_sweep_kernel_info(pymc_handle *h, int *launches_per_sweep, const char **kernel_name);
 int pymc_get_sweep_counter(pymc_handle *h, uint64_t *counter);
 int pymc_set_sweep_counter(pymc_handle *h, uint64_t counter);
 

@@ -13,7 +13,7 @@ from ._build import LIBPATH
 ABI_VERSION = 1
 MODEL_ISING, MODEL_LATGAS = 0, 1
 LAYOUT_INT8, LAYOUT_BITS = 0, 1
-KERNEL_AUTO, KERNEL_GENERIC = 0, 1
+KERNEL_AUTO, KERNEL_GENERIC, KERNEL_TWO_PASS = 0, 1, 2
 NCLASS = {MODEL_ISING: 5, MODEL_LATGAS: 10}
 
 # every symbol include/pymc_b200.h declares (tests check the library exports all of them)
@@ -25,7 +25,7 @@ SYMBOLS = [
     "pymc_get_tracked", "pymc_propose", "pymc_timer_start", "pymc_timer_stop",
     "pymc_rx_setup", "pymc_rx_energies", "pymc_rx_buffers", "pymc_rx_exchange", "pymc_rx_cycle",
     "pymc_rx_get_energies", "pymc_rx_get_stats", "pymc_rx_get_round", "pymc_rx_set_round",
-    "pymc_host_alloc", "pymc_host_free", "pymc_reduce_observables_static",
+    "pymc_host_alloc", "pymc_host_free", "pymc_reduce_observables_static", "pymc_sweep_kernel_info",
 ]
 
 
@@ -45,6 +45,8 @@ class PymcError(RuntimeError):
 
 
 def _load():
+    global LIBPATH
+    LIBPATH = os.environ.get("PYMC_B200_LIB", LIBPATH)  # alternative build of the same ABI (kernel experiments)
     if not os.path.exists(LIBPATH):
         raise ImportError(
             "py_mc_b200: %s is missing. Build it with `python -m py_mc_b200._build` "
@@ -67,6 +69,7 @@ def _load():
         "pymc_set_replica_to_T": [P, P, I],
         "pymc_get_replica_to_T": [P, P, I],
         "pymc_sweep": [P, I64],
+        "pymc_sweep_kernel_info": [P, C.POINTER(I), C.POINTER(C.c_char_p)],
         "pymc_get_sweep_counter": [P, C.POINTER(C.c_uint64)],
         "pymc_set_sweep_counter": [P, C.c_uint64],
         "pymc_reduce_observables": [P, P, P],
@@ -218,6 +221,12 @@ class Lattices:
     def sweep(self, nsweeps=1):
         self._tracked_cache = None
         check(lib.pymc_sweep(self._h, int(nsweeps)))
+
+    def sweep_kernel_info(self):
+        """(launches per sweep, kernel name) of the sweep path this handle uses."""
+        n, name = C.c_int(0), C.c_char_p()
+        check(lib.pymc_sweep_kernel_info(self._h, C.byref(n), C.byref(name)))
+        return n.value, name.value.decode()
 
     @property
     def sweep_counter(self):

@@ -54,10 +54,13 @@ struct TileShape {
 };
 
 constexpr int TILE_THREADS = 256;
+#ifndef PMC_TILED_MINBLOCKS
+#define PMC_TILED_MINBLOCKS 6
+#endif
 
 // grid = (nw / TW, ceil(lenX / TH), nrep)
 template <int MODEL, class LatT>
-__global__ void __launch_bounds__(TILE_THREADS) sweep_tiled_i8_kernel(LatT L, int colour, uint64_t step, int tw_log2) {
+__global__ void __launch_bounds__(TILE_THREADS, PMC_TILED_MINBLOCKS) sweep_tiled_i8_kernel(LatT L, int colour, uint64_t step, int tw_log2) {
     constexpr int NCLASS = ModelTraits<MODEL>::NCLASS;
     // packed bits: [0, 256) target tile, [256, 256 + (TH+2)*TW) neighbour rows; as u16 pieces for the
     // chunk-granular phases, as u64 words for the update phase

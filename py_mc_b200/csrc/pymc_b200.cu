@@ -17,6 +17,7 @@
 #include "pmc_tiled_i8.cuh"
 #include "pmc_rx.cuh"
 #include "pmc_layout.cuh"
+#include "pmc_fused_i8.cuh"
 
 using namespace pmc;
 
@@ -393,6 +394,7 @@ struct pymc_handle {
     cudaStream_t own_stream, stream;
     cudaEvent_t ev0, ev1;
     int8_t *i8;
+    int8_t *i8_alt;                // second int8 buffer for the out-of-place fused sweep (allocated on first use)
     uint64_t *bits;
     uint32_t *thr;
     int32_t *rep_to_T;
@@ -480,6 +482,7 @@ int pymc_destroy(pymc_handle *h) {
     if (guard.ok) {
         if (h->own_stream) cudaStreamSynchronize(h->own_stream);
         cudaFree(h->i8);
+        cudaFree(h->i8_alt);
         cudaFree(h->bits);
         cudaFree(h->thr);
         cudaFree(h->rep_to_T);
@@ -736,6 +739,30 @@ int pymc_get_replica_to_T(pymc_handle *h, int32_t *map, int n) {
     return PYMC_OK;
 }
 
+static bool uses_fused(const pymc_handle *h) {
+    return h->p.layout == PYMC_LAYOUT_INT8 && h->p.kernel == PYMC_KERNEL_AUTO && h->nk % 64 == 0 &&
+           h->nw % FUSED_TW == 0 && h->p.lenX % FUSED_TH == 0;
+}
+
+int pymc_sweep_kernel_info(pymc_handle *h, int *launches_per_sweep, const char **kernel_name) {
+    REQUIRE(h, PYMC_ERR_BADARG, "pymc_sweep_kernel_info: null handle");
+    const char *name;
+    int n = 2;
+    if (uses_fused(h)) {
+        name = "sweep_fused_i8_kernel";
+        n = 1;
+    } else if (h->p.layout == PYMC_LAYOUT_BITS && h->p.kernel != PYMC_KERNEL_GENERIC) {
+        name = "sweep_bits_rows_kernel";
+    } else if (h->p.layout == PYMC_LAYOUT_INT8 && h->p.kernel != PYMC_KERNEL_GENERIC && h->nk % 64 == 0) {
+        name = "sweep_tiled_i8_kernel";
+    } else {
+        name = "sweep_word_kernel";
+    }
+    if (launches_per_sweep) *launches_per_sweep = n;
+    if (kernel_name) *kernel_name = name;
+    return PYMC_OK;
+}
+
 int pymc_sweep(pymc_handle *h, int64_t nsweeps) {
     ENTER(h);
     REQUIRE(nsweeps >= 0, PYMC_ERR_BADARG, "pymc_sweep: nsweeps %lld", (long long)nsweeps);
@@ -748,6 +775,25 @@ int pymc_sweep(pymc_handle *h, int64_t nsweeps) {
     dim3 grid((h->p.lenX * h->nw + 127) / 128, h->p.nreplicas);
     // K1 tiled int8 kernel: needs whole words (lenY % 128 == 0); tile = TH rows x TW words, TW | nw
     const bool tiled = h->p.layout == PYMC_LAYOUT_INT8 && h->p.kernel != PYMC_KERNEL_GENERIC && h->nk % 64 == 0;
+    // K1f fused two-colour int8 kernel: whole 32 x 8-word tiles, out of place (ping-pong buffers)
+    const bool fused = uses_fused(h);
+    if (fused && !h->i8_alt && nsweeps > 0)
+        CUDA_TRY(cudaMalloc(&h->i8_alt, (size_t)h->p.nreplicas * 2 * h->p.lenX * h->nk));
+    if (fused) {
+        dim3 fgrid(h->nw / FUSED_TW, h->p.lenX / FUSED_TH, h->p.nreplicas);
+        for (int64_t s = 0; s < nsweeps; ++s) {
+            if (h->p.model == PYMC_MODEL_ISING)
+                sweep_fused_i8_kernel<MODEL_ISING, Lat><<<fgrid, FUSED_THREADS, 0, h->stream>>>(L, h->i8, h->i8_alt, h->sweep_counter);
+            else
+                sweep_fused_i8_kernel<MODEL_LATGAS, Lat><<<fgrid, FUSED_THREADS, 0, h->stream>>>(L, h->i8, h->i8_alt, h->sweep_counter);
+            int8_t *tmp = h->i8;
+            h->i8 = h->i8_alt;
+            h->i8_alt = tmp;
+            h->sweep_counter++;
+        }
+        CUDA_TRY(cudaGetLastError());
+        return PYMC_OK;
+    }
     const bool bitrows = h->p.layout == PYMC_LAYOUT_BITS && h->p.kernel != PYMC_KERNEL_GENERIC;
     const int rpt = h->p.lenX % 4 == 0 ? 4 : 2;
     int tw_log2 = 0;

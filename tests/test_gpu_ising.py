@@ -181,3 +181,38 @@ def test_batched_replicas_are_independent_streams():
         ref = before[r].copy()
         o_ising.sweep(ref, -1.0, kTs[perm[r]], seed, r, 6)
         assert np.array_equal(lat.download(r), ref), r
+
+
+@pytest.mark.parametrize("shape,nrep", [((32, 1024), 1), ((64, 2048), 3), ((96, 1024), 2)])
+def test_fused_two_pass_and_generic_kernels_agree(shape, nrep):
+    """The fused two-colour int8 kernel recomputes a halo ring per tile; it must follow the same
+    trajectory as the two-pass and the generic kernels (and the oracle), including lattices that are a
+    single tile wide or high, where the ring wraps onto the tile itself."""
+    c = _cabi()
+    seed, kT = 4711, 2.3
+    thr = o_ising.threshold_table(-1.0, kT)[1][None, :]
+    lats = {}
+    for name, kernel, layout in (("fused", c.KERNEL_AUTO, INT8), ("two_pass", c.KERNEL_TWO_PASS, INT8),
+                                 ("generic", c.KERNEL_GENERIC, INT8), ("bits", c.KERNEL_AUTO, BITS)):
+        lat = c.Lattices(c.MODEL_ISING, shape[0], shape[1], nreplicas=nrep, seed=seed, layout=layout, kernel=kernel)
+        lat.init_random()
+        lat.set_accept_tables(thr)
+        lats[name] = lat
+    assert lats["fused"].sweep_kernel_info() == (1, "sweep_fused_i8_kernel")
+    assert lats["two_pass"].sweep_kernel_info() == (2, "sweep_tiled_i8_kernel")
+    assert lats["generic"].sweep_kernel_info() == (2, "sweep_word_kernel")
+    assert lats["bits"].sweep_kernel_info() == (2, "sweep_bits_rows_kernel")
+    ref = o_ising.init_config(seed, nrep - 1, *shape)
+    for sw in range(5):  # odd number of sweeps: the fused kernel ends in its second buffer
+        for lat in lats.values():
+            lat.sweep(1)
+        o_ising.sweep(ref, -1.0, kT, seed, nrep - 1, sw)
+    want = {r: lats["generic"].download(r) for r in range(nrep)}
+    assert np.array_equal(want[nrep - 1], ref)
+    for name, lat in lats.items():
+        for r in range(nrep):
+            assert np.array_equal(lat.download(r), want[r]), (name, r)
+        assert np.array_equal(lat.tracked()[0], lats["generic"].tracked()[0]), name
+        assert np.array_equal(lat.tracked()[1], lats["generic"].tracked()[1]), name
+        b, m = lat.reduce_observables()
+        assert np.array_equal(b, lats["generic"].tracked()[0]) and np.array_equal(m, lats["generic"].tracked()[1])
