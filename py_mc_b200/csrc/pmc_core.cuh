@@ -73,8 +73,10 @@ __device__ __forceinline__ uint64_t decide_hard(const uint64_t (&hm)[MAXH], cons
         if (!__any_sync(0xFFFFFFFFu, und != 0)) break;
         uint64_t pe, po;
         word_planes(word_idx, replica, step, domain, call, key, pe, po);
-        uint64_t te = 0, to = 0;
+        // (A four-way uniform branch per plane on the pair of threshold bits needs fewer logic
+        // operations but measured 4% slower: the extra branches cost more issue slots than they save.)
         const int be = 31 - 2 * (int)call, bo = be - 1;
+        uint64_t te = 0, to = 0;
 #pragma unroll
         for (int k = 0; k < MAXH; ++k) {
             te |= hm[k] & (0ull - (uint64_t)((ht[k] >> be) & 1u));
@@ -93,46 +95,68 @@ __device__ __forceinline__ uint64_t decide_hard(const uint64_t (&hm)[MAXH], cons
 // Per-temperature plans: everything that depends only on the (warp-uniform) threshold row is
 // worked out once per thread, outside the per-word path.
 // ------------------------------------------------------------------------------------------
+constexpr int PLAN_WORDS = 16;  // 32-bit words per temperature in the device plan table
+
 template <int MODEL>
 struct Plan;
 
 // Ising.  dE = -2J(2a-4) with a = aligned neighbours, so dE > 0 for a in {3,4} when J < 0 and for
 // a in {0,1} when J > 0 (pymc_set_accept_tables rejects anything else).  Counting *anti*-aligned
 // neighbours in the second case maps it onto the first: the hard classes are always count 3 and 4.
+// Row layout (built on the host by build_row): 0 count-aligned flag, 1-2 thresholds of count 3 / 4,
+// 3-4 enable flags, 5 orientation (1 = flipped).
 template <>
 struct Plan<MODEL_ISING> {
     uint64_t notmask;  // ~0: count aligned neighbours; 0: count anti-aligned neighbours
     uint64_t en3, en4;  // ~0 where the class needs a draw
     uint32_t ht[2];
     int sign;           // +1 / -1: orientation of the bond-sum change
-    __device__ __forceinline__ void init(const uint32_t *__restrict__ thr) {
-        const uint32_t t0 = __ldg(thr + 0), t1 = __ldg(thr + 1), t3 = __ldg(thr + 3), t4 = __ldg(thr + 4);
-        const bool low = (t0 != THR_ALWAYS) || (t1 != THR_ALWAYS);
-        notmask = low ? 0ull : ~0ull;
-        sign = low ? -1 : 1;
-        ht[0] = low ? t1 : t3;
-        ht[1] = low ? t0 : t4;
-        en3 = ht[0] != THR_ALWAYS ? ~0ull : 0ull;
-        en4 = ht[1] != THR_ALWAYS ? ~0ull : 0ull;
+    __device__ __forceinline__ void init(const uint32_t *__restrict__ row) {
+        notmask = __ldg(row + 0) ? ~0ull : 0ull;
+        ht[0] = __ldg(row + 1);
+        ht[1] = __ldg(row + 2);
+        en3 = __ldg(row + 3) ? ~0ull : 0ull;
+        en4 = __ldg(row + 4) ? ~0ull : 0ull;
+        sign = __ldg(row + 5) ? -1 : 1;
+    }
+    static __host__ void build_row(const uint32_t *thr, uint32_t *row) {
+        const bool low = thr[0] != THR_ALWAYS || thr[1] != THR_ALWAYS;
+        const uint32_t tA = low ? thr[1] : thr[3], tB = low ? thr[0] : thr[4];
+        row[0] = low ? 0u : 1u;
+        row[1] = tA;
+        row[2] = tB;
+        row[3] = tA != THR_ALWAYS;
+        row[4] = tB != THR_ALWAYS;
+        row[5] = low ? 1u : 0u;
+        for (int k = 6; k < PLAN_WORDS; ++k) row[k] = 0;
     }
 };
 
 // Lattice gas.  Class = 5c + nn; dE(c=0,nn) = -dE(c=1,nn), so for each nn at most one of the two
-// occupancies needs a draw.
+// occupancies needs a draw.  Row layout: 0-4 "hard class is the empty site" flags, 5-9 thresholds,
+// 10-14 enable flags.
 template <>
 struct Plan<MODEL_LATGAS> {
     uint64_t sel[5];  // XOR-ed with S: result 1 = lane is in the hard occupancy for this nn
     uint64_t en[5];   // ~0 if that nn has a hard class at all
     uint32_t ht[5];
-    __device__ __forceinline__ void init(const uint32_t *__restrict__ thr) {
+    __device__ __forceinline__ void init(const uint32_t *__restrict__ row) {
 #pragma unroll
         for (int n = 0; n < 5; ++n) {
-            const uint32_t te = __ldg(thr + n), to = __ldg(thr + 5 + n);  // empty / occupied site
-            const bool hard_occ = to != THR_ALWAYS;
-            sel[n] = hard_occ ? 0ull : ~0ull;
-            ht[n] = hard_occ ? to : te;
-            en[n] = ht[n] != THR_ALWAYS ? ~0ull : 0ull;
+            sel[n] = __ldg(row + n) ? ~0ull : 0ull;
+            ht[n] = __ldg(row + 5 + n);
+            en[n] = __ldg(row + 10 + n) ? ~0ull : 0ull;
         }
+    }
+    static __host__ void build_row(const uint32_t *thr, uint32_t *row) {
+        for (int n = 0; n < 5; ++n) {
+            const uint32_t te = thr[n], to = thr[5 + n];  // empty / occupied site
+            const bool hard_occ = to != THR_ALWAYS;
+            row[n] = hard_occ ? 0u : 1u;
+            row[5 + n] = hard_occ ? to : te;
+            row[10 + n] = row[5 + n] != THR_ALWAYS;
+        }
+        row[15] = 0;
     }
 };
 

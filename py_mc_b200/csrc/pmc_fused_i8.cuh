@@ -45,7 +45,7 @@ __global__ void __launch_bounds__(FUSED_THREADS, PMC_FUSED_MINBLOCKS)
     const int rep = blockIdx.z, w0 = blockIdx.x * TW, i0 = blockIdx.y * TH;
     const int lenX = L.lenX, nk = L.nk;
     Plan<MODEL> plan;
-    plan.init(L.thr + (size_t)L.rep_to_T[L.rep_offset + rep] * ModelTraits<MODEL>::NCLASS);
+    plan.init(L.plans + (size_t)L.rep_to_T[L.rep_offset + rep] * PLAN_WORDS);
     const int8_t *sb = src + (size_t)(rep * 2 + 0) * lenX * nk;
     const int8_t *sw = src + (size_t)(rep * 2 + 1) * lenX * nk;
     auto wrap_row = [lenX](int i) { return i < 0 ? i + lenX : (i >= lenX ? i - lenX : i); };

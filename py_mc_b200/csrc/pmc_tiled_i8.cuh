@@ -61,7 +61,6 @@ constexpr int TILE_THREADS = 256;
 // grid = (nw / TW, ceil(lenX / TH), nrep)
 template <int MODEL, class LatT>
 __global__ void __launch_bounds__(TILE_THREADS, PMC_TILED_MINBLOCKS) sweep_tiled_i8_kernel(LatT L, int colour, uint64_t step, int tw_log2) {
-    constexpr int NCLASS = ModelTraits<MODEL>::NCLASS;
     // packed bits: [0, 256) target tile, [256, 256 + (TH+2)*TW) neighbour rows; as u16 pieces for the
     // chunk-granular phases, as u64 words for the update phase
     __shared__ __align__(16) uint64_t s_words[256 + 288];
@@ -79,7 +78,7 @@ __global__ void __launch_bounds__(TILE_THREADS, PMC_TILED_MINBLOCKS) sweep_tiled
     const int cpr_log2 = tw_log2 + 2;
 
     Plan<MODEL> plan;
-    plan.init(L.thr + (size_t)L.rep_to_T[L.rep_offset + rep] * NCLASS);
+    plan.init(L.plans + (size_t)L.rep_to_T[L.rep_offset + rep] * PLAN_WORDS);
 
     const int8_t *tgt = L.i8 + (size_t)(rep * 2 + colour) * L.lenX * L.nk;
     const int8_t *oth = L.i8 + (size_t)(rep * 2 + oc) * L.lenX * L.nk;

@@ -55,7 +55,7 @@ struct Lat {
     uint64_t *bits;
     int lenX, lenY, nk, nw;
     int nrep, rep_offset;
-    const uint32_t *thr;       // [ntemps][nclass]
+    const uint32_t *plans;     // [ntemps][PLAN_WORDS] per-temperature plan rows (pmc_core.cuh)
     const int32_t *rep_to_T;   // [nrep_global]
     unsigned long long *tracked;  // [nrep][2]
     PhiloxKey key;
@@ -166,7 +166,7 @@ __device__ __forceinline__ void block_accumulate(int a, int b, unsigned long lon
 template <int MODEL>
 __device__ __forceinline__ void load_plan(const Lat &L, int rep, Plan<MODEL> &plan) {
     const int t = L.rep_to_T[L.rep_offset + rep];
-    plan.init(L.thr + (size_t)t * ModelTraits<MODEL>::NCLASS);
+    plan.init(L.plans + (size_t)t * PLAN_WORDS);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -396,7 +396,7 @@ struct pymc_handle {
     int8_t *i8;
     int8_t *i8_alt;                // second int8 buffer for the out-of-place fused sweep (allocated on first use)
     uint64_t *bits;
-    uint32_t *thr;
+    uint32_t *plans;               // [ntemps][PLAN_WORDS]
     int32_t *rep_to_T;
     unsigned long long *tracked;   // [nrep][2]
     unsigned long long *reduced;   // [nrep][2] output of reduce_kernel
@@ -426,7 +426,7 @@ static Lat make_lat(const pymc_handle *h) {
     L.nw = h->nw;
     L.nrep = h->p.nreplicas;
     L.rep_offset = h->p.replica_offset;
-    L.thr = h->thr;
+    L.plans = h->plans;
     L.rep_to_T = h->rep_to_T;
     L.tracked = h->tracked;
     L.key = make_key(h->p.seed);
@@ -484,7 +484,7 @@ int pymc_destroy(pymc_handle *h) {
         cudaFree(h->i8);
         cudaFree(h->i8_alt);
         cudaFree(h->bits);
-        cudaFree(h->thr);
+        cudaFree(h->plans);
         cudaFree(h->rep_to_T);
         cudaFree(h->tracked);
         cudaFree(h->reduced);
@@ -556,7 +556,7 @@ int pymc_create(const pymc_params *p, pymc_handle **out) {
         } else {
             check(cudaMalloc(&h->bits, nrep * 2 * p->lenX * (size_t)h->nw * 8), "cudaMalloc(bits)");
         }
-        check(cudaMalloc(&h->thr, (size_t)p->ntemps * h->nclass * 4), "cudaMalloc(thr)");
+        check(cudaMalloc(&h->plans, (size_t)p->ntemps * PLAN_WORDS * 4), "cudaMalloc(plans)");
         check(cudaMalloc(&h->rep_to_T, (size_t)p->nreplicas_global * 4), "cudaMalloc(rep_to_T)");
         check(cudaMalloc(&h->tracked, nrep * 16), "cudaMalloc(tracked)");
         check(cudaMalloc(&h->reduced, nrep * 16), "cudaMalloc(reduced)");
@@ -698,8 +698,19 @@ int pymc_set_accept_tables(pymc_handle *h, const uint32_t *thr, int ntemps, int 
                         "pymc_set_accept_tables: row %d has dE > 0 for both occupancies at %d neighbours", t, n);
         }
     }
-    CUDA_TRY(cudaMemcpyAsync(h->thr, thr, (size_t)ntemps * nclass * 4, cudaMemcpyHostToDevice, h->stream));
-    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    // expand each threshold row into the plan row the kernels read (orientation, enables, bit streams)
+    uint32_t *rows = new (std::nothrow) uint32_t[(size_t)ntemps * PLAN_WORDS];
+    REQUIRE(rows, PYMC_ERR_BADARG, "pymc_set_accept_tables: out of host memory");
+    for (int t = 0; t < ntemps; ++t) {
+        if (h->p.model == PYMC_MODEL_ISING)
+            Plan<MODEL_ISING>::build_row(thr + (size_t)t * nclass, rows + (size_t)t * PLAN_WORDS);
+        else
+            Plan<MODEL_LATGAS>::build_row(thr + (size_t)t * nclass, rows + (size_t)t * PLAN_WORDS);
+    }
+    cudaError_t e = cudaMemcpyAsync(h->plans, rows, (size_t)ntemps * PLAN_WORDS * 4, cudaMemcpyHostToDevice, h->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    delete[] rows;
+    if (e != cudaSuccess) return fail(PYMC_ERR_CUDA, "pymc_set_accept_tables: upload failed: %s", cudaGetErrorString(e));
     h->tables_set = true;
     return PYMC_OK;
 }
