@@ -153,6 +153,18 @@ int pymc_reduce_observables_static(pymc_handle *h, int64_t *bond, int64_t *secon
 int pymc_propose(pymc_handle *h, int replica, const int32_t *x, const int32_t *y, int n,
                  int32_t *site_out, int32_t *nnsum_out);
 
+/* ---- particle moves of the lattice gas ------------------------------------------------
+ * Takes over the move branch of latticegas.trialstep (examples/latgas_move.py:56-83) with
+ * nearest-neighbour particle-hole exchanges on 16 conflict-free bond classes and the physically
+ * correct dE = J*d, d = (occupied neighbours gained) - (lost) in -3..3 (the reference's dE for moves
+ * is defective).  thr[t][d+3] as in pymc_set_accept_tables.  One pair sweep tries every
+ * nearest-neighbour bond once (2*lenX*lenY bonds); class_mask selects bond classes (bit c = class c;
+ * 0xFFFF all, 0x00FF horizontal, 0xFF00 vertical).  Needs lenX % 4 == 0 and lenY % 4 == 0. */
+int pymc_set_pair_tables(pymc_handle *h, const uint32_t *thr, int ntemps, int nclass);
+int pymc_pair_sweep(pymc_handle *h, int64_t nsweeps, uint32_t class_mask);
+int pymc_get_pair_counter(pymc_handle *h, uint64_t *counter);
+int pymc_set_pair_counter(pymc_handle *h, uint64_t counter);
+
 /* ---- replica exchange -----------------------------------------------------------------
  * Replaces TemperatureRX_MPI (py_mc/mc_mpi.py:75-209).  Needs ntemps == nreplicas_global
  * (the reference's own requirement, mc_mpi.py:47-52).

@@ -26,6 +26,7 @@ SYMBOLS = [
     "pymc_rx_setup", "pymc_rx_energies", "pymc_rx_buffers", "pymc_rx_exchange", "pymc_rx_cycle",
     "pymc_rx_get_energies", "pymc_rx_get_stats", "pymc_rx_get_round", "pymc_rx_set_round",
     "pymc_host_alloc", "pymc_host_free", "pymc_reduce_observables_static", "pymc_sweep_kernel_info",
+    "pymc_set_pair_tables", "pymc_pair_sweep", "pymc_get_pair_counter", "pymc_set_pair_counter",
 ]
 
 
@@ -76,6 +77,10 @@ def _load():
         "pymc_get_tracked": [P, P, P],
         "pymc_reduce_observables_static": [P, P, P],
         "pymc_propose": [P, I, P, P, I, P, P],
+        "pymc_set_pair_tables": [P, P, I, I],
+        "pymc_pair_sweep": [P, I64, C.c_uint32],
+        "pymc_get_pair_counter": [P, C.POINTER(C.c_uint64)],
+        "pymc_set_pair_counter": [P, C.c_uint64],
         "pymc_rx_setup": [P, P, I, C.c_double, C.c_double],
         "pymc_rx_energies": [P],
         "pymc_rx_buffers": [P, C.POINTER(P), C.POINTER(P)],
@@ -271,6 +276,25 @@ class Lattices:
         nn = np.empty(xs.size, dtype=np.int32)
         check(lib.pymc_propose(self._h, replica, _ptr(xs), _ptr(ys), xs.size, _ptr(site), _ptr(nn)))
         return site, nn
+
+    # -- particle-hole exchange (lattice gas)
+    def set_pair_tables(self, thr):
+        t = np.ascontiguousarray(thr, dtype=np.uint32).reshape(self.ntemps, 7)
+        check(lib.pymc_set_pair_tables(self._h, _ptr(t), t.shape[0], t.shape[1]))
+
+    def pair_sweep(self, nsweeps=1, class_mask=0xFFFF):
+        self._tracked_cache = None
+        check(lib.pymc_pair_sweep(self._h, int(nsweeps), int(class_mask)))
+
+    @property
+    def pair_counter(self):
+        c = C.c_uint64(0)
+        check(lib.pymc_get_pair_counter(self._h, C.byref(c)))
+        return c.value
+
+    @pair_counter.setter
+    def pair_counter(self, v):
+        check(lib.pymc_set_pair_counter(self._h, int(v)))
 
     # -- replica exchange
     def rx_setup(self, betas, c_bond, c_second=0.0):

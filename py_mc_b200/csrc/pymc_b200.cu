@@ -18,6 +18,7 @@
 #include "pmc_rx.cuh"
 #include "pmc_layout.cuh"
 #include "pmc_fused_i8.cuh"
+#include "pmc_pair.cuh"
 
 using namespace pmc;
 
@@ -56,6 +57,7 @@ struct Lat {
     int lenX, lenY, nk, nw;
     int nrep, rep_offset;
     const uint32_t *plans;     // [ntemps][PLAN_WORDS] per-temperature plan rows (pmc_core.cuh)
+    const uint32_t *pair_plans;  // [ntemps][PLAN_WORDS] rows for the pair-exchange kernel (pmc_pair.cuh)
     const int32_t *rep_to_T;   // [nrep_global]
     unsigned long long *tracked;  // [nrep][2]
     PhiloxKey key;
@@ -99,6 +101,19 @@ struct Loader<PYMC_LAYOUT_INT8> {
     static __device__ __forceinline__ int site(const Lat &L, int rep, int colour, int i, int k) {
         return row(L, rep, colour, i)[k] > 0;
     }
+    // flip the occupancy (0 <-> 1) of the lanes in mask / of one site
+    static __device__ __forceinline__ void toggle(const Lat &L, int rep, int colour, int i, int w, uint64_t mask) {
+        int8_t *p = const_cast<int8_t *>(row(L, rep, colour, i)) + 64 * w;
+        while (mask) {
+            const int l = __ffsll((long long)mask) - 1;
+            mask &= mask - 1;
+            p[l] = (int8_t)(1 - p[l]);
+        }
+    }
+    static __device__ __forceinline__ void toggle_site(const Lat &L, int rep, int colour, int i, int k) {
+        int8_t *p = const_cast<int8_t *>(row(L, rep, colour, i)) + k;
+        *p = (int8_t)(1 - *p);
+    }
 };
 
 // one bit per site
@@ -110,7 +125,28 @@ struct Loader<PYMC_LAYOUT_BITS> {
     static __device__ __forceinline__ int site(const Lat &L, int rep, int colour, int i, int k) {
         return (int)((word(L, rep, colour, i, k >> 6) >> (k & 63)) & 1u);
     }
+    // atomic because the carry lane of a horizontal bond class lands in a word another thread also updates
+    static __device__ __forceinline__ void toggle(const Lat &L, int rep, int colour, int i, int w, uint64_t mask) {
+        if (mask) atomicXor((unsigned long long *)(L.bits + ((size_t)(rep * 2 + colour) * L.lenX + i) * L.nw + w), mask);
+    }
+    static __device__ __forceinline__ void toggle_site(const Lat &L, int rep, int colour, int i, int k) {
+        toggle(L, rep, colour, i, k >> 6, 1ull << (k & 63));
+    }
 };
+
+// word of `colour`, row i, whose lane l holds site k+1 (dir = +1) or k-1 (dir = -1) of word w, periodic
+template <int LAYOUT>
+__device__ __forceinline__ uint64_t shifted_word(const Lat &L, int rep, int colour, int i, int w, int nvalid, int dir) {
+    const uint64_t W = Loader<LAYOUT>::word(L, rep, colour, i, w);
+    if (dir > 0) {
+        int knext = 64 * w + nvalid;
+        if (knext >= L.nk) knext = 0;
+        return (W >> 1) | ((uint64_t)Loader<LAYOUT>::site(L, rep, colour, i, knext) << (nvalid - 1));
+    }
+    int kprev = 64 * w - 1;
+    if (kprev < 0) kprev = L.nk - 1;
+    return (W << 1) | (uint64_t)Loader<LAYOUT>::site(L, rep, colour, i, kprev);
+}
 
 // Neighbour words of word (colour, i, w): U, D, C and the two shifted same-row words
 // Lf (site k-1) and Rt (site k+1) of the other colour, periodic in both directions.
@@ -268,6 +304,91 @@ __global__ void __launch_bounds__(128) sweep_bits_rows_kernel(Lat L, int colour,
 }
 
 // ------------------------------------------------------------------------------------------
+// K6: one bond class of the particle-hole exchange sweep (see pmc_pair.cuh).  One thread per word of
+// first sites.  grid = (ceil(rows_in_class * nw / block), nrep)
+// ------------------------------------------------------------------------------------------
+template <int LAYOUT>
+__global__ void __launch_bounds__(128) pair_class_kernel(Lat L, int cls, uint64_t step) {
+    const int rep = blockIdx.y;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool horiz = cls < 8;
+    const int ri = horiz ? cls >> 2 : (cls - 8) >> 1, cj = horiz ? cls & 3 : (cls - 8) & 1;
+    const int rstride = horiz ? 2 : 4;
+    const int nrows = L.lenX / rstride;
+    const bool on = idx < nrows * L.nw;
+    PairPlan plan;
+    plan.init(L.pair_plans + (size_t)L.rep_to_T[L.rep_offset + rep] * PLAN_WORDS);
+    uint64_t S = 0, Bw = 0, A0 = 0, A1 = 0, B0 = 0, B1 = 0, active = 0;
+    int i = 0, w = 0, nvalid = 64, ca = 0, oc = 1, q = 0, i1 = 0;
+    if (on) {
+        const int ridx = idx / L.nw;
+        w = idx - ridx * L.nw;
+        i = ri + rstride * ridx;
+        nvalid = min(64, L.nk - 64 * w);
+        const uint64_t valid = nvalid == 64 ? ~0ull : ((1ull << nvalid) - 1);
+        ca = (i + cj) & 1;
+        oc = ca ^ 1;
+        q = cj & 1;  // column parity of the first site = offset of its colour in this row
+        const int im = i == 0 ? L.lenX - 1 : i - 1, ip = i == L.lenX - 1 ? 0 : i + 1;
+        S = Loader<LAYOUT>::word(L, rep, ca, i, w);
+        if (horiz) {
+            active = valid & (((cj >> 1) & 1) ? 0xAAAAAAAAAAAAAAAAull : 0x5555555555555555ull);
+            const uint64_t Coc = Loader<LAYOUT>::word(L, rep, oc, i, w);
+            const uint64_t Ua = Loader<LAYOUT>::word(L, rep, oc, im, w), Da = Loader<LAYOUT>::word(L, rep, oc, ip, w);
+            uint64_t La, Ub, Db;
+            if (!q) {  // second site at the same k of the other colour; left neighbour of the first at k-1
+                Bw = Coc;
+                La = shifted_word<LAYOUT>(L, rep, oc, i, w, nvalid, -1);
+                Ub = Loader<LAYOUT>::word(L, rep, ca, im, w);
+                Db = Loader<LAYOUT>::word(L, rep, ca, ip, w);
+            } else {  // second site at k+1; left neighbour of the first at k
+                Bw = shifted_word<LAYOUT>(L, rep, oc, i, w, nvalid, +1);
+                La = Coc;
+                Ub = shifted_word<LAYOUT>(L, rep, ca, im, w, nvalid, +1);
+                Db = shifted_word<LAYOUT>(L, rep, ca, ip, w, nvalid, +1);
+            }
+            const uint64_t Rb = shifted_word<LAYOUT>(L, rep, ca, i, w, nvalid, +1);  // (i, j+2)
+            add3(Ua, Da, La, A0, A1);
+            add3(Ub, Db, Rb, B0, B1);
+        } else {
+            active = valid;
+            i1 = ip;
+            const int i2 = i1 == L.lenX - 1 ? 0 : i1 + 1;
+            Bw = Loader<LAYOUT>::word(L, rep, oc, i1, w);
+            const uint64_t Ua = Loader<LAYOUT>::word(L, rep, oc, im, w);
+            const uint64_t Ca = Loader<LAYOUT>::word(L, rep, oc, i, w);
+            const uint64_t Sa = shifted_word<LAYOUT>(L, rep, oc, i, w, nvalid, q ? +1 : -1);
+            const uint64_t Db = Loader<LAYOUT>::word(L, rep, ca, i2, w);
+            const uint64_t Cb = Loader<LAYOUT>::word(L, rep, ca, i1, w);
+            const uint64_t Sb = shifted_word<LAYOUT>(L, rep, ca, i1, w, nvalid, q ? +1 : -1);
+            add3(Ua, Ca, Sa, A0, A1);
+            add3(Db, Cb, Sb, B0, B1);
+        }
+    }
+    int dB = 0;
+    const uint64_t acc = pair_update(S, Bw, A0, A1, B0, B1, active, plan, (uint32_t)(i * L.nw + w),
+                                     (uint32_t)(L.rep_offset + rep), step, L.key, dB);
+    if (on && acc) {
+        Loader<LAYOUT>::toggle(L, rep, ca, i, w, acc);
+        if (!horiz) {
+            Loader<LAYOUT>::toggle(L, rep, oc, i1, w, acc);
+        } else if (!q) {
+            Loader<LAYOUT>::toggle(L, rep, oc, i, w, acc);
+        } else {
+            const uint64_t top = 1ull << (nvalid - 1);
+            const uint64_t valid = nvalid == 64 ? ~0ull : ((1ull << nvalid) - 1);
+            Loader<LAYOUT>::toggle(L, rep, oc, i, w, (acc << 1) & valid);
+            if (acc & top) {
+                int knext = 64 * w + nvalid;
+                if (knext >= L.nk) knext = 0;
+                Loader<LAYOUT>::toggle_site(L, rep, oc, i, knext);
+            }
+        }
+    }
+    block_accumulate(on ? dB : 0, 0, L.tracked + 2 * (size_t)rep);
+}
+
+// ------------------------------------------------------------------------------------------
 // K3: exact integer observables per replica (bond sum and magnetisation / particle number).
 // Each word of either colour contributes its bonds to the row above and to the site on its left.
 // grid = (ceil(2*lenX*nw / block), nrep)
@@ -397,6 +518,8 @@ struct pymc_handle {
     int8_t *i8_alt;                // second int8 buffer for the out-of-place fused sweep (allocated on first use)
     uint64_t *bits;
     uint32_t *plans;               // [ntemps][PLAN_WORDS]
+    uint32_t *pair_plans;          // [ntemps][PLAN_WORDS], allocated by pymc_set_pair_tables
+    uint64_t pair_counter;         // pair-exchange sweeps done (random-stream position)
     int32_t *rep_to_T;
     unsigned long long *tracked;   // [nrep][2]
     unsigned long long *reduced;   // [nrep][2] output of reduce_kernel
@@ -427,6 +550,7 @@ static Lat make_lat(const pymc_handle *h) {
     L.nrep = h->p.nreplicas;
     L.rep_offset = h->p.replica_offset;
     L.plans = h->plans;
+    L.pair_plans = h->pair_plans;
     L.rep_to_T = h->rep_to_T;
     L.tracked = h->tracked;
     L.key = make_key(h->p.seed);
@@ -485,6 +609,7 @@ int pymc_destroy(pymc_handle *h) {
         cudaFree(h->i8_alt);
         cudaFree(h->bits);
         cudaFree(h->plans);
+        cudaFree(h->pair_plans);
         cudaFree(h->rep_to_T);
         cudaFree(h->tracked);
         cudaFree(h->reduced);
@@ -1055,6 +1180,79 @@ int pymc_rx_get_round(pymc_handle *h, uint64_t *round) {
 int pymc_rx_set_round(pymc_handle *h, uint64_t round) {
     REQUIRE(h, PYMC_ERR_BADARG, "pymc_rx_set_round: null handle");
     h->rx_round = round;
+    return PYMC_OK;
+}
+
+
+// ------------------------------------------------------------------------------------------
+// particle-hole exchange (lattice gas)
+// ------------------------------------------------------------------------------------------
+int pymc_set_pair_tables(pymc_handle *h, const uint32_t *thr, int ntemps, int nclass) {
+    ENTER(h);
+    REQUIRE(thr, PYMC_ERR_BADARG, "pymc_set_pair_tables: null pointer");
+    REQUIRE(h->p.model == PYMC_MODEL_LATGAS, PYMC_ERR_UNSUPPORTED, "pymc_set_pair_tables: lattice-gas handles only");
+    REQUIRE(ntemps == h->p.ntemps && nclass == PAIR_NCLASS, PYMC_ERR_BADARG,
+            "pymc_set_pair_tables: got %d x %d, handle expects %d x %d", ntemps, nclass, h->p.ntemps, PAIR_NCLASS);
+    REQUIRE(h->p.lenX % 4 == 0 && h->p.lenY % 4 == 0, PYMC_ERR_UNSUPPORTED,
+            "pymc_set_pair_tables: the bond-class schedule needs lenX %% 4 == 0 and lenY %% 4 == 0 (got %dx%d)",
+            h->p.lenX, h->p.lenY);
+    uint32_t *rows = new (std::nothrow) uint32_t[(size_t)ntemps * PLAN_WORDS];
+    REQUIRE(rows, PYMC_ERR_BADARG, "pymc_set_pair_tables: out of host memory");
+    for (int t = 0; t < ntemps; ++t) {
+        if (!PairPlan::build_row(thr + (size_t)t * nclass, rows + (size_t)t * PLAN_WORDS)) {
+            delete[] rows;
+            return fail(PYMC_ERR_UNSUPPORTED,
+                        "pymc_set_pair_tables: row %d is not a pair-exchange table (dE > 0 on both sides or at d = 0)", t);
+        }
+    }
+    cudaError_t e = cudaSuccess;
+    if (!h->pair_plans) e = cudaMalloc(&h->pair_plans, (size_t)ntemps * PLAN_WORDS * 4);
+    if (e == cudaSuccess)
+        e = cudaMemcpyAsync(h->pair_plans, rows, (size_t)ntemps * PLAN_WORDS * 4, cudaMemcpyHostToDevice, h->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    delete[] rows;
+    if (e != cudaSuccess) return fail(PYMC_ERR_CUDA, "pymc_set_pair_tables: %s", cudaGetErrorString(e));
+    return PYMC_OK;
+}
+
+int pymc_pair_sweep(pymc_handle *h, int64_t nsweeps, uint32_t class_mask) {
+    ENTER(h);
+    REQUIRE(nsweeps >= 0, PYMC_ERR_BADARG, "pymc_pair_sweep: nsweeps %lld", (long long)nsweeps);
+    REQUIRE(h->pair_plans, PYMC_ERR_STATE, "pymc_pair_sweep: call pymc_set_pair_tables first");
+    REQUIRE((class_mask & 0xFFFFu) != 0 && (class_mask >> 16) == 0, PYMC_ERR_BADARG, "pymc_pair_sweep: class mask %#x",
+            class_mask);
+    if (h->dirty) {
+        int rc = rebase_tracked(h);
+        if (rc) return rc;
+    }
+    Lat L = make_lat(h);
+    for (int64_t s = 0; s < nsweeps; ++s) {
+        for (int c = 0; c < 16; ++c) {
+            if (!((class_mask >> c) & 1u)) continue;
+            const int nrows = h->p.lenX / (c < 8 ? 2 : 4);
+            dim3 grid((nrows * h->nw + 127) / 128, h->p.nreplicas);
+            const uint64_t step = 16 * h->pair_counter + c;
+            if (h->p.layout == PYMC_LAYOUT_BITS)
+                pair_class_kernel<PYMC_LAYOUT_BITS><<<grid, 128, 0, h->stream>>>(L, c, step);
+            else
+                pair_class_kernel<PYMC_LAYOUT_INT8><<<grid, 128, 0, h->stream>>>(L, c, step);
+        }
+        h->pair_counter++;
+    }
+    CUDA_TRY(cudaGetLastError());
+    return PYMC_OK;
+}
+
+int pymc_get_pair_counter(pymc_handle *h, uint64_t *counter) {
+    REQUIRE(h && counter, PYMC_ERR_BADARG, "pymc_get_pair_counter: null pointer");
+    *counter = h->pair_counter;
+    return PYMC_OK;
+}
+
+int pymc_set_pair_counter(pymc_handle *h, uint64_t counter) {
+    REQUIRE(h, PYMC_ERR_BADARG, "pymc_set_pair_counter: null handle");
+    REQUIRE(counter < (1ull << 51), PYMC_ERR_BADARG, "pymc_set_pair_counter: counter too large");
+    h->pair_counter = counter;
     return PYMC_OK;
 }
 
