@@ -186,14 +186,18 @@ class CanonicalMonteCarlo:
         key = (self.kT, self.model._pmc_table_key())
         if lat is not self._lat or self._table_kT != key:
             lat.set_accept_tables(self.model._pmc_thresholds(self.kT)[None, :])
+            if getattr(self.model, "_pmc_pair_moves", False):
+                lat.set_pair_tables(self.model._pmc_pair_thresholds(self.kT)[None, :])
             self._lat = lat
             self._table_kT = key
         return lat
 
     @property
     def attempts_per_step(self):
-        """Single-site Metropolis trials performed by one ``MCstep`` (= one sweep)."""
-        return self.config.lenX * self.config.lenY
+        """Metropolis trials performed by one ``MCstep``: one sweep of single-site moves, plus as
+        many particle-hole exchange attempts for models with particle moves (latgas_move)."""
+        n = self.config.lenX * self.config.lenY
+        return 2 * n if getattr(self.model, "_pmc_pair_moves", False) else n
 
     @property
     def energy(self):
@@ -216,7 +220,12 @@ class CanonicalMonteCarlo:
 
     def _sweeps(self, n):
         lat = self._device()
-        lat.sweep(n)
+        if getattr(self.model, "_pmc_pair_moves", False):
+            for _ in range(n):  # flip sweep, then half of the bond classes (horizontal / vertical in turn)
+                lat.sweep(1)
+                lat.pair_sweep(1, 0x00FF if lat.pair_counter % 2 == 0 else 0xFF00)
+        else:
+            lat.sweep(n)
         self.config._device_changed()
         self._energy = None
 

@@ -40,3 +40,8 @@ def golden_rx():
 @pytest.fixture(scope="session")
 def golden_latgas():
     return load_golden("latgas")
+
+
+@pytest.fixture(scope="session")
+def golden_latgas_move():
+    return load_golden("latgas_move")

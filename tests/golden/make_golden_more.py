@@ -203,4 +203,80 @@ def gen_latgas(out):
     out["meta"] = np.array(json.dumps(meta))
 
 
-MORE = {"rx": gen_rx, "latgas": gen_latgas}
+class MoveInjector:
+    """random-module stand-in for latgas_move.trialstep: scripted random(), randrange(), choice()."""
+
+    def __init__(self):
+        self.script = []
+
+    def random(self):
+        kind, v = self.script.pop(0)
+        assert kind == "random"
+        return v
+
+    def randrange(self, n):
+        kind, v = self.script.pop(0)
+        assert kind == "randrange" and 0 <= v < n
+        return v
+
+    def choice(self, seq):
+        kind, v = self.script.pop(0)
+        assert kind == "choice"
+        return seq[v % len(seq)]
+
+
+def gen_latgas_move(out):
+    """dconfig / dE of examples/latgas_move.py trialstep (flip and move branches) on fixed
+    configurations with scripted draws -- including the defective move dE -- and newconfig."""
+    ref_root = os.environ.get("PYMC_REFERENCE", "/root/reference")
+    sys.path.insert(0, ref_root)
+    sys.path.insert(0, os.path.join(ref_root, "examples"))
+    import latgas_move as ref_move
+    from oracle import latgas as o_latgas
+    inj = MoveInjector()
+    ref_move.rand = inj
+    rng = np.random.default_rng(2718)
+    meta = []
+    for n, (lenX, lenY, J, Eads, mu, seed) in enumerate([(5, 5, -0.25, -0.4, -0.1, 21), (6, 8, 1.0, 0.5, 0.25, 22),
+                                                         (4, 4, 0.0, -0.4, 0.3, 23)]):
+        name = "mv%d" % n
+        cfg = ref_move.latgas_config(lenX, lenY)
+        init = (rng.random((lenX, lenY)) >= 0.5).astype(np.int8) if lenX % 2 else o_latgas.init_config(seed, 0, lenX, lenY)
+        cfg.config[:, :] = init
+        model = ref_move.latticegas(Eads=Eads, J=J, mu=mu)
+        scripts, dconfigs, dEs = [], [], []
+        nocc, nemp = int(init.sum()), int((1 - init).sum())
+        trials = []
+        for t in range(60):
+            if t % 3 == 0:
+                trials.append([("random", 0.25), ("randrange", int(rng.integers(lenX))), ("randrange", int(rng.integers(lenY)))])
+            else:
+                trials.append([("random", 0.75), ("choice", int(rng.integers(nocc))), ("choice", int(rng.integers(nemp)))])
+        # make sure the quirky branches are hit: empty site in the last row / last column
+        emp = np.transpose(np.where(init == 0))
+        for idx, (x, y) in enumerate(emp):
+            if x == lenX - 1 or y == lenY - 1:
+                trials.append([("random", 0.9), ("choice", 0), ("choice", idx)])
+        for tr in trials:
+            inj.script = list(tr)
+            dconfig, dE = model.trialstep(cfg, 0.0)
+            assert not inj.script
+            scripts.append([[k, float(v)] for k, v in tr])
+            dconfigs.append([int(v) for v in dconfig] + [-1] * (4 - len(dconfig)))
+            dEs.append(float(dE))
+        assert np.array_equal(cfg.config, init)
+        after = ref_move.latgas_config(lenX, lenY)
+        after.config[:, :] = init
+        mv = next(d for d in dconfigs if d[2] >= 0)
+        model.newconfig(after, mv)
+        out[name + "_init"] = init
+        out[name + "_dconfig"] = np.array(dconfigs, dtype=np.int64)
+        out[name + "_dE"] = np.array(dEs, dtype=np.float64)
+        out[name + "_after_move"] = after.config.astype(np.int8)
+        out[name + "_move"] = np.array(mv, dtype=np.int64)
+        meta.append(dict(name=name, lenX=lenX, lenY=lenY, J=J, Eads=Eads, mu=mu, scripts=scripts))
+        print("latgas_move", name, "trials", len(trials), "moves", sum(1 for d in dconfigs if d[2] >= 0))
+    out["meta"] = np.array(json.dumps(meta))
+
+
+MORE = {"rx": gen_rx, "latgas": gen_latgas, "latgas_move": gen_latgas_move}
