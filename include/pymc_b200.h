@@ -165,6 +165,31 @@ int pymc_pair_sweep(pymc_handle *h, int64_t nsweeps, uint32_t class_mask);
 int pymc_get_pair_counter(pymc_handle *h, uint64_t *counter);
 int pymc_set_pair_counter(pymc_handle *h, uint64_t counter);
 
+/* ---- hard discs -----------------------------------------------------------------------
+ * Batched replicas of the continuum hard-disc model of examples/2D_hardcore/model_setup.py.
+ * pymc_discs_run      ntrials single-disc trials per replica = that many MCstep() calls
+ *                     (py_mc/mc.py:170-185) on HC_2D.trialstep / newconfig (model_setup.py:40-67);
+ *                     isotropic = 0 reproduces the reference's diagonal displacement (:48).
+ * pymc_discs_propose  the (id, new coordinates, overlap) the next trial of one replica would
+ *                     propose, without applying it: the content of trialstep's (dconfig, dE).
+ * pymc_discs_observe  overlap[r] = 1 iff HC_2D.energy would return inf (model_setup.py:24-37);
+ *                     counts[r][b] = 2 * number of pairs with around(dist/dr) == b+1, the integer part
+ *                     of g_r (model_setup.py:116-122); the prefactor is applied by the caller.
+ * coors are float64 [ndisc][2]; at most 32 discs per replica (the shipped script uses 20). */
+typedef struct pymc_discs pymc_discs;
+int pymc_discs_create(int device, int nreplicas, int replica_offset, int ndisc, double Lcell, double rdisc,
+                      double maxstep, uint64_t seed, int isotropic, pymc_discs **out);
+int pymc_discs_destroy(pymc_discs *d);
+int pymc_discs_upload(pymc_discs *d, int replica, const double *coors);
+int pymc_discs_download(pymc_discs *d, int replica, double *coors);
+int pymc_discs_run(pymc_discs *d, int64_t ntrials);
+int pymc_discs_propose(pymc_discs *d, int replica, int *id, double *newcoor, int *overlap);
+int pymc_discs_observe(pymc_discs *d, double dr, int nbins, int32_t *overlap, int64_t *counts);
+int pymc_discs_counters(pymc_discs *d, uint64_t *trial_counter, uint64_t *accepted);
+int pymc_discs_set_trial_counter(pymc_discs *d, uint64_t counter);
+/* runs ntrials like pymc_discs_run and returns the device time of that launch (CUDA events) */
+int pymc_discs_timer(pymc_discs *d, int64_t ntrials, float *elapsed_ms);
+
 /* ---- replica exchange -----------------------------------------------------------------
  * Replaces TemperatureRX_MPI (py_mc/mc_mpi.py:75-209).  Needs ntemps == nreplicas_global
  * (the reference's own requirement, mc_mpi.py:47-52).

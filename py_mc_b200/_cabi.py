@@ -27,6 +27,9 @@ SYMBOLS = [
     "pymc_rx_get_energies", "pymc_rx_get_stats", "pymc_rx_get_round", "pymc_rx_set_round",
     "pymc_host_alloc", "pymc_host_free", "pymc_reduce_observables_static", "pymc_sweep_kernel_info",
     "pymc_set_pair_tables", "pymc_pair_sweep", "pymc_get_pair_counter", "pymc_set_pair_counter",
+    "pymc_discs_create", "pymc_discs_destroy", "pymc_discs_upload", "pymc_discs_download", "pymc_discs_run",
+    "pymc_discs_propose", "pymc_discs_observe", "pymc_discs_counters", "pymc_discs_set_trial_counter",
+    "pymc_discs_timer",
 ]
 
 
@@ -81,6 +84,16 @@ def _load():
         "pymc_pair_sweep": [P, I64, C.c_uint32],
         "pymc_get_pair_counter": [P, C.POINTER(C.c_uint64)],
         "pymc_set_pair_counter": [P, C.c_uint64],
+        "pymc_discs_create": [I, I, I, I, C.c_double, C.c_double, C.c_double, C.c_uint64, I, C.POINTER(P)],
+        "pymc_discs_destroy": [P],
+        "pymc_discs_upload": [P, I, P],
+        "pymc_discs_download": [P, I, P],
+        "pymc_discs_run": [P, I64],
+        "pymc_discs_propose": [P, I, C.POINTER(I), P, C.POINTER(I)],
+        "pymc_discs_observe": [P, C.c_double, I, P, P],
+        "pymc_discs_counters": [P, C.POINTER(C.c_uint64), P],
+        "pymc_discs_set_trial_counter": [P, C.c_uint64],
+        "pymc_discs_timer": [P, I64, C.POINTER(C.c_float)],
         "pymc_rx_setup": [P, P, I, C.c_double, C.c_double],
         "pymc_rx_energies": [P],
         "pymc_rx_buffers": [P, C.POINTER(P), C.POINTER(P)],
@@ -346,3 +359,65 @@ class Lattices:
         ms = C.c_float(0)
         check(lib.pymc_timer_stop(self._h, C.byref(ms)))
         return ms.value
+
+
+class Discs:
+    """A batch of hard-disc replicas on one GPU (owner of a pymc_discs handle)."""
+
+    def __init__(self, nreplicas, ndisc, Lcell, rdisc, maxstep, seed=0, isotropic=False, device=0, replica_offset=0):
+        self._h = C.c_void_p()
+        self.nreplicas, self.ndisc = int(nreplicas), int(ndisc)
+        check(lib.pymc_discs_create(int(device), self.nreplicas, int(replica_offset), self.ndisc, float(Lcell),
+                                    float(rdisc), float(maxstep), int(seed) & 0xFFFFFFFFFFFFFFFF,
+                                    1 if isotropic else 0, C.byref(self._h)))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            lib.pymc_discs_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def upload(self, replica, coors):
+        a = np.ascontiguousarray(coors, dtype=np.float64)
+        if a.shape != (self.ndisc, 2):
+            raise ValueError("coors shape %s, expected (%d, 2)" % (a.shape, self.ndisc))
+        check(lib.pymc_discs_upload(self._h, replica, _ptr(a)))
+
+    def download(self, replica):
+        a = np.empty((self.ndisc, 2), dtype=np.float64)
+        check(lib.pymc_discs_download(self._h, replica, _ptr(a)))
+        return a
+
+    def run(self, ntrials):
+        check(lib.pymc_discs_run(self._h, int(ntrials)))
+
+    def timed_run(self, ntrials):
+        ms = C.c_float(0)
+        check(lib.pymc_discs_timer(self._h, int(ntrials), C.byref(ms)))
+        return ms.value
+
+    def propose(self, replica):
+        i, ov = C.c_int(0), C.c_int(0)
+        new = np.empty(2, dtype=np.float64)
+        check(lib.pymc_discs_propose(self._h, replica, C.byref(i), _ptr(new), C.byref(ov)))
+        return i.value, new, bool(ov.value)
+
+    def observe(self, dr=0.0, nbins=0):
+        ov = np.empty(self.nreplicas, dtype=np.int32)
+        counts = np.zeros((self.nreplicas, max(nbins, 0)), dtype=np.int64)
+        check(lib.pymc_discs_observe(self._h, float(dr), int(nbins), _ptr(ov), _ptr(counts) if nbins else None))
+        return ov.astype(bool), counts
+
+    def counters(self):
+        t = C.c_uint64(0)
+        acc = np.empty(self.nreplicas, dtype=np.uint64)
+        check(lib.pymc_discs_counters(self._h, C.byref(t), _ptr(acc)))
+        return t.value, acc
+
+    def set_trial_counter(self, v):
+        check(lib.pymc_discs_set_trial_counter(self._h, int(v)))

@@ -19,6 +19,7 @@
 #include "pmc_layout.cuh"
 #include "pmc_fused_i8.cuh"
 #include "pmc_pair.cuh"
+#include "pmc_discs.cuh"
 
 using namespace pmc;
 
@@ -1254,6 +1255,183 @@ int pymc_set_pair_counter(pymc_handle *h, uint64_t counter) {
     REQUIRE(counter < (1ull << 51), PYMC_ERR_BADARG, "pymc_set_pair_counter: counter too large");
     h->pair_counter = counter;
     return PYMC_OK;
+}
+
+
+// ------------------------------------------------------------------------------------------
+// hard discs (examples/2D_hardcore)
+// ------------------------------------------------------------------------------------------
+struct pymc_discs {
+    int device;
+    cudaStream_t stream;
+    DiscParams P;
+    int *d_overlap;        // [nrep]
+    long long *d_counts;   // [nrep][cap_bins]
+    int cap_bins;
+    int *d_probe_i;        // id, overlap
+    double *d_probe_d;     // new x, y
+    uint64_t trial_counter;
+};
+
+#define ENTER_D(d)                                                        \
+    REQUIRE((d) != nullptr, PYMC_ERR_BADARG, "%s: null handle", __func__); \
+    DeviceGuard _guard((d)->device);                                      \
+    REQUIRE(_guard.ok, PYMC_ERR_CUDA, "%s: cannot select device %d", __func__, (d)->device)
+
+int pymc_discs_destroy(pymc_discs *d) {
+    if (!d) return PYMC_OK;
+    DeviceGuard guard(d->device);
+    if (guard.ok) {
+        if (d->stream) cudaStreamSynchronize(d->stream);
+        cudaFree(d->P.coors);
+        cudaFree(d->P.accepted);
+        cudaFree(d->d_overlap);
+        cudaFree(d->d_counts);
+        cudaFree(d->d_probe_i);
+        cudaFree(d->d_probe_d);
+        if (d->stream) cudaStreamDestroy(d->stream);
+    }
+    delete d;
+    return PYMC_OK;
+}
+
+int pymc_discs_create(int device, int nreplicas, int replica_offset, int ndisc, double Lcell, double rdisc,
+                      double maxstep, uint64_t seed, int isotropic, pymc_discs **out) {
+    REQUIRE(out, PYMC_ERR_BADARG, "pymc_discs_create: null pointer");
+    *out = nullptr;
+    REQUIRE(nreplicas >= 1 && replica_offset >= 0, PYMC_ERR_BADARG, "pymc_discs_create: nreplicas %d offset %d",
+            nreplicas, replica_offset);
+    REQUIRE(ndisc >= 1 && ndisc <= 32, PYMC_ERR_UNSUPPORTED,
+            "pymc_discs_create: 1..32 discs per replica are supported (one disc per warp lane), got %d", ndisc);
+    REQUIRE(Lcell > 0.0 && rdisc > 0.0, PYMC_ERR_BADARG, "pymc_discs_create: Lcell and rdisc must be positive");
+    int ndev = 0;
+    CUDA_TRY(cudaGetDeviceCount(&ndev));
+    REQUIRE(device >= 0 && device < ndev, PYMC_ERR_BADARG, "pymc_discs_create: device %d of %d", device, ndev);
+    pymc_discs *d = new (std::nothrow) pymc_discs();
+    REQUIRE(d, PYMC_ERR_BADARG, "pymc_discs_create: out of host memory");
+    memset(d, 0, sizeof(*d));
+    d->device = device;
+    d->P.nrep = nreplicas;
+    d->P.ndisc = ndisc;
+    d->P.Lcell = Lcell;
+    d->P.two_r = rdisc * 2;
+    d->P.maxstep = maxstep;
+    d->P.isotropic = isotropic ? 1 : 0;
+    d->P.key = make_key(seed);
+    d->P.replica_offset = replica_offset;
+    DeviceGuard guard(device);
+    cudaError_t e = guard.ok ? cudaSuccess : cudaErrorInvalidDevice;
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaMalloc(&d->P.coors, (size_t)nreplicas * ndisc * 16);
+    if (e == cudaSuccess) e = cudaMalloc(&d->P.accepted, (size_t)nreplicas * 8);
+    if (e == cudaSuccess) e = cudaMalloc(&d->d_overlap, (size_t)nreplicas * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&d->d_probe_i, 8);
+    if (e == cudaSuccess) e = cudaMalloc(&d->d_probe_d, 16);
+    if (e == cudaSuccess) e = cudaMemsetAsync(d->P.coors, 0, (size_t)nreplicas * ndisc * 16, d->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(d->P.accepted, 0, (size_t)nreplicas * 8, d->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(d->stream);
+    if (e != cudaSuccess) {
+        pymc_discs_destroy(d);
+        return fail(PYMC_ERR_CUDA, "pymc_discs_create: %s", cudaGetErrorString(e));
+    }
+    *out = d;
+    return PYMC_OK;
+}
+
+int pymc_discs_upload(pymc_discs *d, int replica, const double *coors) {
+    ENTER_D(d);
+    REQUIRE(coors && replica >= 0 && replica < d->P.nrep, PYMC_ERR_BADARG, "pymc_discs_upload: bad arguments");
+    CUDA_TRY(cudaMemcpyAsync(d->P.coors + (size_t)replica * d->P.ndisc * 2, coors, (size_t)d->P.ndisc * 16,
+                             cudaMemcpyHostToDevice, d->stream));
+    CUDA_TRY(cudaStreamSynchronize(d->stream));
+    return PYMC_OK;
+}
+
+int pymc_discs_download(pymc_discs *d, int replica, double *coors) {
+    ENTER_D(d);
+    REQUIRE(coors && replica >= 0 && replica < d->P.nrep, PYMC_ERR_BADARG, "pymc_discs_download: bad arguments");
+    CUDA_TRY(cudaMemcpyAsync(coors, d->P.coors + (size_t)replica * d->P.ndisc * 2, (size_t)d->P.ndisc * 16,
+                             cudaMemcpyDeviceToHost, d->stream));
+    CUDA_TRY(cudaStreamSynchronize(d->stream));
+    return PYMC_OK;
+}
+
+int pymc_discs_run(pymc_discs *d, int64_t ntrials) {
+    ENTER_D(d);
+    REQUIRE(ntrials >= 0, PYMC_ERR_BADARG, "pymc_discs_run: ntrials %lld", (long long)ntrials);
+    if (ntrials == 0) return PYMC_OK;
+    discs_run_kernel<<<(d->P.nrep + 3) / 4, 128, 0, d->stream>>>(d->P, d->trial_counter, (long long)ntrials);
+    CUDA_TRY(cudaGetLastError());
+    d->trial_counter += (uint64_t)ntrials;
+    return PYMC_OK;
+}
+
+int pymc_discs_propose(pymc_discs *d, int replica, int *id, double *newcoor, int *overlap) {
+    ENTER_D(d);
+    REQUIRE(id && newcoor && overlap && replica >= 0 && replica < d->P.nrep, PYMC_ERR_BADARG,
+            "pymc_discs_propose: bad arguments");
+    discs_propose_kernel<<<1, 32, 0, d->stream>>>(d->P, replica, d->trial_counter, d->d_probe_i, d->d_probe_d,
+                                                  d->d_probe_i + 1);
+    CUDA_TRY(cudaGetLastError());
+    int hi[2];
+    CUDA_TRY(cudaMemcpyAsync(hi, d->d_probe_i, 8, cudaMemcpyDeviceToHost, d->stream));
+    CUDA_TRY(cudaMemcpyAsync(newcoor, d->d_probe_d, 16, cudaMemcpyDeviceToHost, d->stream));
+    CUDA_TRY(cudaStreamSynchronize(d->stream));
+    *id = hi[0];
+    *overlap = hi[1];
+    return PYMC_OK;
+}
+
+int pymc_discs_observe(pymc_discs *d, double dr, int nbins, int32_t *overlap, int64_t *counts) {
+    ENTER_D(d);
+    REQUIRE(nbins >= 0 && (nbins == 0 || (dr > 0.0 && counts)), PYMC_ERR_BADARG, "pymc_discs_observe: bad histogram");
+    if (nbins > d->cap_bins) {
+        cudaFree(d->d_counts);
+        d->d_counts = nullptr;
+        d->cap_bins = 0;
+        CUDA_TRY(cudaMalloc(&d->d_counts, (size_t)d->P.nrep * nbins * 8));
+        d->cap_bins = nbins;
+    }
+    if (nbins) CUDA_TRY(cudaMemsetAsync(d->d_counts, 0, (size_t)d->P.nrep * nbins * 8, d->stream));
+    discs_observe_kernel<<<(d->P.nrep + 3) / 4, 128, 0, d->stream>>>(d->P, dr, nbins, d->d_overlap,
+                                                                     nbins ? d->d_counts : nullptr);
+    CUDA_TRY(cudaGetLastError());
+    if (overlap) CUDA_TRY(cudaMemcpyAsync(overlap, d->d_overlap, (size_t)d->P.nrep * 4, cudaMemcpyDeviceToHost, d->stream));
+    if (nbins) CUDA_TRY(cudaMemcpyAsync(counts, d->d_counts, (size_t)d->P.nrep * nbins * 8, cudaMemcpyDeviceToHost, d->stream));
+    CUDA_TRY(cudaStreamSynchronize(d->stream));
+    return PYMC_OK;
+}
+
+int pymc_discs_counters(pymc_discs *d, uint64_t *trial_counter, uint64_t *accepted) {
+    ENTER_D(d);
+    if (trial_counter) *trial_counter = d->trial_counter;
+    if (accepted) {
+        CUDA_TRY(cudaMemcpyAsync(accepted, d->P.accepted, (size_t)d->P.nrep * 8, cudaMemcpyDeviceToHost, d->stream));
+        CUDA_TRY(cudaStreamSynchronize(d->stream));
+    }
+    return PYMC_OK;
+}
+
+int pymc_discs_set_trial_counter(pymc_discs *d, uint64_t counter) {
+    REQUIRE(d, PYMC_ERR_BADARG, "pymc_discs_set_trial_counter: null handle");
+    d->trial_counter = counter;
+    return PYMC_OK;
+}
+
+int pymc_discs_timer(pymc_discs *d, int64_t ntrials, float *elapsed_ms) {
+    ENTER_D(d);
+    REQUIRE(elapsed_ms, PYMC_ERR_BADARG, "pymc_discs_timer: null pointer");
+    cudaEvent_t e0, e1;
+    CUDA_TRY(cudaEventCreate(&e0));
+    CUDA_TRY(cudaEventCreate(&e1));
+    CUDA_TRY(cudaEventRecord(e0, d->stream));
+    int rc = pymc_discs_run(d, ntrials);
+    cudaEventRecord(e1, d->stream);
+    cudaEventSynchronize(e1);
+    cudaEventElapsedTime(elapsed_ms, e0, e1);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    return rc;
 }
 
 int pymc_host_alloc(size_t bytes, void **out) {

@@ -174,7 +174,12 @@ class CanonicalMonteCarlo:
         self._energy = None
 
     # -- device plumbing ---------------------------------------------------------------
+    def _is_discs(self):
+        return getattr(self.model, "_pmc_kind", None) == "discs" and hasattr(self.config, "_attach")
+
     def _device(self):
+        if self._is_discs():
+            return self.config._attach(self.model)
         code = getattr(self.model, "_pmc_model", None)
         if code is None or not hasattr(self.config, "_attach"):
             raise TypeError(
@@ -195,12 +200,17 @@ class CanonicalMonteCarlo:
     @property
     def attempts_per_step(self):
         """Metropolis trials performed by one ``MCstep``: one sweep of single-site moves, plus as
-        many particle-hole exchange attempts for models with particle moves (latgas_move)."""
+        many particle-hole exchange attempts for models with particle moves (latgas_move); one
+        single-disc trial for the hard-disc model."""
+        if self._is_discs():
+            return 1
         n = self.config.lenX * self.config.lenY
         return 2 * n if getattr(self.model, "_pmc_pair_moves", False) else n
 
     @property
     def energy(self):
+        if self._energy is None and self._is_discs():
+            self._energy = self.model.energy(self.config)
         if self._energy is None:
             obs = self.config._device_observables()
             if obs is None:  # the host copy is the newest (someone took a writable view): recompute
@@ -220,6 +230,10 @@ class CanonicalMonteCarlo:
 
     def _sweeps(self, n):
         lat = self._device()
+        if self._is_discs():  # n single-disc trials in one launch; a valid state keeps E = 0
+            lat.run(n)
+            self.config._device_changed()
+            return
         if getattr(self.model, "_pmc_pair_moves", False):
             for _ in range(n):  # flip sweep, then half of the bond classes (horizontal / vertical in turn)
                 lat.sweep(1)
@@ -238,8 +252,11 @@ class CanonicalMonteCarlo:
         observables = 0.0
         nsample = 0
         lat = self._device()
-        lat.reduce_observables()  # model.energy(config) at the top of run (mc.py:191)
-        self._energy = None
+        if self._is_discs():
+            self._energy = self.model.energy(self.config)
+        else:
+            lat.reduce_observables()  # model.energy(config) at the top of run (mc.py:191)
+            self._energy = None
         output = open("obs.dat", "a")
         try:
             with open(os.devnull, "w") as devnull:

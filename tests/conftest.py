@@ -45,3 +45,8 @@ def golden_latgas():
 @pytest.fixture(scope="session")
 def golden_latgas_move():
     return load_golden("latgas_move")
+
+
+@pytest.fixture(scope="session")
+def golden_discs():
+    return load_golden("discs")

@@ -279,4 +279,80 @@ def gen_latgas_move(out):
     out["meta"] = np.array(json.dumps(meta))
 
 
-MORE = {"rx": gen_rx, "latgas": gen_latgas, "latgas_move": gen_latgas_move}
+DISC_CASES = [
+    dict(name="hd_shipped", L=1.0, rdisc=1.0 / 14.0, ndisc=20, maxstep=1.0 / 28.0, seed=88, replica=0, ntrials=3000,
+         dr=0.01),
+    dict(name="hd_dense", L=2.0, rdisc=0.21, ndisc=16, maxstep=0.25, seed=89, replica=5, ntrials=2000, dr=0.05),
+]
+
+
+def gen_discs(out):
+    """examples/2D_hardcore: HC_2D trialstep/newconfig under CanonicalMonteCarlo.MCstep, energy, g_r."""
+    import types
+    ref_root = os.environ.get("PYMC_REFERENCE", "/root/reference")
+    sys.path.insert(0, os.path.join(ref_root, "py_mc"))                 # "from mc import model" (model_setup.py:10)
+    sys.path.insert(0, os.path.join(ref_root, "examples", "2D_hardcore"))
+    stub = types.ModuleType("matplotlib")                                # matplotlib is absent; only plot_fig uses it
+    stub.pyplot = types.ModuleType("matplotlib.pyplot")
+    sys.modules.setdefault("matplotlib", stub)
+    sys.modules.setdefault("matplotlib.pyplot", stub.pyplot)
+    import mc as refmc_flat
+    import model_setup as ref_hc
+    from oracle import harddisc as o_hd
+
+    state = {}
+
+    class NPProxy:
+        """numpy with random.randint replaced (model_setup.py:45 draws the disc from numpy's global RNG)."""
+
+        class random:
+            @staticmethod
+            def randint(n):
+                return state["id"]
+
+        def __getattr__(self, k):
+            return getattr(np, k)
+
+    class RandProxy:
+        @staticmethod
+        def uniform(a, b):
+            return a + (b - a) * state["u"]
+
+    ref_hc.np = NPProxy()
+    ref_hc.rand = RandProxy()
+    refmc_flat.random = lambda: state["x32"] * (1.0 / 4294967296.0)
+    meta = []
+    for case in DISC_CASES:
+        n = case["name"]
+        cfg = ref_hc.HC_2D_config(case["L"], case["ndisc"], case["rdisc"])
+        cfg.prepare_ordered()
+        start = cfg.coors.copy()
+        model = ref_hc.HC_2D(case["maxstep"])
+        grid = refmc_flat.grid_1D(case["dr"], case["dr"], case["L"] / 2.0)
+        calc = refmc_flat.CanonicalMonteCarlo(model, 1, cfg, grid=grid)
+        calc.energy = model.energy(cfg)
+        e0 = calc.energy
+        g0 = ref_hc.g_r(cfg, grid)
+        snaps, nacc, ids = [], 0, []
+        for t in range(case["ntrials"]):
+            state["id"], state["u"], state["x32"] = o_hd.trial_draws(case["seed"], case["replica"], t, case["ndisc"])
+            before = cfg.coors.copy()
+            calc.MCstep()
+            nacc += int(not np.array_equal(before, cfg.coors))
+            ids.append(state["id"])
+            if (t + 1) % 500 == 0:
+                snaps.append(cfg.coors.copy())
+        out[n + "_start"] = start
+        out[n + "_snaps"] = np.array(snaps)
+        out[n + "_g0"] = g0
+        out[n + "_g_end"] = ref_hc.g_r(cfg, grid)
+        out[n + "_gridx"] = grid.x
+        out[n + "_ids"] = np.array(ids[:50])
+        c = dict(case)
+        c.update(nacc=nacc, e0=float(e0), e_end=float(model.energy(cfg)), g_pref=float(cfg.g_pref))
+        meta.append(c)
+        print("discs", n, "accepted", nacc, "of", case["ntrials"], "E0", e0, "nbins", len(grid.x))
+    out["meta"] = np.array(json.dumps(meta))
+
+
+MORE = {"rx": gen_rx, "latgas": gen_latgas, "latgas_move": gen_latgas_move, "discs": gen_discs}
