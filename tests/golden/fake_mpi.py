@@ -102,6 +102,23 @@ class Comm:
         _target(recvbuf)[...] = total
 
 
+def _reduce(self, sendbuf, recvbuf, op=None, root=0):
+    """Sum to root in rank order (examples/analyze_ising2D_mpi.py:34,44)."""
+    self.coll += 1
+    tag = ("rd", self.coll)
+    data = _payload(sendbuf)
+    if self.rank != root:
+        self._put(root, tag, data)
+        return
+    total = np.zeros_like(data)
+    for r in range(self.size):
+        total = total + (data if r == root else self._get(r, tag))
+    _target(recvbuf)[...] = total
+
+
+Comm.Reduce = _reduce
+
+
 def install(comm):
     """Register a fake ``mpi4py`` package whose COMM_WORLD is ``comm``."""
     MPI = types.SimpleNamespace(COMM_WORLD=comm, INT=_Datatype("INT"), DOUBLE=_Datatype("DOUBLE"), SUM=_Op("SUM"))

@@ -96,6 +96,11 @@ def _rx_rank_main(comm, case, workdir, ref_root):
     rx = refmpi.TemperatureRX_MPI(comm, refmc.CanonicalMonteCarlo, model, configs, kTs)
     obs = ref_ising.observer()
     out = rx.run(case["nsweeps"] * N, case["rx_every"] * N, N, 10 ** 12, obs, True, True)
+    # post-processing of the reference (examples/analyze_ising2D_mpi.py), run unmodified on the files above
+    import runpy
+    sys.argv = ["analyze_ising2D_mpi.py", str(R)]
+    comm.coll = 0
+    runpy.run_path(os.path.join(ref_root, "examples", "analyze_ising2D_mpi.py"), run_name="__main__")
     res = dict(
         rank_to_T=np.array(rx.rank_to_T, dtype=np.int64),
         config=rx.mycalc.config.config.astype(np.int8),
@@ -106,7 +111,10 @@ def _rx_rank_main(comm, case, workdir, ref_root):
         exchange_draws=inj.exchange_draws,
         obs_list=np.array(out, dtype=np.float64) if rank == 0 else None,
         files=sorted(os.listdir(os.path.join(workdir, str(rank)))),
-        top_files=sorted(f for f in os.listdir(workdir) if not f.isdigit()) if rank == 0 else None,
+        top_files=sorted(f for f in os.listdir(workdir) if not f.isdigit() and f not in ("obs_mean.dat", "binning.dat"))
+        if rank == 0 else None,
+        obs_mean=open(os.path.join(workdir, "obs_mean.dat")).read() if rank == 0 else None,
+        binning=open(os.path.join(workdir, "binning.dat")).read() if rank == 0 else None,
     )
     return res
 
@@ -132,6 +140,8 @@ def gen_rx(out):
         c["files"] = res[0]["files"]
         c["top_files"] = res[0]["top_files"]
         c["exchange_draws"] = int(sum(r["exchange_draws"] for r in res))
+        c["obs_mean_dat"] = res[0]["obs_mean"]
+        c["binning_dat"] = res[0]["binning"]
         meta.append(c)
         print("rx", n, "final rank_to_T", res[0]["rank_to_T"], "draws", c["exchange_draws"], "files", c["files"],
               c["top_files"])
