@@ -216,6 +216,19 @@ int pymc_rx_get_stats(pymc_handle *h, uint64_t *tried, uint64_t *accepted, int n
 int pymc_rx_get_round(pymc_handle *h, uint64_t *round);
 int pymc_rx_set_round(pymc_handle *h, uint64_t round);
 
+/* ---- device-side statistics ----------------------------------------------------------
+ * Per-temperature sums of the standard observables without a host round trip per sample: the
+ * accumulation obs[rank_to_T[rank]] += observe(...) of TemperatureRX_MPI.run (py_mc/mc_mpi.py:170-177)
+ * for E = c_bond*bond + c_second*second and M = second.  sums[t] = {sum E, sum E^2, sum |M|, sum M^2,
+ * sum M^4, sum M}, counts[t] = samples taken at table row t.  From these: <E>, <|M|>, the specific
+ * heat (<E^2>-<E>^2)/kT^2 and the Binder cumulant 1 - <M^4>/(3<M^2>^2).  With several GPUs each
+ * handle holds the contribution of its own replicas; add them up (the reference's closing Allreduce,
+ * mc_mpi.py:204). */
+#define PYMC_NSTAT 6
+int pymc_stats_reset(pymc_handle *h, double c_bond, double c_second);
+int pymc_stats_accumulate(pymc_handle *h);
+int pymc_stats_get(pymc_handle *h, double *sums, uint64_t *counts, int ntemps, int nstat);
+
 /* ---- pinned host memory ----------------------------------------------------------------
  * Page-locked buffers for upload/download at full PCIe speed (the reference keeps its arrays in
  * ordinary numpy memory, examples/ising2D.py:62; pageable buffers work too, only slower). */

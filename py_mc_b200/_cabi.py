@@ -29,7 +29,7 @@ SYMBOLS = [
     "pymc_set_pair_tables", "pymc_pair_sweep", "pymc_get_pair_counter", "pymc_set_pair_counter",
     "pymc_discs_create", "pymc_discs_destroy", "pymc_discs_upload", "pymc_discs_download", "pymc_discs_run",
     "pymc_discs_propose", "pymc_discs_observe", "pymc_discs_counters", "pymc_discs_set_trial_counter",
-    "pymc_discs_timer",
+    "pymc_discs_timer", "pymc_stats_reset", "pymc_stats_accumulate", "pymc_stats_get",
 ]
 
 
@@ -94,6 +94,9 @@ def _load():
         "pymc_discs_counters": [P, C.POINTER(C.c_uint64), P],
         "pymc_discs_set_trial_counter": [P, C.c_uint64],
         "pymc_discs_timer": [P, I64, C.POINTER(C.c_float)],
+        "pymc_stats_reset": [P, C.c_double, C.c_double],
+        "pymc_stats_accumulate": [P],
+        "pymc_stats_get": [P, P, P, I, I],
         "pymc_rx_setup": [P, P, I, C.c_double, C.c_double],
         "pymc_rx_energies": [P],
         "pymc_rx_buffers": [P, C.POINTER(P), C.POINTER(P)],
@@ -308,6 +311,22 @@ class Lattices:
     @pair_counter.setter
     def pair_counter(self, v):
         check(lib.pymc_set_pair_counter(self._h, int(v)))
+
+    # -- device-side statistics
+    NSTAT = 6
+
+    def stats_reset(self, c_bond, c_second=0.0):
+        check(lib.pymc_stats_reset(self._h, float(c_bond), float(c_second)))
+
+    def stats_accumulate(self):
+        check(lib.pymc_stats_accumulate(self._h))
+
+    def stats_get(self):
+        """(sums [ntemps, 6] = sum of E, E^2, |M|, M^2, M^4, M;  counts [ntemps])."""
+        sums = np.empty((self.ntemps, self.NSTAT), dtype=np.float64)
+        counts = np.empty(self.ntemps, dtype=np.uint64)
+        check(lib.pymc_stats_get(self._h, _ptr(sums), _ptr(counts), self.ntemps, self.NSTAT))
+        return sums, counts
 
     # -- replica exchange
     def rx_setup(self, betas, c_bond, c_second=0.0):

@@ -49,6 +49,31 @@ __global__ void rx_decide_kernel(const double *__restrict__ energies, const doub
     }
 }
 
+// K9: per-temperature accumulators, the device-side form of  obs[rank_to_T[rank]] += obs_step
+// (py_mc/mc_mpi.py:172) for the standard observables: E, E^2, |M|, M^2, M^4, M (M = second tracked
+// observable: magnetisation or particle number).  One thread per local replica; several replicas may
+// share a temperature row (independent replicas at equal T), hence atomics.
+constexpr int NSTAT = 6;
+__global__ void stats_accumulate_kernel(const unsigned long long *__restrict__ tracked, int nrep, int offset,
+                                        const int32_t *__restrict__ rep_to_T, double c_bond, double c_second,
+                                        double *stats, unsigned long long *counts) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= nrep) return;
+    const double b = (double)(long long)tracked[2 * r], m = (double)(long long)tracked[2 * r + 1];
+    double e = __dmul_rn(c_bond, b);
+    if (c_second != 0.0) e = __dadd_rn(e, __dmul_rn(m, c_second));
+    const int t = rep_to_T[offset + r];
+    double *row = stats + (size_t)t * NSTAT;
+    const double m2 = m * m;
+    atomicAdd(row + 0, e);
+    atomicAdd(row + 1, e * e);
+    atomicAdd(row + 2, fabs(m));
+    atomicAdd(row + 3, m2);
+    atomicAdd(row + 4, m2 * m2);
+    atomicAdd(row + 5, m);
+    atomicAdd(counts + t, 1ull);
+}
+
 __global__ void rx_invert_map_kernel(const int32_t *__restrict__ rep_to_T, int32_t *T_to_rep, int n) {
     const int r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r < n) T_to_rep[rep_to_T[r]] = r;

@@ -533,6 +533,8 @@ struct pymc_handle {
     int32_t *T_to_rep;             // [ntemps]
     unsigned long long *rx_tried, *rx_accepted;  // [ntemps] per lower temperature index of a pair
     double c_bond, c_second;
+    double *stats;                 // [ntemps][NSTAT] device-side observable sums (pymc_stats_*)
+    unsigned long long *stats_count;  // [ntemps]
     bool rx_ready;
     uint64_t rx_round;
     bool tables_set;
@@ -621,6 +623,8 @@ int pymc_destroy(pymc_handle *h) {
         cudaFree(h->T_to_rep);
         cudaFree(h->rx_tried);
         cudaFree(h->rx_accepted);
+        cudaFree(h->stats);
+        cudaFree(h->stats_count);
         if (h->ev0) cudaEventDestroy(h->ev0);
         if (h->ev1) cudaEventDestroy(h->ev1);
         if (h->own_stream) cudaStreamDestroy(h->own_stream);
@@ -1432,6 +1436,47 @@ int pymc_discs_timer(pymc_discs *d, int64_t ntrials, float *elapsed_ms) {
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
     return rc;
+}
+
+
+// ------------------------------------------------------------------------------------------
+// device-side statistics
+// ------------------------------------------------------------------------------------------
+int pymc_stats_reset(pymc_handle *h, double c_bond, double c_second) {
+    ENTER(h);
+    if (!h->stats) {
+        CUDA_TRY(cudaMalloc(&h->stats, (size_t)h->p.ntemps * NSTAT * 8));
+        CUDA_TRY(cudaMalloc(&h->stats_count, (size_t)h->p.ntemps * 8));
+    }
+    h->c_bond = c_bond;
+    h->c_second = c_second;
+    CUDA_TRY(cudaMemsetAsync(h->stats, 0, (size_t)h->p.ntemps * NSTAT * 8, h->stream));
+    CUDA_TRY(cudaMemsetAsync(h->stats_count, 0, (size_t)h->p.ntemps * 8, h->stream));
+    return PYMC_OK;
+}
+
+int pymc_stats_accumulate(pymc_handle *h) {
+    ENTER(h);
+    REQUIRE(h->stats, PYMC_ERR_STATE, "pymc_stats_accumulate: call pymc_stats_reset first");
+    if (h->dirty) {
+        int rc = rebase_tracked(h);
+        if (rc) return rc;
+    }
+    stats_accumulate_kernel<<<(h->p.nreplicas + 127) / 128, 128, 0, h->stream>>>(
+        h->tracked, h->p.nreplicas, h->p.replica_offset, h->rep_to_T, h->c_bond, h->c_second, h->stats, h->stats_count);
+    CUDA_TRY(cudaGetLastError());
+    return PYMC_OK;
+}
+
+int pymc_stats_get(pymc_handle *h, double *sums, uint64_t *counts, int ntemps, int nstat) {
+    ENTER(h);
+    REQUIRE(h->stats, PYMC_ERR_STATE, "pymc_stats_get: call pymc_stats_reset first");
+    REQUIRE(sums && counts && ntemps == h->p.ntemps && nstat == NSTAT, PYMC_ERR_BADARG,
+            "pymc_stats_get: need [%d][%d] sums", h->p.ntemps, NSTAT);
+    CUDA_TRY(cudaMemcpyAsync(sums, h->stats, (size_t)ntemps * NSTAT * 8, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaMemcpyAsync(counts, h->stats_count, (size_t)ntemps * 8, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return PYMC_OK;
 }
 
 int pymc_host_alloc(size_t bytes, void **out) {

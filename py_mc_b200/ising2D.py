@@ -48,6 +48,9 @@ class ising2D(model):
     def _pmc_energy(self, bond, second):
         return self.J * float(bond)
 
+    def _pmc_second(self, config):
+        return self.magnetization(config)
+
     def _pmc_energy_coeffs(self):
         """(c_bond, c_second) with E = c_bond*bond + c_second*second, for the on-device exchange test."""
         return float(self.J), 0.0

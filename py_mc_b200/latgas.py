@@ -44,6 +44,9 @@ class latticegas(model):
     def _pmc_energy(self, bond, second):
         return self.J * float(bond) + float(second) * (self.Eads - self.mu)
 
+    def _pmc_second(self, config):
+        return self.density(config)
+
     def _pmc_energy_coeffs(self):
         return float(self.J), float(self.Eads - self.mu)
 

@@ -314,6 +314,35 @@ class TemperatureRX_MPI(ParallelMC):
         else:  # host path (gloo): used by the CPU tests of the plumbing only
             raise RuntimeError("multi-process replica exchange needs the NCCL backend (one process per GPU)")
 
+    def _run_device_stats(self, nsteps, RXtrial_frequency, sample_frequency, observer):
+        """The run loop with sampling on the device: nothing in it synchronises with the host."""
+        lat = self._lat
+        lat.stats_reset(*self.model._pmc_energy_coeffs())
+        XCscheme, done, nsample = 0, 0, 0
+        while done < nsteps:
+            chunk = min(nsteps - done, RXtrial_frequency - done % RXtrial_frequency,
+                        sample_frequency - done % sample_frequency)
+            lat.sweep(chunk)
+            done += chunk
+            if done % RXtrial_frequency == 0:
+                self._exchange(XCscheme)
+                XCscheme = (XCscheme + 1) % 2
+            if done % sample_frequency == 0:
+                lat.stats_accumulate()
+                nsample += 1
+        sums, counts = lat.stats_get()
+        if self.procs > 1:
+            sums = self.comm.allreduce_sum_host(sums)
+            counts = np.rint(self.comm.allreduce_sum_host(counts.astype(np.float64))).astype(np.uint64)
+        self.rank_to_T = lat.get_replica_to_T().astype(int)
+        self._configs_changed()
+        self._refresh_states(with_energy=True)
+        _, accepted = lat.rx_stats()
+        self.accept_count = int(accepted.sum())
+        observer._finish(sums, counts, self.kTs)
+        if nsample:
+            return [[observer.mean_E[i], observer.mean_absM[i]] for i in range(len(self.kTs))]
+
     # -- the run loop (mc_mpi.py:143-209) --------------------------------------------------------
     def run(self, nsteps, RXtrial_frequency, sample_frequency=verylargeint, print_frequency=verylargeint,
             observer=None, subdirs=True, save_obs=True):
@@ -335,6 +364,8 @@ class TemperatureRX_MPI(ParallelMC):
             obs = np.zeros([self.nlocal, len(self.kTs), len(test_observe)])
         nsample = 0
         XCscheme = 0
+        if getattr(observer, "_pmc_device", False) and observe:
+            return self._run_device_stats(nsteps, RXtrial_frequency, sample_frequency, observer)
         outs = [open(self._path(loc, "obs.dat"), "a") for loc in range(self.nlocal)]
         done = 0
         try:

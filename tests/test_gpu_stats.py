@@ -1,0 +1,117 @@
+"""GPU physics checks with stated statistical error bars (independent streams): exact 4x4 canonical
+averages incl. specific heat and Binder cumulant from the device-side accumulators, Kaufman's exact
+finite-size energy at the Onsager T_c, and the device observer on the replica-exchange path."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import ising as o_ising
+from oracle import kaufman
+
+pytestmark = pytest.mark.gpu
+
+# kT: (<E>/N, <|M|>/N, C_v/N, U4) of the 4x4 periodic Ising model, J = -1
+EXACT_4x4 = {
+    1.0: (-1.997158440256, 0.999274583701, 0.023409397457, 0.666553756794),
+    2.0: (-1.755380288777, 0.918943267402, 0.605532657210, 0.644810791188),
+    2.269185314: (-1.565623787638, 0.843860444813, 0.783266825929, 0.617199318412),
+    3.0: (-1.017069626955, 0.601291326039, 0.603134714254, 0.480540660059),
+    5.0: (-0.456135369543, 0.342765627554, 0.119546188787, 0.207859765073),
+}
+
+
+def test_device_accumulators_reproduce_exact_4x4_thermodynamics():
+    from py_mc_b200 import _cabi
+    from py_mc_b200.observers import thermo
+    kTs = np.array(sorted(EXACT_4x4))
+    nT, per = len(kTs), 256
+    R = nT * per
+    lat = _cabi.Lattices(_cabi.MODEL_ISING, 4, 4, nreplicas=R, ntemps=nT, seed=99)
+    lat.init_random()
+    lat.set_accept_tables(np.array([o_ising.threshold_table(-1.0, kT)[1] for kT in kTs]))
+    lat.set_replica_to_T((np.arange(R) % nT).astype(np.int32))
+    lat.sweep(500)
+    blocks = []
+    host_sum = np.zeros((nT, 6))
+    for blk in range(16):
+        lat.stats_reset(-1.0)
+        for _ in range(100):
+            lat.sweep(4)
+            lat.stats_accumulate()
+            if blk == 0:  # cross-check the kernel's sums against host arithmetic on the same samples
+                b, m = lat.tracked()
+                e, m = -1.0 * b.astype(np.float64), m.astype(np.float64)
+                for k, v in enumerate((e, e * e, np.abs(m), m * m, m ** 4, m)):
+                    host_sum[:, k] += np.bincount(np.arange(R) % nT, weights=v, minlength=nT)
+        sums, counts = lat.stats_get()
+        assert np.all(counts == 100 * per)
+        if blk == 0:
+            assert np.array_equal(sums, host_sum)  # integer-valued doubles: exact
+        blocks.append(thermo(sums, counts, kTs))
+    for i, kT in enumerate(kTs):
+        e_ex, m_ex, cv_ex, u_ex = EXACT_4x4[kT]
+        for key, exact, scale in (("mean_E", e_ex, 16.0), ("mean_absM", m_ex, 16.0), ("specific_heat", cv_ex, 16.0),
+                                  ("binder", u_ex, 1.0)):
+            vals = np.array([b[key][i] for b in blocks]) / scale
+            mean, err = vals.mean(), vals.std(ddof=1) / np.sqrt(len(vals))
+            assert abs(mean - exact) < 5 * err + 2e-4, (kT, key, mean, exact, err)
+
+
+def test_energy_at_onsager_tc_matches_kaufman_32x32():
+    """T_c = 2/ln(1+sqrt 2); <E>/N and C_v/N of the 32x32 torus from Kaufman's exact partition function."""
+    from py_mc_b200 import _cabi
+    L, R = 32, 512
+    kT = kaufman.onsager_tc()
+    e_ex, cv_ex = kaufman.energy_and_cv_per_site(L, L, kT)
+    lat = _cabi.Lattices(_cabi.MODEL_ISING, L, L, nreplicas=R, ntemps=1, seed=2718)
+    lat.init_random()
+    lat.set_accept_tables(o_ising.threshold_table(-1.0, kT)[1][None, :])
+    lat.sweep(4000)
+    es = []
+    for _ in range(150):
+        lat.sweep(20)
+        b, _ = lat.tracked()
+        es.append(-1.0 * b.astype(np.float64))
+    es = np.array(es)                     # [sample, replica]; replicas are independent chains
+    per_rep = es.mean(axis=0) / (L * L)
+    mean, err = per_rep.mean(), per_rep.std(ddof=1) / np.sqrt(R)
+    assert abs(mean - e_ex) < 5 * err, (mean, e_ex, err)
+    cv_rep = es.var(axis=0, ddof=1) / (kT * kT) / (L * L)
+    cv, cv_err = cv_rep.mean(), cv_rep.std(ddof=1) / np.sqrt(R)
+    # the per-replica variance over a finite correlated window underestimates C_v slightly; allow that bias
+    assert abs(cv - cv_ex) < 5 * cv_err + 0.08 * cv_ex, (cv, cv_ex, cv_err)
+
+
+def test_device_observer_on_replica_exchange(tmp_path):
+    import py_mc_b200
+    from py_mc_b200.ising2D import ising2D, ising2D_config
+    from py_mc_b200.mc import CanonicalMonteCarlo
+    from py_mc_b200.mc_mpi import TemperatureRX_MPI
+    from py_mc_b200.observers import device_observer
+    old = os.getcwd()
+    os.chdir(tmp_path)
+    try:
+        py_mc_b200.set_seed(31)
+        R, L = 16, 16
+        kTs = np.linspace(1.8, 3.0, R)
+        configs = []
+        for _ in range(R):
+            c = ising2D_config(L, L)
+            c.prepare_random()
+            configs.append(c)
+        rx = TemperatureRX_MPI(None, CanonicalMonteCarlo, ising2D(-1.0), configs, kTs)
+        rx.run(1500, 5)
+        obs = device_observer()
+        out = rx.run(6000, 5, 5, observer=obs)
+        assert len(out) == R and np.all(obs.counts == 1200)
+        assert rx.accept_count > 0
+        e = np.array([o[0] for o in out]) / (L * L)
+        assert np.all(np.diff(e) > -0.02) and e[0] < e[-1]      # energy rises with temperature
+        for i in (0, R // 2, R - 1):
+            e_ex, _ = kaufman.energy_and_cv_per_site(L, L, kTs[i])
+            assert abs(e[i] - e_ex) < 0.02, (kTs[i], e[i], e_ex)
+        assert obs.binder[0] > obs.binder[-1]                    # ordered side -> 2/3, disordered -> 0
+        assert np.argmax(obs.specific_heat) not in (0, R - 1)    # C_v peaks inside the ladder (near T_c)
+    finally:
+        os.chdir(old)
