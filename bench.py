@@ -271,9 +271,69 @@ def run_rx(args):
         dist.destroy_process_group()
 
 
+def run_latgas(args):
+    """BASELINE config 4: pair-interaction lattice gas, 512 batched replicas of 256 x 256 (size not given by
+    BASELINE; stated here), J = -1, Eads - mu = 0, kT = 1.  One step = one flip sweep + one full
+    particle-hole exchange sweep of every replica.  Single GPU."""
+    import numpy as np
+    from py_mc_b200 import _cabi
+    from py_mc_b200.latgas_move import latticegas
+    L, R = args.lg_L, args.lg_replicas
+    layout = _cabi.LAYOUT_BITS if args.layout == "bits" else _cabi.LAYOUT_INT8
+    model = latticegas(Eads=0.0, J=-1.0, mu=0.0)
+    lat = _cabi.Lattices(_cabi.MODEL_LATGAS, L, L, nreplicas=R, ntemps=1, seed=SEED, layout=layout)
+    lat.init_random()
+    lat.set_accept_tables(model._pmc_thresholds(1.0)[None, :])
+    lat.set_pair_tables(model._pmc_pair_thresholds(1.0)[None, :])
+    nsites = R * L * L
+    out = {}
+    for name, fn, attempts in (("flip", lambda n: lat.sweep(n), nsites), ("pair_exchange", lambda n: lat.pair_sweep(n), 2 * nsites)):
+        fn(args.warmup)
+        lat.synchronize()
+        lat.timer_start()
+        fn(args.steps)
+        ms = lat.timer_stop()
+        out[name] = {"value": attempts * args.steps / (ms * 1e-3), "unit": "attempts/s", "ms_per_step": ms / args.steps}
+    b, n = lat.tracked()
+    b2, n2 = lat.reduce_observables()
+    assert np.array_equal(b, b2) and np.array_equal(n, n2)
+    lps, kname = lat.sweep_kernel_info()
+    line = {"metric": "lattice-gas attempts/s", "value": out["flip"]["value"], "unit": "attempts/s", "n_gpus": 1,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": out["flip"]["ms_per_step"],
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "latgas_%d_replicas_of_%dx%d_J=-1_kT=1" % (R, L, L), "layout": args.layout,
+                       "flip_kernel": kname, "seed": SEED},
+            "pair_exchange": out["pair_exchange"], "gpu_launches": lps * args.steps}
+    print(json.dumps(line), flush=True)
+
+
+def run_discs(args):
+    """BASELINE config 5 (re-interpreted, SURVEY.md section 8 notes): batched independent hard-disc replicas,
+    64 x 128 = 8192 replicas of the shipped system (20 discs, L = 1, r = 1/14, maxstep = r/2)."""
+    from py_mc_b200.hardcore import DiscBatch
+    R = args.disc_replicas
+    b = DiscBatch(R, 1.0, 20, 1.0 / 14.0, 1.0 / 28.0, isotropic=False, seed=SEED)
+    per = args.disc_trials
+    b._d.timed_run(per)
+    ms = [b._d.timed_run(per) for _ in range(max(3, args.steps // 10))]
+    ms_best = sorted(ms)[len(ms) // 2]
+    assert not b.any_overlap().any()
+    line = {"metric": "hard-disc move attempts/s", "value": R * per / (ms_best * 1e-3), "unit": "attempts/s", "n_gpus": 1,
+            "steps": len(ms), "warmup": 1, "ms_per_step": ms_best, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "hard_discs_%d_replicas_20_discs_%d_trials_per_launch" % (R, per), "seed": SEED,
+                       "acceptance": float(b.acceptance().mean())},
+            "gpu_launches": len(ms)}
+    print(json.dumps(line), flush=True)
+
+
 def run_ours(args):
     import numpy as np
     rank, local_rank, world = dist_env()
+    if args.workload == "latgas":
+        return run_latgas(args)
+    if args.workload == "discs":
+        return run_discs(args)
     if pick_workload(args, world) == "rx":
         return run_rx(args)
     from py_mc_b200 import _cabi
@@ -405,7 +465,11 @@ def main():
     ap.add_argument("--also-bits", action="store_true", default=True)
     ap.add_argument("--no-also-bits", dest="also_bits", action="store_false")
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--workload", default="auto", choices=["auto", "ising16k", "rx"])
+    ap.add_argument("--workload", default="auto", choices=["auto", "ising16k", "rx", "latgas", "discs"])
+    ap.add_argument("--lg-replicas", type=int, default=512)
+    ap.add_argument("--lg-L", type=int, default=256)
+    ap.add_argument("--disc-replicas", type=int, default=8192)
+    ap.add_argument("--disc-trials", type=int, default=2000)
     ap.add_argument("--rx-replicas", type=int, default=256, help="replicas per GPU (weak scaling)")
     ap.add_argument("--rx-L", type=int, default=1024)
     ap.add_argument("--rx-every", type=int, default=10, help="sweeps between exchanges")
