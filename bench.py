@@ -99,8 +99,9 @@ def dist_env():
 def cpu_baseline(seconds_target=12.0):
     from oracle import cpu_port
     cores = os.cpu_count() or 1
-    rate1 = 2.5e5  # attempts/s/core, survey-time indication; only used to size the sample
-    ntrials = int(rate1 * seconds_target)
+    # size the sample from a short calibration so that it is about seconds_target of CPU work per core
+    calib, _ = cpu_port.time_all_cores(1024, -1.0, TC, 100000, 1)
+    ntrials = int(max(calib, 5e4) * seconds_target)
     value, wall = cpu_port.time_all_cores(1024, -1.0, TC, ntrials, cores)
     return {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
             "sample": "%d single-site MCstep trials per core on a 1024x1024 float64 lattice at kT=Tc, one replica "
