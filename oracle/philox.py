@@ -13,15 +13,17 @@ through injected ``random``/``randrange`` objects.
 Stream layout ("pmc stream v1"), restated in ``py_mc_b200/csrc/pmc_stream.cuh``:
 
 ``key      = (seed & 0xffffffff, seed >> 32)``
-``counter  = (idx, replica, step_lo, domain<<28 | call<<24 | step_hi[23:0])``
+``counter  = (idx, replica, step_lo, domain<<28 | call<<24 | lane<<18 | step_hi[17:0])``
 
 * domain 0 (Metropolis sweep): ``idx`` = word index ``row*nwords_per_row + wcol``
-  of a 64-site word of one colour, ``step = 2*sweep + colour``, ``call`` = 0..15.
-  Call ``m`` yields two 64-bit *bit planes*: plane ``2m = o0 | o1<<32`` and plane
-  ``2m+1 = o2 | o3<<32``.  The 32-bit uniform of lane ``l`` of the word is
-  ``x32 = sum_j bit_l(plane_j) << (31-j)`` (plane 0 is the most significant bit).
-  A kernel may stop generating planes as soon as every comparison ``x32 <= thr``
-  in the warp is decided; the value is *defined* by all 32 planes.
+  of a 64-site word of one colour, ``step = 2*sweep + colour``.  The 32-bit uniform
+  ``x32`` of lane ``l`` of the word has two parts.  *Head*: its 8 most significant
+  bits are bit ``l`` of the 64-bit *bit planes* 0..7; call ``m`` in 0..3 (lane field 0)
+  yields plane ``2m = o0 | o1<<32`` and plane ``2m+1 = o2 | o3<<32``, plane 0 is the
+  MSB.  *Tail*: its 24 low bits are ``o0 >> 8`` of the lane's own call (call 15, lane
+  field ``l``).  A kernel compares the head bit-serially for all 64 lanes at once
+  (which decides 255 of 256 comparisons ``x32 <= thr``) and evaluates the tail only
+  for lanes that are still undecided; the value is *defined* by both parts.
 * domain 1 (initial configuration): ``idx`` = ``site >> 2`` (natural row-major site
   index), element ``site & 3`` of the output; spin = +1 iff ``x32 >= 2**31``
   (the ``random() >= 0.5`` rule of ``examples/ising2D.py:67-70``).
@@ -79,17 +81,22 @@ def seed_key(seed):
     return (seed & 0xFFFFFFFF, seed >> 32)
 
 
-def make_counter(idx, replica, step, domain, call=0):
-    """Build counters [..., 4] following the stream layout above (idx may be an array)."""
+HEAD_PLANES = 8
+TAIL_CALL = 15
+
+
+def make_counter(idx, replica, step, domain, call=0, lane=0):
+    """Build counters [..., 4] following the stream layout above (idx and lane may be arrays)."""
     idx = np.asarray(idx, dtype=np.uint64)
     step = int(step)
-    assert 0 <= step < (1 << 56)
+    assert 0 <= step < (1 << 50)
     assert 0 <= call < 16 and 0 <= domain < 16
     ctr = np.empty(idx.shape + (4,), dtype=np.uint32)
     ctr[..., 0] = (idx & _MASK32).astype(np.uint32)
     ctr[..., 1] = np.uint32(int(replica) & 0xFFFFFFFF)
     ctr[..., 2] = np.uint32(step & 0xFFFFFFFF)
-    ctr[..., 3] = np.uint32((domain << 28) | (call << 24) | ((step >> 32) & 0xFFFFFF))
+    ctr[..., 3] = (np.uint32((domain << 28) | (call << 24) | ((step >> 32) & 0x3FFFF)) |
+                   (np.asarray(lane, dtype=np.uint32) << np.uint32(18)))
     return ctr
 
 
@@ -103,15 +110,19 @@ def word_planes(seed, replica, step, word_idx, call, domain=DOMAIN_SWEEP):
 
 
 def word_lane_x32(seed, replica, step, word_idx, domain=DOMAIN_SWEEP):
-    """x32 for all 64 lanes of each word: uint32 array [..., 64] (all 32 planes evaluated)."""
+    """x32 for all 64 lanes of each word: uint32 array [..., 64] (head planes + per-lane tail)."""
     word_idx = np.asarray(word_idx, dtype=np.uint64)
     lanes = np.arange(64, dtype=np.uint64)
     x = np.zeros(word_idx.shape + (64,), dtype=np.uint64)
-    for call in range(16):
+    for call in range(HEAD_PLANES // 2):
         even, odd = word_planes(seed, replica, step, word_idx, call, domain)
         for j, plane in ((2 * call, even), (2 * call + 1, odd)):
             bits = (plane[..., None] >> lanes) & np.uint64(1)
             x |= bits << np.uint64(31 - j)
+    idx = np.broadcast_to(word_idx[..., None], word_idx.shape + (64,))
+    lane = np.broadcast_to(lanes.astype(np.uint32), idx.shape)
+    tail = philox4x32_10(make_counter(idx, replica, step, domain, TAIL_CALL, lane), seed_key(seed))[..., 0]
+    x |= tail.astype(np.uint64) >> np.uint64(HEAD_PLANES)
     return x.astype(np.uint32)
 
 

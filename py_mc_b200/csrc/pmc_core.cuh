@@ -10,8 +10,8 @@
 // neighbours), the caller supplies one 32-bit threshold per class
 // (thr = floor(exp(-dE/kT) 2^32), 2^32-1 = always accept), and a lane is accepted iff its
 // uniform x32 <= thr.  x32 is defined bit-serially by the Philox planes of pmc_stream.cuh, so the
-// comparison runs MSB-first on all 64 lanes in parallel and stops as soon as every lane of the
-// warp is decided (about log2(2048) + 1 planes instead of 32).
+// comparison runs MSB-first on all 64 lanes in parallel for the first eight bits; the few lanes that
+// are still undecided then are settled one per thread from their own Philox block.
 #pragma once
 #include "pmc_stream.cuh"
 
@@ -52,13 +52,16 @@ __device__ __forceinline__ void count_masks(uint64_t a0, uint64_t a1, uint64_t a
     m[4] = a2;
 }
 
-// Bit-serial x32 <= thr for all lanes.  Every thread of the warp must call this together.
+// x32 <= thr for all lanes.  Every thread of the warp must call this together.
 //
 // Only the lanes of *hard* classes (thr < 2^32-1, i.e. dE > 0) need random bits; the caller
-// passes them compacted as hm[k] (one-hot lane masks) / ht[k] (thresholds, warp-uniform).  Per
-// plane the per-lane threshold bit is T = OR_k (hm[k] & -bit_j(ht[k])); the selectors are
-// uniform, so the per-lane work is 2 logic ops per hard class plus 3 for the lt/und update on each
-// 32-bit half.
+// passes them compacted as hm[k] (one-hot lane masks) / ht[k] (thresholds, warp-uniform).
+// Head: the 8 most significant bits are compared bit-serially for all 64 lanes at once -- per plane
+// the per-lane threshold bit is T = OR_k (hm[k] & -bit_j(ht[k])), 2 logic operations per hard class plus 3
+// for the lt/und update on each 32-bit half -- which leaves about 1 lane in 256 undecided.
+// Tail: each undecided lane is settled by one Philox block of its own (its low bits), by the thread
+// that owns the word.  (Queueing the warp's undecided lanes in shared memory and sharing them out one
+// per thread was tried and measured slower: the bookkeeping cost more than the blocks it saved.)
 template <int MAXH>
 __device__ __forceinline__ uint64_t decide_hard(const uint64_t (&hm)[MAXH], const uint32_t (&ht)[MAXH],
                                                 uint64_t always, uint64_t valid, uint32_t word_idx,
@@ -66,15 +69,13 @@ __device__ __forceinline__ uint64_t decide_hard(const uint64_t (&hm)[MAXH], cons
     uint64_t needed = 0;
 #pragma unroll
     for (int k = 0; k < MAXH; ++k) needed |= hm[k];
-    uint64_t und = needed & valid;  // lanes whose x32 still equals thr on all planes seen so far
+    uint64_t und = needed & valid;  // lanes whose x32 still equals thr on all bits seen so far
     uint64_t lt = 0;                // lanes already known to have x32 < thr
-#pragma unroll 1
-    for (uint32_t call = 0; call < 16; ++call) {
+#pragma unroll
+    for (uint32_t call = 0; call < HEAD_PLANES / 2; ++call) {
         if (!__any_sync(0xFFFFFFFFu, und != 0)) break;
         uint64_t pe, po;
         word_planes(word_idx, replica, step, domain, call, key, pe, po);
-        // (A four-way uniform branch per plane on the pair of threshold bits needs fewer logic
-        // operations but measured 4% slower: the extra branches cost more issue slots than they save.)
         const int be = 31 - 2 * (int)call, bo = be - 1;
         uint64_t te = 0, to = 0;
 #pragma unroll
@@ -87,8 +88,22 @@ __device__ __forceinline__ uint64_t decide_hard(const uint64_t (&hm)[MAXH], cons
         lt |= und & to & ~po;
         und &= ~(to ^ po);
     }
-    // und != 0 here only after all 32 planes: x32 == thr, which the reference accepts (u <= p).
-    return ((always & valid) | lt | und);
+    // Tail: every thread settles its own undecided lanes, one Philox block per lane; the warp loops
+    // until the thread with the most of them is done (usually one or two rounds).
+#pragma unroll 1
+    while (__any_sync(0xFFFFFFFFu, und != 0)) {
+        if (und) {
+            const int l = __ffsll((long long)und) - 1;
+            und &= und - 1;
+            uint32_t thr = ht[0];
+#pragma unroll
+            for (int k = 1; k < MAXH; ++k)
+                if ((hm[k] >> l) & 1ull) thr = ht[k];
+            const uint32_t x = lane_tail(word_idx, replica, step, domain, (uint32_t)l, key);
+            if (x <= (thr & ((1u << TAIL_BITS) - 1u))) lt |= 1ull << l;  // head bits equal: the low bits decide
+        }
+    }
+    return (always & valid) | lt;
 }
 
 // ------------------------------------------------------------------------------------------

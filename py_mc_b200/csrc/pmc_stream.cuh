@@ -5,11 +5,15 @@
 // definition shared by every kernel; oracle/philox.py restates it for the CPU checker.
 //
 //   key     = (seed_lo, seed_hi)
-//   counter = (idx, replica, step_lo, domain<<28 | call<<24 | step_hi[23:0])
+//   counter = (idx, replica, step_lo, domain<<28 | call<<24 | lane<<18 | step_hi[17:0])
 //
 // Domain 0 (sweeps): idx = word index (row*nwords_per_row + wcol) of a 64-site word of one
-// colour, step = 2*sweep + colour, call m in 0..15 yields bit planes 2m (o0 | o1<<32) and
-// 2m+1 (o2 | o3<<32).  Lane l's 32-bit uniform is x32 = sum_j bit_l(plane_j) << (31-j).
+// colour, step = 2*sweep + colour.  The 32-bit uniform x32 of lane l of that word has two parts:
+//   head  its HEAD_PLANES = 8 most significant bits are bit l of the bit planes 0..7; call m
+//         (lane field 0) yields planes 2m (o0 | o1<<32) and 2m+1 (o2 | o3<<32), plane 0 = MSB;
+//   tail  its 24 low bits are o0 >> 8 of the lane's own call (call = TAIL_CALL = 15, lane field l).
+// The head serves all 64 lanes with one Philox block per two bits and decides 255/256 of the
+// comparisons; the few lanes still undecided take their remaining bits from one block each.
 #pragma once
 #include <stdint.h>
 
@@ -33,8 +37,15 @@ __host__ __device__ __forceinline__ PhiloxKey make_key(uint64_t seed) {
     return k;
 }
 
-__host__ __device__ __forceinline__ uint32_t ctr3(uint32_t domain, uint32_t call, uint64_t step) {
-    return (domain << 28) | (call << 24) | ((uint32_t)(step >> 32) & 0xFFFFFFu);
+#ifndef PMC_HEAD_PLANES
+#define PMC_HEAD_PLANES 8
+#endif
+constexpr int HEAD_PLANES = PMC_HEAD_PLANES;  // planes compared bit-serially for all lanes of a word (even)
+constexpr uint32_t TAIL_CALL = 15;   // call number of a lane's own block
+constexpr int TAIL_BITS = 32 - HEAD_PLANES;
+
+__host__ __device__ __forceinline__ uint32_t ctr3(uint32_t domain, uint32_t call, uint64_t step, uint32_t lane = 0) {
+    return (domain << 28) | (call << 24) | (lane << 18) | ((uint32_t)(step >> 32) & 0x3FFFFu);
 }
 
 // One Philox4x32-10 block.  The round keys depend only on the (uniform) seed, so the
@@ -63,6 +74,12 @@ __device__ __forceinline__ void word_planes(uint32_t word_idx, uint32_t replica,
     uint4 o = philox4x32_10(word_idx, replica, (uint32_t)step, ctr3(domain, call, step), key);
     even = (uint64_t)o.x | ((uint64_t)o.y << 32);
     odd = (uint64_t)o.z | ((uint64_t)o.w << 32);
+}
+
+// The 26 low bits of lane `lane` of a word.
+__device__ __forceinline__ uint32_t lane_tail(uint32_t word_idx, uint32_t replica, uint64_t step, uint32_t domain,
+                                              uint32_t lane, PhiloxKey key) {
+    return philox4x32_10(word_idx, replica, (uint32_t)step, ctr3(domain, TAIL_CALL, step, lane), key).x >> HEAD_PLANES;
 }
 
 }  // namespace pmc
