@@ -71,7 +71,11 @@ __device__ __forceinline__ uint64_t decide_hard(const uint64_t (&hm)[MAXH], cons
     for (int k = 0; k < MAXH; ++k) needed |= hm[k];
     uint64_t und = needed & valid;  // lanes whose x32 still equals thr on all bits seen so far
     uint64_t lt = 0;                // lanes already known to have x32 < thr
+#ifdef PMC_HEAD_ROLLED
+#pragma unroll 1
+#else
 #pragma unroll
+#endif
     for (uint32_t call = 0; call < HEAD_PLANES / 2; ++call) {
         if (!__any_sync(0xFFFFFFFFu, und != 0)) break;
         uint64_t pe, po;
