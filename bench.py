@@ -35,6 +35,27 @@ def measured_peak_hbm():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def profiled_traffic(kernel_name, nsites_expected):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
+    ncu --set full summary of this workload (profiles/); None if there is no capture for this kernel/size."""
+    import csv
+    table = {"sweep_fused_i8_kernel": ("r1_fused_final_summary.csv", 268435456),
+             "sweep_bits_rows_kernel": ("r1_bits_final_summary.csv", 268435456)}
+    if kernel_name not in table or table[kernel_name][1] != nsites_expected:
+        return None, None
+    path = os.path.join(ROOT, "profiles", table[kernel_name][0])
+    try:
+        vals = {}
+        for row in csv.reader(open(path)):
+            if row and row[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[row[1]]
+                nums = [float(v.replace(",", "")) * scale for v in row[2:] if v]
+                vals[row[0]] = sum(nums) / len(nums)
+        return vals["dram__bytes_read.sum"] + vals["dram__bytes_write.sum"], "profiles/" + table[kernel_name][0]
+    except Exception:
+        return None, None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons while the timed region runs."""
 
@@ -418,6 +439,7 @@ def run_ours(args):
     launch_ms = ms / (lps * args.steps)
     peak, peak_src = measured_peak_hbm()
     achieved = alg_bytes_per_launch / (launch_ms * 1e-3) / 1e9
+    traffic, traffic_src = profiled_traffic(kname, nsites)
 
     extra = {}
     if args.also_bits and layout == _cabi.LAYOUT_INT8:
@@ -446,8 +468,9 @@ def run_ours(args):
                     "note": "C-ABI upload(pinned host int8) + sweeps + download(host int8) + tracked observables per step"},
             "gpu_launches": lps * args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "kernel": kname, "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": alg_bytes_per_launch},
+                         "traffic": traffic, "traffic_source": traffic_src, "kernel": kname, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": alg_bytes_per_launch,
+                         "note": "not HBM-bound: the integer ALU pipe limits this kernel (profiles/README.md)"},
         }
         line.update(extra)
         if world == 1 and not args.no_cpu:

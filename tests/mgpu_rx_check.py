@@ -65,6 +65,39 @@ def main():
             print("case %s on %d GPUs: %s" % (n, world, "ok" if flag.item() else "MISMATCH"), flush=True)
         ok &= bool(flag.item())
         os.chdir(work[0])
+    # device-side observer and ParallelMC on the partitioned replicas: results must not depend on the
+    # number of GPUs (compared with a single-process run of the same seed on rank 0)
+    from py_mc_b200.mc_mpi import ParallelMC
+    from py_mc_b200.observers import device_observer
+
+    def rx_device(comm_obj, R=8):
+        py_mc_b200.set_seed(1234)
+        kTs = np.linspace(1.8, 3.0, R)
+        cfgs = []
+        for r in range(R):
+            c = ising2D_config(8, 8)
+            c.config[:, :] = o_ising.init_config(1234, r, 8, 8)
+            cfgs.append(c)
+        rx = TemperatureRX_MPI(comm_obj, CanonicalMonteCarlo, ising2D(-1.0), cfgs, kTs)
+        obs = device_observer()
+        out = rx.run(300, 2, 3, observer=obs)
+        return np.array(out), obs.counts.copy(), rx.rank_to_T.copy()
+
+    if world in (2, 4, 8):
+        os.makedirs("devobs", exist_ok=True)
+        dist.barrier()
+        os.chdir(os.path.join(work[0], "devobs"))
+        multi = rx_device(ReplicaComm(dist))
+        good = True
+        if rank == 0:
+            single = rx_device(ReplicaComm(None))
+            good = (np.allclose(multi[0], single[0], rtol=1e-12) and np.array_equal(multi[1], single[1])
+                    and np.array_equal(multi[2], single[2]))
+            print("device observer on %d GPUs vs 1 GPU: %s" % (world, "ok" if good else "MISMATCH"), flush=True)
+        flag = torch.tensor([1 if good else 0], device="cuda")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        ok &= bool(flag.item())
+        os.chdir(work[0])
     if rank == 0:
         print("MGPU_RX_CHECK", "PASS" if ok else "FAIL", flush=True)
     dist.destroy_process_group()
