@@ -226,10 +226,15 @@ def run_rx(args):
     ex0 = state["exchanges"]
     ev0.record(stream)
     steps(args.steps)
+    ex1 = state["exchanges"]
     ev1.record(stream)
     torch.cuda.synchronize()
     ms = ev0.elapsed_time(ev1)
+    if ms < 400.0:  # keep the same loop running (untimed) until the sampler has seen ~0.4 s under load
+        steps(int(args.steps * (400.0 - ms) / max(ms, 1e-3)) + 1)
+        torch.cuda.synchronize()
     clocks = sampler.stop()
+    clocks["window"] = "timed region" if ms >= 400.0 else "timed region + untimed repeat of the same loop (0.4 s in all)"
     if dist is not None:
         dist.barrier()
         t = torch.tensor([ms], device="cuda")
@@ -237,7 +242,7 @@ def run_rx(args):
         ms = float(t.item())
     nsites = nloc * L * L
     value = world * nsites * args.steps / (ms * 1e-3)
-    nex = state["exchanges"] - ex0
+    nex = ex1 - ex0
 
     # end to end: host configurations in, sweeps + exchanges, observables and the map out, every step
     host = [lat.download(r) for r in range(min(nloc, 4))]
@@ -401,7 +406,11 @@ def run_ours(args):
     sampler = ClockSampler(local_rank)
     sampler.start()
     ms = timed(lat, args.steps, args.warmup)
+    if ms < 400.0:  # keep the same kernel running (untimed) until the sampler has seen ~0.4 s under load
+        lat.sweep(int(args.steps * (400.0 - ms) / max(ms, 1e-3)) + 1)
+        lat.synchronize()
     clocks = sampler.stop()
+    clocks["window"] = "timed region" if ms >= 400.0 else "timed region + untimed repeat of the same loop (0.4 s in all)"
     if dist is not None:
         import torch
         t = torch.tensor([ms], device="cuda")
