@@ -81,12 +81,19 @@ __device__ __forceinline__ uint64_t decide_hard(const uint64_t (&hm)[MAXH], cons
         uint64_t pe, po;
         word_planes(word_idx, replica, step, domain, call, key, pe, po);
         const int be = 31 - 2 * (int)call, bo = be - 1;
-        uint64_t te = 0, to = 0;
+        // per-lane threshold bit of this plane: T = OR_k (hm[k] if bit_j(ht[k])).  The class masks are
+        // disjoint, so the OR is a sum and the selection a multiplication by 0 or 1: integer
+        // multiply-adds run on the FMA pipe, which is otherwise idle here, instead of the logic pipe.
+        uint32_t te_lo = 0, te_hi = 0, to_lo = 0, to_hi = 0;
 #pragma unroll
         for (int k = 0; k < MAXH; ++k) {
-            te |= hm[k] & (0ull - (uint64_t)((ht[k] >> be) & 1u));
-            to |= hm[k] & (0ull - (uint64_t)((ht[k] >> bo) & 1u));
+            const uint32_t b_e = (ht[k] >> be) & 1u, b_o = (ht[k] >> bo) & 1u;
+            te_lo += (uint32_t)hm[k] * b_e;
+            te_hi += (uint32_t)(hm[k] >> 32) * b_e;
+            to_lo += (uint32_t)hm[k] * b_o;
+            to_hi += (uint32_t)(hm[k] >> 32) * b_o;
         }
+        const uint64_t te = ((uint64_t)te_hi << 32) | te_lo, to = ((uint64_t)to_hi << 32) | to_lo;
         lt |= und & te & ~pe;
         und &= ~(te ^ pe);
         lt |= und & to & ~po;
