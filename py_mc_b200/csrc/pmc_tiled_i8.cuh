@@ -31,7 +31,7 @@ __device__ __forceinline__ uint32_t pack16(uint4 v) {
             // bit 0 of each byte: bits 0,8,16,24 -> product bits 28..31
             nib = ((w[j] & 0x01010101u) * 0x10204080u) >> 28;
         }
-        r |= nib << (4 * j);
+        r += nib * (1u << (4 * j));  // disjoint nibbles: a multiply-add (FMA pipe) instead of shift + or
     }
     return (MODEL == MODEL_ISING) ? (~r & 0xFFFFu) : r;
 }
@@ -44,7 +44,8 @@ __device__ __forceinline__ uint4 unpack16(uint32_t bits) {
     for (int j = 0; j < 4; ++j) {
         const uint32_t nib = (bits >> (4 * j)) & 0xFu;
         const uint32_t spread = (nib * 0x00204081u) & 0x01010101u;  // bit b -> byte b (0 or 1)
-        w[j] = (MODEL == MODEL_ISING) ? ~(spread * 0xFEu) : spread;  // 1 -> 0x01, 0 -> 0xFF
+        // 1 -> 0x01, 0 -> 0xFF:  0xFF - 0xFE*bit per byte, one multiply-add
+        w[j] = (MODEL == MODEL_ISING) ? 0xFFFFFFFFu - spread * 0xFEu : spread;
     }
     return make_uint4(w[0], w[1], w[2], w[3]);
 }
