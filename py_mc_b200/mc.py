@@ -215,6 +215,8 @@ class CanonicalMonteCarlo:
             obs = self.config._device_observables()
             if obs is None:  # the host copy is the newest (someone took a writable view): recompute
                 self._energy = self.model.energy(self.config)
+            elif hasattr(self.model, "_pmc_energy_for"):
+                self._energy = self.model._pmc_energy_for(self.config, *obs)
             else:
                 self._energy = self.model._pmc_energy(*obs)
         return self._energy

@@ -176,7 +176,9 @@ class ParallelMC(object):
             b, s = self._lat.tracked()
         for loc, st in enumerate(self.states):
             st.kT = self.kTs[self.rank_to_T[self.first + loc]]
-            if with_energy:
+            if with_energy and hasattr(self.model, "_pmc_energy_for"):
+                st.energy = self.model._pmc_energy_for(st.config, int(b[loc]), int(s[loc]))
+            elif with_energy:
                 st.energy = self.model._pmc_energy(int(b[loc]), int(s[loc]))
 
     def _configs_changed(self):
