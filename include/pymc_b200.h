@@ -153,6 +153,30 @@ int pymc_reduce_observables_static(pymc_handle *h, int64_t *bond, int64_t *secon
 int pymc_propose(pymc_handle *h, int replica, const int32_t *x, const int32_t *y, int n,
                  int32_t *site_out, int32_t *nnsum_out);
 
+/* ---- one lattice over several GPUs (row slabs) ----------------------------------------
+ * No counterpart in the reference (it has no domain decomposition).
+ * pymc_create_slab: params->lenX/lenY are the WHOLE lattice; this handle owns rows
+ *   [slab_index*lenX/nslabs, +lenX/nslabs) plus two halo rows on either side.  int8 layout, fused
+ *   sweep kernel; needs (lenX/nslabs) % 32 == 0 and lenY % 1024 == 0.  The random stream is indexed by
+ *   whole-lattice rows, so the union of the slabs follows exactly the single-GPU trajectory.
+ * pymc_slab_ipc_export / pymc_slab_connect: each process exports three CUDA IPC handles (its two
+ *   lattice buffers and its flag words, 3 x 64 bytes) and is given those of the slab above and below
+ *   (periodic).  After that pymc_sweep stores the first/last two rows it computes straight into the
+ *   neighbours' halo rows over NVLink from inside the sweep kernel, and a one-thread kernel per sweep
+ *   does the neighbour barrier through the flag words (bounded wait: pymc_slab_status reports 1 if a
+ *   neighbour never arrived).  All slabs must issue the same pymc_sweep calls.
+ * pymc_upload_config / pymc_download_config move the owned rows only ((lenX/nslabs)*lenY sites);
+ *   after uploads, every slab calls pymc_slab_push_halos once.  pymc_init_random needs no exchange.
+ * pymc_reduce_observables / pymc_get_tracked return this slab's share: add them up over the slabs. */
+int pymc_create_slab(const pymc_params *params, int slab_index, int nslabs, pymc_handle **out);
+int pymc_slab_ipc_export(pymc_handle *h, void *handles, size_t nbytes);
+int pymc_slab_connect(pymc_handle *h, const void *up_handles, const void *down_handles, size_t nbytes);
+/* Neighbours inside one process (tests, one host thread driving several slabs): plain handles instead
+ * of IPC, no flag barrier; the caller puts all slabs on one stream and sweeps them one sweep at a time in turn. */
+int pymc_slab_connect_local(pymc_handle *h, pymc_handle *up, pymc_handle *down);
+int pymc_slab_push_halos(pymc_handle *h);
+int pymc_slab_status(pymc_handle *h, int *status);
+
 /* ---- particle moves of the lattice gas ------------------------------------------------
  * Takes over the move branch of latticegas.trialstep (examples/latgas_move.py:56-83) with
  * nearest-neighbour particle-hole exchanges on 16 conflict-free bond classes and the physically

@@ -29,6 +29,8 @@ SYMBOLS = [
     "pymc_set_pair_tables", "pymc_pair_sweep", "pymc_get_pair_counter", "pymc_set_pair_counter",
     "pymc_discs_create", "pymc_discs_destroy", "pymc_discs_upload", "pymc_discs_download", "pymc_discs_run",
     "pymc_discs_propose", "pymc_discs_observe", "pymc_discs_counters", "pymc_discs_set_trial_counter",
+    "pymc_create_slab", "pymc_slab_ipc_export", "pymc_slab_connect", "pymc_slab_connect_local",
+    "pymc_slab_push_halos", "pymc_slab_status",
     "pymc_discs_timer", "pymc_stats_reset", "pymc_stats_accumulate", "pymc_stats_get",
 ]
 
@@ -94,6 +96,12 @@ def _load():
         "pymc_discs_counters": [P, C.POINTER(C.c_uint64), P],
         "pymc_discs_set_trial_counter": [P, C.c_uint64],
         "pymc_discs_timer": [P, I64, C.POINTER(C.c_float)],
+        "pymc_create_slab": [C.POINTER(Params), I, I, C.POINTER(P)],
+        "pymc_slab_ipc_export": [P, P, C.c_size_t],
+        "pymc_slab_connect": [P, P, P, C.c_size_t],
+        "pymc_slab_connect_local": [P, P, P],
+        "pymc_slab_push_halos": [P],
+        "pymc_slab_status": [P, C.POINTER(I)],
         "pymc_stats_reset": [P, C.c_double, C.c_double],
         "pymc_stats_accumulate": [P],
         "pymc_stats_get": [P, P, P, I, I],
@@ -166,7 +174,7 @@ class Lattices:
     """A batch of replicas of one lattice model on one GPU (thin owner of a pymc_handle)."""
 
     def __init__(self, model, lenX, lenY, nreplicas=1, ntemps=1, seed=0, layout=LAYOUT_INT8, device=0,
-                 replica_offset=0, nreplicas_global=None, kernel=KERNEL_AUTO):
+                 replica_offset=0, nreplicas_global=None, kernel=KERNEL_AUTO, slab=None):
         self._h = C.c_void_p()
         self.model, self.lenX, self.lenY = int(model), int(lenX), int(lenY)
         self.nreplicas, self.ntemps, self.layout = int(nreplicas), int(ntemps), int(layout)
@@ -176,7 +184,12 @@ class Lattices:
         self.device = int(device)
         p = Params(ABI_VERSION, self.device, self.model, self.layout, self.lenX, self.lenY, self.nreplicas,
                    self.replica_offset, self.nreplicas_global, self.ntemps, self.seed, int(kernel), 0)
-        check(lib.pymc_create(C.byref(p), C.byref(self._h)))
+        self.slab = slab  # (index, count): this handle owns one row slab of the lenX x lenY lattice
+        if slab is None:
+            check(lib.pymc_create(C.byref(p), C.byref(self._h)))
+        else:
+            check(lib.pymc_create_slab(C.byref(p), int(slab[0]), int(slab[1]), C.byref(self._h)))
+            self.rows = self.lenX // int(slab[1])
         self._tracked_cache = None  # (bond, second) valid until the configurations change
 
     # -- lifetime
@@ -206,17 +219,20 @@ class Lattices:
         check(lib.pymc_synchronize(self._h))
 
     # -- configurations
+    def _local_shape(self):
+        return (self.rows if self.slab else self.lenX, self.lenY)
+
     def upload(self, replica, config_int8):
         a = np.ascontiguousarray(config_int8, dtype=np.int8)
-        if a.shape != (self.lenX, self.lenY):
-            raise ValueError("config shape %s, lattice is %dx%d" % (a.shape, self.lenX, self.lenY))
+        if a.shape != self._local_shape():
+            raise ValueError("config shape %s, lattice (slab) is %dx%d" % ((a.shape,) + self._local_shape()))
         self._tracked_cache = None
         check(lib.pymc_upload_config(self._h, replica, _ptr(a), a.size))
 
     def download(self, replica, out=None):
         if out is None:
-            out = np.empty((self.lenX, self.lenY), dtype=np.int8)
-        assert out.dtype == np.int8 and out.flags.c_contiguous and out.size == self.nsites
+            out = np.empty(self._local_shape(), dtype=np.int8)
+        assert out.dtype == np.int8 and out.flags.c_contiguous and out.size == int(np.prod(self._local_shape()))
         check(lib.pymc_download_config(self._h, replica, _ptr(out), out.size))
         return out
 
@@ -311,6 +327,27 @@ class Lattices:
     @pair_counter.setter
     def pair_counter(self, v):
         check(lib.pymc_set_pair_counter(self._h, int(v)))
+
+    # -- row slabs (one lattice over several GPUs)
+    def slab_ipc_export(self):
+        buf = (C.c_char * 192)()
+        check(lib.pymc_slab_ipc_export(self._h, buf, 192))
+        return bytes(buf)
+
+    def slab_connect(self, up_handles, down_handles):
+        check(lib.pymc_slab_connect(self._h, C.c_char_p(up_handles), C.c_char_p(down_handles), 192))
+
+    def slab_connect_local(self, up, down):
+        check(lib.pymc_slab_connect_local(self._h, up._h, down._h))
+
+    def slab_push_halos(self):
+        self._tracked_cache = None
+        check(lib.pymc_slab_push_halos(self._h))
+
+    def slab_status(self):
+        st = C.c_int(0)
+        check(lib.pymc_slab_status(self._h, C.byref(st)))
+        return st.value
 
     # -- device-side statistics
     NSTAT = 6

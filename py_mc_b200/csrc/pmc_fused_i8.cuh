@@ -16,6 +16,11 @@
 //   colour 1: rows i0 .. i0+31 (256 words); its inputs are rows i0-2 .. i0+33 of old colour 1 for the
 //     colour-0 update.
 // Needs lenX % 32 == 0 and (lenY/128) % 8 == 0; other shapes use the two-pass kernel.
+//
+// Slab mode (one lattice split by rows over several GPUs, pymc_create_slab): the local arrays carry two
+// halo rows on either side, the tiles cover the owned rows only, the random stream is indexed by the row of
+// the whole lattice, and phase C also writes the first and last two owned rows into the neighbours' halo
+// rows through peer pointers -- compute and halo exchange in one kernel.
 #pragma once
 #include "pmc_tiled_i8.cuh"
 
@@ -29,7 +34,8 @@ constexpr int FUSED_TW = 8, FUSED_TH = 32, FUSED_THREADS = 256;
 // grid = (nw / 8, lenX / 32, nrep)
 template <int MODEL, class LatT>
 __global__ void __launch_bounds__(FUSED_THREADS, PMC_FUSED_MINBLOCKS)
-    sweep_fused_i8_kernel(LatT L, const int8_t *__restrict__ src, int8_t *__restrict__ dst, uint64_t sweep) {
+    sweep_fused_i8_kernel(LatT L, const int8_t *__restrict__ src, int8_t *__restrict__ dst, uint64_t sweep,
+                          int8_t *__restrict__ peer_up, int8_t *__restrict__ peer_dn) {
     constexpr int TW = FUSED_TW, TH = FUSED_TH, CPR = TW * 4;  // 32 chunks of 16 bytes per tile row
     constexpr int NB = (TH + 2) * TW, NW = (TH + 4) * TW;      // 272 / 288 words
     constexpr int NBC = NB * 4, NWC = NW * 4;                  // 1088 / 1152 chunks
@@ -42,8 +48,14 @@ __global__ void __launch_bounds__(FUSED_THREADS, PMC_FUSED_MINBLOCKS)
     uint16_t *s_b16 = reinterpret_cast<uint16_t *>(s_b), *s_w16 = reinterpret_cast<uint16_t *>(s_w);
 
     const int t = threadIdx.x;
-    const int rep = blockIdx.z, w0 = blockIdx.x * TW, i0 = blockIdx.y * TH;
+    const int rep = blockIdx.z, w0 = blockIdx.x * TW, i0 = L.own_lo + blockIdx.y * TH;
     const int lenX = L.lenX, nk = L.nk;
+    // row of the whole lattice (random-stream index); differs from the local row only in slab mode
+    const int row_shift = L.row_shift, lenXg = L.lenX_global;
+    auto grow = [row_shift, lenXg](int i) {
+        int g = i + row_shift;
+        return g < 0 ? g + lenXg : (g >= lenXg ? g - lenXg : g);
+    };
     Plan<MODEL> plan;
     plan.init(L.plans + (size_t)L.rep_to_T[L.rep_offset + rep] * PLAN_WORDS);
     const int8_t *sb = src + (size_t)(rep * 2 + 0) * lenX * nk;
@@ -118,7 +130,7 @@ __global__ void __launch_bounds__(FUSED_THREADS, PMC_FUSED_MINBLOCKS)
                 Sd = (C >> 1) | (in << 63);
             }
             valid = ~0ull;
-            word_idx = (uint32_t)(i * L.nw + w0 + w);
+            word_idx = (uint32_t)(grow(i) * L.nw + w0 + w);
             owned = r >= 1 && r <= TH;
         } else if (item < NB + TH) {
             const int r = item - NB, i = i0 + r;
@@ -133,7 +145,7 @@ __global__ void __launch_bounds__(FUSED_THREADS, PMC_FUSED_MINBLOCKS)
             C = ((bits >> 3) & 1) << lane;
             Sd = ((bits >> 4) & 1) << lane;
             valid = 1ull << lane;
-            word_idx = (uint32_t)(i * L.nw + we);
+            word_idx = (uint32_t)(grow(i) * L.nw + we);
         }
         int b, s2;
         const uint64_t Snew = update_word<MODEL>(S, U, D, C, Sd, valid, plan, word_idx, greplica, 2 * sweep, L.key, b, s2);
@@ -164,7 +176,7 @@ __global__ void __launch_bounds__(FUSED_THREADS, PMC_FUSED_MINBLOCKS)
             Sd = (C >> 1) | (in << 63);
         }
         int b, s2;
-        const uint64_t Snew = update_word<MODEL>(S, U, D, C, Sd, ~0ull, plan, (uint32_t)(i * L.nw + w0 + w), greplica,
+        const uint64_t Snew = update_word<MODEL>(S, U, D, C, Sd, ~0ull, plan, (uint32_t)(grow(i) * L.nw + w0 + w), greplica,
                                                  2 * sweep + 1, L.key, b, s2);
         s_w[(r + 2) * TW + w] = Snew;
         dB += b;
@@ -180,8 +192,26 @@ __global__ void __launch_bounds__(FUSED_THREADS, PMC_FUSED_MINBLOCKS)
         const int idx = t + FUSED_THREADS * j;
         const int r = idx >> 5, c = idx & (CPR - 1);
         const size_t off = (size_t)(i0 + r) * nk + (size_t)w0 * 64;
-        reinterpret_cast<uint4 *>(db + off)[c] = unpack16<MODEL>(s_b16[(r + 1) * CPR + c]);
-        reinterpret_cast<uint4 *>(dw + off)[c] = unpack16<MODEL>(s_w16[(r + 2) * CPR + c]);
+        const uint4 vb = unpack16<MODEL>(s_b16[(r + 1) * CPR + c]), vw = unpack16<MODEL>(s_w16[(r + 2) * CPR + c]);
+        reinterpret_cast<uint4 *>(db + off)[c] = vb;
+        reinterpret_cast<uint4 *>(dw + off)[c] = vw;
+        // Slab mode: my first / last two rows are the neighbours' halo rows.  Store them straight into the
+        // neighbour's destination buffer over NVLink (peer mapping), so no separate exchange step exists.
+        const int ro = i0 + r - L.own_lo, nown = L.own_hi - L.own_lo;
+        int8_t *peer = nullptr;
+        int prow = 0;
+        if (peer_up && ro < 2) {
+            peer = peer_up;
+            prow = L.own_hi + ro;  // the up neighbour's lower halo
+        } else if (peer_dn && ro >= nown - 2) {
+            peer = peer_dn;
+            prow = ro - (nown - 2);  // the down neighbour's upper halo
+        }
+        if (peer) {
+            const size_t poff = (size_t)prow * nk + (size_t)w0 * 64;
+            reinterpret_cast<uint4 *>(peer + (size_t)(rep * 2 + 0) * lenX * nk + poff)[c] = vb;
+            reinterpret_cast<uint4 *>(peer + (size_t)(rep * 2 + 1) * lenX * nk + poff)[c] = vw;
+        }
     }
 
     dB = __reduce_add_sync(0xFFFFFFFFu, dB);

@@ -55,10 +55,11 @@ template <int LAYOUT, int MODEL, class LatT>
 __global__ void __launch_bounds__(256) pack_fast_kernel(LatT L, int rep, const int8_t *__restrict__ natural) {
     const int cpr = L.lenY >> 4;  // chunks per natural row
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool active = idx < L.lenX * cpr;
-    const int i = active ? idx / cpr : 0, c = active ? idx - i * cpr : 0;
+    const bool active = idx < (L.own_hi - L.own_lo) * cpr;
+    const int irow = active ? idx / cpr : 0, c = active ? idx - irow * cpr : 0;
+    const int i = L.own_lo + irow;  // device row; the host image holds the owned rows only
     uint2 even = make_uint2(0, 0), odd = make_uint2(0, 0);
-    if (active) deinterleave16(__ldg(reinterpret_cast<const uint4 *>(natural + (size_t)i * L.lenY) + c), even, odd);
+    if (active) deinterleave16(__ldg(reinterpret_cast<const uint4 *>(natural + (size_t)irow * L.lenY) + c), even, odd);
     const int ce = i & 1, co = ce ^ 1;  // colour of the even / odd columns of row i
     if (LAYOUT == PYMC_LAYOUT_INT8) {
         if (active) {
@@ -85,8 +86,9 @@ template <int LAYOUT, int MODEL, class LatT>
 __global__ void __launch_bounds__(256) unpack_fast_kernel(LatT L, int rep, int8_t *__restrict__ natural) {
     const int cpr = L.lenY >> 4;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= L.lenX * cpr) return;
-    const int i = idx / cpr, c = idx - i * cpr;
+    if (idx >= (L.own_hi - L.own_lo) * cpr) return;
+    const int irow = idx / cpr, c = idx - irow * cpr;
+    const int i = L.own_lo + irow;
     const int ce = i & 1, co = ce ^ 1;
     uint2 even, odd;
     if (LAYOUT == PYMC_LAYOUT_INT8) {
@@ -99,7 +101,7 @@ __global__ void __launch_bounds__(256) unpack_fast_kernel(LatT L, int rep, int8_
         even = unpack8<MODEL>((uint32_t)(we >> sh) & 0xFFu);
         odd = unpack8<MODEL>((uint32_t)(wo >> sh) & 0xFFu);
     }
-    reinterpret_cast<uint4 *>(natural + (size_t)i * L.lenY)[c] = interleave16(even, odd);
+    reinterpret_cast<uint4 *>(natural + (size_t)irow * L.lenY)[c] = interleave16(even, odd);
 }
 
 }  // namespace pmc

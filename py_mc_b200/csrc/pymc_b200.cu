@@ -62,6 +62,10 @@ struct Lat {
     const int32_t *rep_to_T;   // [nrep_global]
     unsigned long long *tracked;  // [nrep][2]
     PhiloxKey key;
+    // Row-slab mode (one lattice split over GPUs): the local arrays hold the owned rows [own_lo, own_hi)
+    // plus two halo rows on either side; global row = local row + row_shift (mod lenX_global).
+    // Whole-lattice mode: own_lo = 0, own_hi = lenX, row_shift = 0, lenX_global = lenX.
+    int own_lo, own_hi, row_shift, lenX_global;
 };
 
 template <int LAYOUT>
@@ -398,12 +402,12 @@ template <int LAYOUT, int MODEL>
 __global__ void __launch_bounds__(256) reduce_kernel(Lat L, unsigned long long *out) {
     const int rep = blockIdx.y;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    const int per_colour = L.lenX * L.nw;
+    const int per_colour = (L.own_hi - L.own_lo) * L.nw;
     int dB = 0, dS = 0;
     if (idx < 2 * per_colour) {
         const int colour = idx / per_colour;
         const int word = idx - colour * per_colour;
-        const int i = word / L.nw, w = word - i * L.nw;
+        const int i = L.own_lo + word / L.nw, w = word % L.nw;
         const int nvalid = min(64, L.nk - 64 * w);
         const uint64_t valid = nvalid == 64 ? ~0ull : ((1ull << nvalid) - 1);
         const bool q = (i + colour) & 1;
@@ -508,6 +512,73 @@ __global__ void propose_kernel(Lat L, int rep, const int32_t *xs, const int32_t 
 }
 
 // ------------------------------------------------------------------------------------------
+// row-slab mode helpers
+// ------------------------------------------------------------------------------------------
+// Hot start of a slab including its halo rows: every row is a pure function of the whole-lattice row
+// index (stream domain 1), so no communication is needed.  Thread per Philox call = 4 sites of one row.
+template <int MODEL>
+__global__ void init_slab_kernel(Lat L) {
+    const int rep = blockIdx.y;
+    const int per_row = L.lenY >> 2;
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (size_t)L.lenX * per_row) return;
+    const int il = (int)(idx / per_row), j4 = (int)(idx - (size_t)il * per_row);
+    int g = il + L.row_shift;
+    g = g < 0 ? g + L.lenX_global : (g >= L.lenX_global ? g - L.lenX_global : g);
+    const size_t call = (size_t)g * per_row + j4;
+    uint4 o = philox4x32_10((uint32_t)call, (uint32_t)(L.rep_offset + rep), 0u, ctr3(DOMAIN_INIT, 0, 0), L.key);
+    const uint32_t x[4] = {o.x, o.y, o.z, o.w};
+    for (int e = 0; e < 4; ++e) {
+        const int j = 4 * j4 + e;
+        const int colour = (il + j) & 1, k = j >> 1;
+        const int up = x[e] >= 0x80000000u;
+        L.i8[((size_t)(rep * 2 + colour) * L.lenX + il) * L.nk + k] = (MODEL == MODEL_ISING) ? (int8_t)(2 * up - 1) : (int8_t)up;
+    }
+}
+
+// Copy my first / last two owned rows (both colours) into the neighbours' halo rows of the buffer with the
+// same index.  grid = (ceil(nk/16 / block), 4 rows, 2*nrep colours)
+__global__ void slab_push_halos_kernel(Lat L, const int8_t *mine, int8_t *peer_up, int8_t *peer_dn) {
+    const int c16 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c16 >= L.nk / 16) return;
+    const int which = blockIdx.y;  // 0,1: first two owned rows -> up neighbour; 2,3: last two -> down neighbour
+    const size_t plane = (size_t)blockIdx.z * L.lenX * L.nk;
+    const int nown = L.own_hi - L.own_lo;
+    int src_row, dst_row;
+    int8_t *peer;
+    if (which < 2) {
+        src_row = L.own_lo + which;
+        dst_row = L.own_hi + which;
+        peer = peer_up;
+    } else {
+        src_row = L.own_lo + nown - 2 + (which - 2);
+        dst_row = which - 2;
+        peer = peer_dn;
+    }
+    const uint4 v = reinterpret_cast<const uint4 *>(mine + plane + (size_t)src_row * L.nk)[c16];
+    reinterpret_cast<uint4 *>(peer + plane + (size_t)dst_row * L.nk)[c16] = v;
+}
+
+// Neighbour barrier over peer memory: publish my epoch to both neighbours, wait for theirs.  One thread.
+// The wait is bounded: if a neighbour does not arrive, an error flag is raised instead of hanging the GPU.
+__global__ void slab_sync_kernel(volatile unsigned long long *my_flags, unsigned long long *up_flags,
+                                 unsigned long long *dn_flags, unsigned long long epoch, int *err,
+                                 long long timeout_cycles) {
+    __threadfence_system();  // my halo stores (previous kernel) are visible before the epoch is
+    *(volatile unsigned long long *)(up_flags + 1) = epoch;  // I am the "down" neighbour of the rank above
+    *(volatile unsigned long long *)(dn_flags + 0) = epoch;  // and the "up" neighbour of the rank below
+    __threadfence_system();
+    const long long t0 = clock64();
+    while (my_flags[0] < epoch || my_flags[1] < epoch) {
+        if (clock64() - t0 > timeout_cycles) {
+            *err = 1;
+            break;
+        }
+    }
+    __threadfence_system();
+}
+
+// ------------------------------------------------------------------------------------------
 // handle
 // ------------------------------------------------------------------------------------------
 struct pymc_handle {
@@ -537,6 +608,16 @@ struct pymc_handle {
     unsigned long long *stats_count;  // [ntemps]
     bool rx_ready;
     uint64_t rx_round;
+    // row-slab mode (pymc_create_slab): see Lat
+    bool slab;
+    int own_lo, own_hi, row_shift, lenX_global, slab_index, nslabs;
+    int8_t *peer_up[2], *peer_dn[2];      // neighbours' two lattice buffers (CUDA IPC mappings); [k] pairs with my buffer k
+    unsigned long long *flags;            // [2] epochs written by the up / down neighbour
+    unsigned long long *peer_up_flags, *peer_dn_flags;
+    int *slab_error;                      // device flag: set if a neighbour did not arrive in time
+    int8_t *buf[2];                       // the two ping-pong buffers by fixed index (i8 / i8_alt swap)
+    uint64_t slab_epoch;
+    bool local_peers;                     // neighbours are handles of this process (pymc_slab_connect_local)
     bool tables_set;
     bool dirty;                    // configurations changed since the tracked observables were based
     uint64_t sweep_counter;
@@ -557,6 +638,10 @@ static Lat make_lat(const pymc_handle *h) {
     L.rep_to_T = h->rep_to_T;
     L.tracked = h->tracked;
     L.key = make_key(h->p.seed);
+    L.own_lo = h->slab ? h->own_lo : 0;
+    L.own_hi = h->slab ? h->own_hi : h->p.lenX;
+    L.row_shift = h->slab ? h->row_shift : 0;
+    L.lenX_global = h->slab ? h->lenX_global : h->p.lenX;
     return L;
 }
 
@@ -625,6 +710,18 @@ int pymc_destroy(pymc_handle *h) {
         cudaFree(h->rx_accepted);
         cudaFree(h->stats);
         cudaFree(h->stats_count);
+        cudaFree(h->flags);
+        cudaFree(h->slab_error);
+        if (h->slab && h->nslabs > 1 && h->peer_up[0] && !h->local_peers) {
+            cudaIpcCloseMemHandle(h->peer_up[0]);
+            cudaIpcCloseMemHandle(h->peer_up[1]);
+            cudaIpcCloseMemHandle(h->peer_up_flags);
+            if (h->peer_dn[0] != h->peer_up[0]) {
+                cudaIpcCloseMemHandle(h->peer_dn[0]);
+                cudaIpcCloseMemHandle(h->peer_dn[1]);
+                cudaIpcCloseMemHandle(h->peer_dn_flags);
+            }
+        }
         if (h->ev0) cudaEventDestroy(h->ev0);
         if (h->ev1) cudaEventDestroy(h->ev1);
         if (h->own_stream) cudaStreamDestroy(h->own_stream);
@@ -745,8 +842,9 @@ int pymc_upload_config(pymc_handle *h, int replica, const int8_t *host, size_t n
     REQUIRE(host, PYMC_ERR_BADARG, "pymc_upload_config: null host pointer");
     REQUIRE(replica >= 0 && replica < h->p.nreplicas, PYMC_ERR_BADARG, "pymc_upload_config: replica %d of %d", replica,
             h->p.nreplicas);
-    REQUIRE(nsites == (size_t)h->p.lenX * h->p.lenY, PYMC_ERR_BADARG, "pymc_upload_config: %zu sites, lattice has %zu",
-            nsites, (size_t)h->p.lenX * h->p.lenY);
+    const size_t want_up = (size_t)(h->slab ? h->own_hi - h->own_lo : h->p.lenX) * h->p.lenY;
+    REQUIRE(nsites == want_up, PYMC_ERR_BADARG, "pymc_upload_config: %zu sites, lattice (or slab) has %zu", nsites,
+            want_up);
     int rc = ensure_staging(h);
     if (rc) return rc;
     CUDA_TRY(cudaMemcpyAsync(h->staging, host, nsites, cudaMemcpyHostToDevice, h->stream));
@@ -754,7 +852,7 @@ int pymc_upload_config(pymc_handle *h, int replica, const int8_t *host, size_t n
     dim3 grid((h->p.lenX * h->nw + 127) / 128, 2);
     const bool fast = h->p.lenY % 16 == 0 && (h->p.layout == PYMC_LAYOUT_INT8 || h->p.lenY % 128 == 0);
     if (fast) {
-        const int nchunks = h->p.lenX * (h->p.lenY / 16);
+        const int nchunks = (h->slab ? h->own_hi - h->own_lo : h->p.lenX) * (h->p.lenY / 16);
 #define CALL_PACKF(LAY, MOD) pack_fast_kernel<LAY, MOD, Lat><<<(nchunks + 255) / 256, 256, 0, h->stream>>>(L, replica, h->staging)
         DISPATCH(h, CALL_PACKF);
 #undef CALL_PACKF
@@ -773,14 +871,15 @@ int pymc_download_config(pymc_handle *h, int replica, int8_t *host, size_t nsite
     REQUIRE(host, PYMC_ERR_BADARG, "pymc_download_config: null host pointer");
     REQUIRE(replica >= 0 && replica < h->p.nreplicas, PYMC_ERR_BADARG, "pymc_download_config: replica %d of %d",
             replica, h->p.nreplicas);
-    REQUIRE(nsites == (size_t)h->p.lenX * h->p.lenY, PYMC_ERR_BADARG,
-            "pymc_download_config: %zu sites, lattice has %zu", nsites, (size_t)h->p.lenX * h->p.lenY);
+    const size_t want_dn = (size_t)(h->slab ? h->own_hi - h->own_lo : h->p.lenX) * h->p.lenY;
+    REQUIRE(nsites == want_dn, PYMC_ERR_BADARG, "pymc_download_config: %zu sites, lattice (or slab) has %zu", nsites,
+            want_dn);
     int rc = ensure_staging(h);
     if (rc) return rc;
     Lat L = make_lat(h);
     dim3 grid((h->p.lenX * h->nw + 127) / 128, 2);
     const bool fast = h->p.lenY % 16 == 0 && (h->p.layout == PYMC_LAYOUT_INT8 || h->p.lenY % 128 == 0);
-    const int nchunks = h->p.lenX * (h->p.lenY / 16);
+    const int nchunks = (h->slab ? h->own_hi - h->own_lo : h->p.lenX) * (h->p.lenY / 16);
 #define CALL_UNPACK(LAY, MOD)                                                                                     \
     if (fast) unpack_fast_kernel<LAY, MOD, Lat><<<(nchunks + 255) / 256, 256, 0, h->stream>>>(L, replica, h->staging); \
     else unpack_kernel<LAY, MOD><<<grid, 128, 0, h->stream>>>(L, replica, h->staging)
@@ -797,6 +896,16 @@ static int rebase_tracked(pymc_handle *h);
 int pymc_init_random(pymc_handle *h) {
     ENTER(h);
     Lat L = make_lat(h);
+    if (h->slab) {
+        const size_t n = (size_t)h->p.lenX * (h->p.lenY / 4);
+        dim3 sgrid((unsigned)((n + 255) / 256), h->p.nreplicas);
+        if (h->p.model == PYMC_MODEL_ISING)
+            init_slab_kernel<MODEL_ISING><<<sgrid, 256, 0, h->stream>>>(L);
+        else
+            init_slab_kernel<MODEL_LATGAS><<<sgrid, 256, 0, h->stream>>>(L);
+        CUDA_TRY(cudaGetLastError());
+        return rebase_tracked(h);
+    }
     if (h->bits) CUDA_TRY(cudaMemsetAsync(h->bits, 0, (size_t)h->p.nreplicas * 2 * h->p.lenX * h->nw * 8, h->stream));
     const size_t ncalls = ((size_t)h->p.lenX * h->p.lenY + 3) / 4;
     dim3 grid((unsigned)((ncalls + 255) / 256), h->p.nreplicas);
@@ -881,9 +990,12 @@ int pymc_get_replica_to_T(pymc_handle *h, int32_t *map, int n) {
 }
 
 static bool uses_fused(const pymc_handle *h) {
+    const int nown = h->slab ? h->own_hi - h->own_lo : h->p.lenX;
     return h->p.layout == PYMC_LAYOUT_INT8 && h->p.kernel == PYMC_KERNEL_AUTO && h->nk % 64 == 0 &&
-           h->nw % FUSED_TW == 0 && h->p.lenX % FUSED_TH == 0;
+           h->nw % FUSED_TW == 0 && nown % FUSED_TH == 0;
 }
+
+static int slab_sync_async(pymc_handle *h);
 
 int pymc_sweep_kernel_info(pymc_handle *h, int *launches_per_sweep, const char **kernel_name) {
     REQUIRE(h, PYMC_ERR_BADARG, "pymc_sweep_kernel_info: null handle");
@@ -908,6 +1020,7 @@ int pymc_sweep(pymc_handle *h, int64_t nsweeps) {
     ENTER(h);
     REQUIRE(nsweeps >= 0, PYMC_ERR_BADARG, "pymc_sweep: nsweeps %lld", (long long)nsweeps);
     REQUIRE(h->tables_set, PYMC_ERR_STATE, "pymc_sweep: call pymc_set_accept_tables first");
+    REQUIRE(!h->slab || h->peer_up[0], PYMC_ERR_STATE, "pymc_sweep: connect the slab to its neighbours first");
     if (h->dirty) {
         int rc = rebase_tracked(h);
         if (rc) return rc;
@@ -921,20 +1034,31 @@ int pymc_sweep(pymc_handle *h, int64_t nsweeps) {
     if (fused && !h->i8_alt && nsweeps > 0)
         CUDA_TRY(cudaMalloc(&h->i8_alt, (size_t)h->p.nreplicas * 2 * h->p.lenX * h->nk));
     if (fused) {
-        dim3 fgrid(h->nw / FUSED_TW, h->p.lenX / FUSED_TH, h->p.nreplicas);
+        dim3 fgrid(h->nw / FUSED_TW, (L.own_hi - L.own_lo) / FUSED_TH, h->p.nreplicas);
         for (int64_t s = 0; s < nsweeps; ++s) {
+            int8_t *pu = nullptr, *pd = nullptr;
+            if (h->slab) {  // the neighbours' destination buffer has the same index as mine (one slab: myself)
+                const int k = h->i8_alt == h->buf[0] ? 0 : 1;
+                pu = h->peer_up[k];
+                pd = h->peer_dn[k];
+            }
             if (h->p.model == PYMC_MODEL_ISING)
-                sweep_fused_i8_kernel<MODEL_ISING, Lat><<<fgrid, FUSED_THREADS, 0, h->stream>>>(L, h->i8, h->i8_alt, h->sweep_counter);
+                sweep_fused_i8_kernel<MODEL_ISING, Lat><<<fgrid, FUSED_THREADS, 0, h->stream>>>(L, h->i8, h->i8_alt, h->sweep_counter, pu, pd);
             else
-                sweep_fused_i8_kernel<MODEL_LATGAS, Lat><<<fgrid, FUSED_THREADS, 0, h->stream>>>(L, h->i8, h->i8_alt, h->sweep_counter);
+                sweep_fused_i8_kernel<MODEL_LATGAS, Lat><<<fgrid, FUSED_THREADS, 0, h->stream>>>(L, h->i8, h->i8_alt, h->sweep_counter, pu, pd);
             int8_t *tmp = h->i8;
             h->i8 = h->i8_alt;
             h->i8_alt = tmp;
             h->sweep_counter++;
+            if (h->slab) {
+                int rc = slab_sync_async(h);
+                if (rc) return rc;
+            }
         }
         CUDA_TRY(cudaGetLastError());
         return PYMC_OK;
     }
+    REQUIRE(!h->slab, PYMC_ERR_UNSUPPORTED, "pymc_sweep: slab handles use the fused int8 kernel only");
     const bool bitrows = h->p.layout == PYMC_LAYOUT_BITS && h->p.kernel != PYMC_KERNEL_GENERIC;
     const int rpt = h->p.lenX % 4 == 0 ? 4 : 2;
     int tw_log2 = 0;
@@ -1037,6 +1161,7 @@ int pymc_propose(pymc_handle *h, int replica, const int32_t *x, const int32_t *y
                  int32_t *nnsum_out) {
     ENTER(h);
     REQUIRE(x && y && site_out && nnsum_out, PYMC_ERR_BADARG, "pymc_propose: null pointer");
+    REQUIRE(!h->slab, PYMC_ERR_UNSUPPORTED, "pymc_propose: not available on slab handles");
     REQUIRE(replica >= 0 && replica < h->p.nreplicas, PYMC_ERR_BADARG, "pymc_propose: replica %d of %d", replica,
             h->p.nreplicas);
     REQUIRE(n >= 0, PYMC_ERR_BADARG, "pymc_propose: n = %d", n);
@@ -1224,6 +1349,7 @@ int pymc_pair_sweep(pymc_handle *h, int64_t nsweeps, uint32_t class_mask) {
     ENTER(h);
     REQUIRE(nsweeps >= 0, PYMC_ERR_BADARG, "pymc_pair_sweep: nsweeps %lld", (long long)nsweeps);
     REQUIRE(h->pair_plans, PYMC_ERR_STATE, "pymc_pair_sweep: call pymc_set_pair_tables first");
+    REQUIRE(!h->slab, PYMC_ERR_UNSUPPORTED, "pymc_pair_sweep: not available on slab handles");
     REQUIRE((class_mask & 0xFFFFu) != 0 && (class_mask >> 16) == 0, PYMC_ERR_BADARG, "pymc_pair_sweep: class mask %#x",
             class_mask);
     if (h->dirty) {
@@ -1475,6 +1601,143 @@ int pymc_stats_get(pymc_handle *h, double *sums, uint64_t *counts, int ntemps, i
             "pymc_stats_get: need [%d][%d] sums", h->p.ntemps, NSTAT);
     CUDA_TRY(cudaMemcpyAsync(sums, h->stats, (size_t)ntemps * NSTAT * 8, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(cudaMemcpyAsync(counts, h->stats_count, (size_t)ntemps * 8, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return PYMC_OK;
+}
+
+
+// ------------------------------------------------------------------------------------------
+// row-slab mode: one lattice split over GPUs
+// ------------------------------------------------------------------------------------------
+static int slab_sync_async(pymc_handle *h) {
+    if (h->nslabs <= 1 || h->local_peers) return PYMC_OK;
+    h->slab_epoch++;
+    slab_sync_kernel<<<1, 1, 0, h->stream>>>(h->flags, h->peer_up_flags, h->peer_dn_flags, h->slab_epoch, h->slab_error,
+                                            4000000000LL);
+    CUDA_TRY(cudaGetLastError());
+    return PYMC_OK;
+}
+
+int pymc_create_slab(const pymc_params *p, int slab_index, int nslabs, pymc_handle **out) {
+    REQUIRE(p && out, PYMC_ERR_BADARG, "pymc_create_slab: null pointer");
+    *out = nullptr;
+    REQUIRE(nslabs >= 1 && slab_index >= 0 && slab_index < nslabs, PYMC_ERR_BADARG, "pymc_create_slab: slab %d of %d",
+            slab_index, nslabs);
+    REQUIRE(p->layout == PYMC_LAYOUT_INT8 && p->kernel == PYMC_KERNEL_AUTO, PYMC_ERR_UNSUPPORTED,
+            "pymc_create_slab: slabs use the int8 layout and the fused sweep kernel");
+    REQUIRE(p->lenX % nslabs == 0 && (p->lenX / nslabs) % FUSED_TH == 0 && p->lenY % (128 * FUSED_TW) == 0,
+            PYMC_ERR_UNSUPPORTED,
+            "pymc_create_slab: need lenX/nslabs %% %d == 0 and lenY %% %d == 0 (got %dx%d over %d slabs)", FUSED_TH,
+            128 * FUSED_TW, p->lenX, p->lenY, nslabs);
+    const int Xl = p->lenX / nslabs;
+    pymc_params q = *p;
+    q.lenX = Xl + 4;  // two halo rows above and below the owned rows
+    pymc_handle *h = nullptr;
+    int rc = pymc_create(&q, &h);
+    if (rc) return rc;
+    h->slab = true;
+    h->own_lo = 2;
+    h->own_hi = Xl + 2;
+    h->row_shift = slab_index * Xl - 2;
+    h->lenX_global = p->lenX;
+    h->slab_index = slab_index;
+    h->nslabs = nslabs;
+    DeviceGuard guard(h->p.device);
+    const size_t bytes = (size_t)h->p.nreplicas * 2 * h->p.lenX * h->nk;
+    cudaError_t e = cudaMalloc(&h->i8_alt, bytes);
+    if (e == cudaSuccess) e = cudaMemset(h->i8_alt, 0, bytes);
+    if (e == cudaSuccess) e = cudaMalloc(&h->flags, 16);
+    if (e == cudaSuccess) e = cudaMemset(h->flags, 0, 16);
+    if (e == cudaSuccess) e = cudaMalloc(&h->slab_error, 4);
+    if (e == cudaSuccess) e = cudaMemset(h->slab_error, 0, 4);
+    if (e != cudaSuccess) {
+        pymc_destroy(h);
+        return fail(PYMC_ERR_CUDA, "pymc_create_slab: %s", cudaGetErrorString(e));
+    }
+    h->buf[0] = h->i8;
+    h->buf[1] = h->i8_alt;
+    if (nslabs == 1) {  // periodic onto myself: my own buffers are my neighbours' buffers
+        h->peer_up[0] = h->peer_dn[0] = h->buf[0];
+        h->peer_up[1] = h->peer_dn[1] = h->buf[1];
+    }
+    *out = h;
+    return PYMC_OK;
+}
+
+// 3 x 64 bytes: CUDA IPC handles of buffer 0, buffer 1 and the flag words, to be handed to both neighbours
+int pymc_slab_ipc_export(pymc_handle *h, void *handles, size_t nbytes) {
+    ENTER(h);
+    REQUIRE(h->slab && handles && nbytes == 3 * sizeof(cudaIpcMemHandle_t), PYMC_ERR_BADARG,
+            "pymc_slab_ipc_export: need a slab handle and %zu bytes", 3 * sizeof(cudaIpcMemHandle_t));
+    cudaIpcMemHandle_t *out = (cudaIpcMemHandle_t *)handles;
+    CUDA_TRY(cudaIpcGetMemHandle(out + 0, h->buf[0]));
+    CUDA_TRY(cudaIpcGetMemHandle(out + 1, h->buf[1]));
+    CUDA_TRY(cudaIpcGetMemHandle(out + 2, h->flags));
+    return PYMC_OK;
+}
+
+int pymc_slab_connect(pymc_handle *h, const void *up_handles, const void *dn_handles, size_t nbytes) {
+    ENTER(h);
+    REQUIRE(h->slab && h->nslabs > 1, PYMC_ERR_STATE, "pymc_slab_connect: only for slabs with neighbours");
+    REQUIRE(up_handles && dn_handles && nbytes == 3 * sizeof(cudaIpcMemHandle_t), PYMC_ERR_BADARG,
+            "pymc_slab_connect: need two sets of %zu bytes", 3 * sizeof(cudaIpcMemHandle_t));
+    const cudaIpcMemHandle_t *up = (const cudaIpcMemHandle_t *)up_handles, *dn = (const cudaIpcMemHandle_t *)dn_handles;
+    void *pu[3], *pd[3];
+    for (int k = 0; k < 3; ++k) CUDA_TRY(cudaIpcOpenMemHandle(&pu[k], up[k], cudaIpcMemLazyEnablePeerAccess));
+    const bool same = memcmp(up, dn, nbytes) == 0;  // two slabs: the neighbour above is the neighbour below
+    for (int k = 0; k < 3; ++k) {
+        if (same)
+            pd[k] = pu[k];
+        else
+            CUDA_TRY(cudaIpcOpenMemHandle(&pd[k], dn[k], cudaIpcMemLazyEnablePeerAccess));
+    }
+    h->peer_up[0] = (int8_t *)pu[0];
+    h->peer_up[1] = (int8_t *)pu[1];
+    h->peer_up_flags = (unsigned long long *)pu[2];
+    h->peer_dn[0] = (int8_t *)pd[0];
+    h->peer_dn[1] = (int8_t *)pd[1];
+    h->peer_dn_flags = (unsigned long long *)pd[2];
+    return PYMC_OK;
+}
+
+// Neighbours that live in the same process (several slabs driven by one host thread, possibly on one GPU):
+// plain pointers instead of IPC mappings, and no flag barrier -- the caller orders the work itself by
+// putting all slabs on one stream and issuing one sweep per slab in turn.
+int pymc_slab_connect_local(pymc_handle *h, pymc_handle *up, pymc_handle *down) {
+    ENTER(h);
+    REQUIRE(h->slab && up && down && up->slab && down->slab, PYMC_ERR_BADARG, "pymc_slab_connect_local: slab handles only");
+    REQUIRE(up->p.lenX == h->p.lenX && down->p.lenX == h->p.lenX && up->nk == h->nk && down->nk == h->nk,
+            PYMC_ERR_BADARG, "pymc_slab_connect_local: slabs of different shape");
+    h->peer_up[0] = up->buf[0];
+    h->peer_up[1] = up->buf[1];
+    h->peer_dn[0] = down->buf[0];
+    h->peer_dn[1] = down->buf[1];
+    h->peer_up_flags = h->peer_dn_flags = nullptr;
+    h->local_peers = true;
+    return PYMC_OK;
+}
+
+// After pymc_upload_config on every slab: make the halo rows consistent (collective over the neighbours).
+int pymc_slab_push_halos(pymc_handle *h) {
+    ENTER(h);
+    REQUIRE(h->slab, PYMC_ERR_STATE, "pymc_slab_push_halos: not a slab handle");
+    REQUIRE(h->nslabs == 1 || h->peer_up[0], PYMC_ERR_STATE, "pymc_slab_push_halos: call pymc_slab_connect first");
+    Lat L = make_lat(h);
+    const int k = h->i8 == h->buf[0] ? 0 : 1;
+    dim3 grid((h->nk / 16 + 127) / 128, 4, 2 * h->p.nreplicas);
+    slab_push_halos_kernel<<<grid, 128, 0, h->stream>>>(L, h->i8, h->peer_up[k], h->peer_dn[k]);
+    CUDA_TRY(cudaGetLastError());
+    int rc = slab_sync_async(h);
+    if (rc) return rc;
+    h->dirty = true;
+    return PYMC_OK;
+}
+
+// 0 = fine; 1 = a neighbour did not reach a barrier within the time limit (results are invalid)
+int pymc_slab_status(pymc_handle *h, int *status) {
+    ENTER(h);
+    REQUIRE(h->slab && status, PYMC_ERR_BADARG, "pymc_slab_status: bad arguments");
+    CUDA_TRY(cudaMemcpyAsync(status, h->slab_error, 4, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(cudaStreamSynchronize(h->stream));
     return PYMC_OK;
 }
