@@ -50,10 +50,6 @@ __device__ __forceinline__ uint4 unpack16(uint32_t bits) {
     return make_uint4(w[0], w[1], w[2], w[3]);
 }
 
-struct TileShape {
-    int tw_log2;  // TW = 1 << tw_log2 words per tile row (TW divides nw), TH = 256 / TW rows
-};
-
 constexpr int TILE_THREADS = 256;
 #ifndef PMC_TILED_MINBLOCKS
 #define PMC_TILED_MINBLOCKS 6
