@@ -290,4 +290,14 @@ class CanonicalMonteCarlo:
         return None
 
 
+def swap_configs(MCreplicas, rep, accept_count):
+    """Exchange configuration and energy of replicas ``rep`` and ``rep + 1`` (mc.py:220-229; the helper of
+    the reference's disabled single-process ``TemperatureReplicaExchange``).  Host-side: it swaps the
+    objects, whatever engine they belong to."""
+    a, b = MCreplicas[rep], MCreplicas[rep + 1]
+    a.config, b.config = b.config, a.config
+    a.energy, b.energy = b.energy, a.energy
+    return MCreplicas, accept_count + 1
+
+
 _default_observer = observer_base()  # one shared instance, as the reference's default argument (mc.py:188)

@@ -115,3 +115,22 @@ def test_non_device_model_is_rejected(workdir):
     from py_mc_b200.mc import CanonicalMonteCarlo, model
     with pytest.raises(TypeError, match="no CPU fallback"):
         CanonicalMonteCarlo(model(), 1.0, object()).run(1)
+
+
+def test_swap_configs_helper(workdir):
+    from py_mc_b200.ising2D import ising2D, ising2D_config
+    from py_mc_b200.mc import CanonicalMonteCarlo, swap_configs
+    model = ising2D(-1.0)
+    reps = []
+    for kT in (1.5, 3.0):
+        c = ising2D_config(6, 6)
+        c.prepare_random()
+        calc = CanonicalMonteCarlo(model, kT, c)
+        calc.run(3)
+        reps.append(calc)
+    c0, c1, e0, e1 = reps[0].config, reps[1].config, reps[0].energy, reps[1].energy
+    reps, n = swap_configs(reps, 0, 0)
+    assert n == 1 and reps[0].config is c1 and reps[1].config is c0
+    assert (reps[0].energy, reps[1].energy) == (e1, e0)
+    reps[0].run(2)  # the engines keep working on the swapped configurations
+    assert reps[0].energy == model.energy(reps[0].config)

@@ -127,3 +127,39 @@ def test_exchange_acceptance_statistics():
     assert np.array_equal(lat.get_replica_to_T(), ref_map)
     tried, acc = lat.rx_stats()
     assert 0 < acc.sum() < tried.sum()
+
+
+def test_lattice_gas_replica_exchange_matches_oracle_replay():
+    """Exchange with the two-term energy J*B + (Eads-mu)*N of the lattice gas (latgas.py:17-25): the device
+    forms it without FMA contraction, so the decisions equal the host's float64 arithmetic."""
+    from py_mc_b200 import _cabi
+    from py_mc_b200.latgas import latticegas
+    from oracle import latgas as o_latgas
+    R, lenX, lenY, seed = 6, 8, 12, 2025
+    J, Eads, mu = -0.75, -0.5, 0.125
+    kTs = np.linspace(0.6, 1.4, R)
+    model = latticegas(Eads=Eads, J=J, mu=mu)
+    lat = _cabi.Lattices(_cabi.MODEL_LATGAS, lenX, lenY, nreplicas=R, ntemps=R, seed=seed)
+    lat.init_random()
+    lat.set_accept_tables(np.array([model._pmc_thresholds(kT) for kT in kTs]))
+    lat.rx_setup(1.0 / kTs, *model._pmc_energy_coeffs())
+    cfgs = [o_latgas.init_config(seed, r, lenX, lenY) for r in range(R)]
+    thr = [o_latgas.threshold_table(J, Eads, mu, kT) for kT in kTs]
+    rank_to_T = np.arange(R)
+    scheme = 0
+    for s in range(1, 25):
+        lat.sweep(1)
+        for r in range(R):
+            o_latgas.sweep(cfgs[r], thr[rank_to_T[r]], seed, r, s - 1)
+        if s % 2 == 0:
+            lat.rx_energies()
+            lat.rx_exchange(scheme)
+            E = [o_latgas.energy(c, J, Eads, mu) for c in cfgs]
+            assert np.array_equal(lat.rx_get_energies(), np.array(E))  # bit-exact float64 energies
+            o_rx.xtrial(rank_to_T, E, 1.0 / kTs, scheme, seed, s // 2 - 1)
+            scheme ^= 1
+        assert np.array_equal(lat.get_replica_to_T(), rank_to_T), s
+    for r in range(R):
+        assert np.array_equal(lat.download(r), cfgs[r])
+    tried, acc = lat.rx_stats()
+    assert acc.sum() > 0
