@@ -27,15 +27,29 @@
 namespace pmc {
 
 constexpr int FUSED_TW = 8, FUSED_TH = 32, FUSED_THREADS = 256;
+
+// Neighbour synchronisation of the slab mode, carried by the sweep kernel itself (null `mine` = off).
+// Every rank counts collective steps; after finishing step n it writes n into the flag words its two
+// neighbours poll.  The tiles of step n+1 that touch a neighbour (first / last tile row: they read halo
+// rows that neighbour wrote during step n and write halo rows it read during step n) wait until that
+// neighbour's flag says n; all other tiles start at once.  The last block of the grid to finish publishes
+// this rank's step number.  Waits are bounded; a time-out raises *err instead of hanging the GPU.
+struct SlabSync {
+    unsigned long long *mine;  // [2]: written by the up / down neighbour
+    unsigned long long *up, *dn;  // the neighbours' flag words
+    unsigned long long wait_epoch, signal_epoch;
+    unsigned int *done;  // [2] counters of finished top-row / bottom-row tiles of this launch
+    int *err;
+};
 #ifndef PMC_FUSED_MINBLOCKS
 #define PMC_FUSED_MINBLOCKS 4
 #endif
 
 // grid = (nw / 8, lenX / 32, nrep)
-template <int MODEL, class LatT>
+template <int MODEL, bool SLAB, class LatT>
 __global__ void __launch_bounds__(FUSED_THREADS, PMC_FUSED_MINBLOCKS)
     sweep_fused_i8_kernel(LatT L, const int8_t *__restrict__ src, int8_t *__restrict__ dst, uint64_t sweep,
-                          int8_t *__restrict__ peer_up, int8_t *__restrict__ peer_dn) {
+                          int8_t *__restrict__ peer_up, int8_t *__restrict__ peer_dn, SlabSync sync) {
     constexpr int TW = FUSED_TW, TH = FUSED_TH, CPR = TW * 4;  // 32 chunks of 16 bytes per tile row
     constexpr int NB = (TH + 2) * TW, NW = (TH + 4) * TW;      // 272 / 288 words
     constexpr int NBC = NB * 4, NWC = NW * 4;                  // 1088 / 1152 chunks
@@ -48,11 +62,16 @@ __global__ void __launch_bounds__(FUSED_THREADS, PMC_FUSED_MINBLOCKS)
     uint16_t *s_b16 = reinterpret_cast<uint16_t *>(s_b), *s_w16 = reinterpret_cast<uint16_t *>(s_w);
 
     const int t = threadIdx.x;
-    const int rep = blockIdx.z, w0 = blockIdx.x * TW, i0 = L.own_lo + blockIdx.y * TH;
+    // tile rows are issued boundary first (top, bottom, then the interior) so that in slab mode the rows the
+    // neighbours are waiting for leave early
+    const int ntr = gridDim.y;
+    const int tile_row = !(SLAB && sync.mine) ? (int)blockIdx.y : (blockIdx.y == 0 ? 0 : (blockIdx.y == 1 ? ntr - 1 : (int)blockIdx.y - 1));
+    const int rep = blockIdx.z, w0 = blockIdx.x * TW, i0 = (SLAB ? L.own_lo : 0) + tile_row * TH;
     const int lenX = L.lenX, nk = L.nk;
     // row of the whole lattice (random-stream index); differs from the local row only in slab mode
     const int row_shift = L.row_shift, lenXg = L.lenX_global;
     auto grow = [row_shift, lenXg](int i) {
+        if (!SLAB) return i;
         int g = i + row_shift;
         return g < 0 ? g + lenXg : (g >= lenXg ? g - lenXg : g);
     };
@@ -62,6 +81,22 @@ __global__ void __launch_bounds__(FUSED_THREADS, PMC_FUSED_MINBLOCKS)
     const int8_t *sw = src + (size_t)(rep * 2 + 1) * lenX * nk;
     auto wrap_row = [lenX](int i) { return i < 0 ? i + lenX : (i >= lenX ? i - lenX : i); };
     auto wrap_k = [nk](int k) { return k < 0 ? k + nk : (k >= nk ? k - nk : k); };
+
+    if (SLAB && sync.mine) {  // slab mode: boundary tiles wait for the neighbour they share rows with
+        const bool top = tile_row == 0, bottom = tile_row == ntr - 1;
+        if ((top || bottom) && t == 0) {
+            volatile unsigned long long *f = sync.mine;
+            const long long t0 = clock64();
+            while ((top && f[0] < sync.wait_epoch) || (bottom && f[1] < sync.wait_epoch)) {
+                if (clock64() - t0 > 4000000000LL) {
+                    *sync.err = 1;
+                    break;
+                }
+            }
+            __threadfence_system();
+        }
+        if (top || bottom) __syncthreads();
+    }
 
     // ---- phase A: load both colours with halo (128-bit, coalesced), pack, park --------------------
 #pragma unroll
@@ -200,7 +235,8 @@ __global__ void __launch_bounds__(FUSED_THREADS, PMC_FUSED_MINBLOCKS)
         const int ro = i0 + r - L.own_lo, nown = L.own_hi - L.own_lo;
         int8_t *peer = nullptr;
         int prow = 0;
-        if (peer_up && ro < 2) {
+        if (!SLAB) {
+        } else if (peer_up && ro < 2) {
             peer = peer_up;
             prow = L.own_hi + ro;  // the up neighbour's lower halo
         } else if (peer_dn && ro >= nown - 2) {
@@ -226,6 +262,25 @@ __global__ void __launch_bounds__(FUSED_THREADS, PMC_FUSED_MINBLOCKS)
 #pragma unroll
         for (int k = 0; k < 8; ++k) v += s_red[t][k];
         if (v) atomicAdd(L.tracked + 2 * (size_t)rep + t, (unsigned long long)(long long)v);
+    }
+    if (SLAB && sync.mine && (tile_row == 0 || tile_row == ntr - 1)) {
+        // Only the boundary tiles read my halo rows and write the neighbours': when the last tile of the top
+        // (bottom) row is done, the up (down) neighbour may go on -- usually long before this kernel ends.
+        __threadfence_system();
+        __syncthreads();
+        if (t == 0) {
+            const unsigned int per_row = gridDim.x * gridDim.z;
+            if (tile_row == 0 && atomicAdd(sync.done + 0, 1u) == per_row - 1) {
+                sync.done[0] = 0;
+                __threadfence_system();
+                *(volatile unsigned long long *)(sync.up + 1) = sync.signal_epoch;
+            }
+            if (tile_row == ntr - 1 && atomicAdd(sync.done + 1, 1u) == per_row - 1) {
+                sync.done[1] = 0;
+                __threadfence_system();
+                *(volatile unsigned long long *)(sync.dn + 0) = sync.signal_epoch;
+            }
+        }
     }
 }
 

@@ -617,6 +617,8 @@ struct pymc_handle {
     int *slab_error;                      // device flag: set if a neighbour did not arrive in time
     int8_t *buf[2];                       // the two ping-pong buffers by fixed index (i8 / i8_alt swap)
     uint64_t slab_epoch;
+    unsigned int *slab_done;              // block counter used by the in-kernel barrier
+    bool dirty_halo;                      // neighbours may still be writing my halo rows (wait before reading them)
     bool local_peers;                     // neighbours are handles of this process (pymc_slab_connect_local)
     bool tables_set;
     bool dirty;                    // configurations changed since the tracked observables were based
@@ -712,6 +714,7 @@ int pymc_destroy(pymc_handle *h) {
         cudaFree(h->stats_count);
         cudaFree(h->flags);
         cudaFree(h->slab_error);
+        cudaFree(h->slab_done);
         if (h->slab && h->nslabs > 1 && h->peer_up[0] && !h->local_peers) {
             cudaIpcCloseMemHandle(h->peer_up[0]);
             cudaIpcCloseMemHandle(h->peer_up[1]);
@@ -1042,18 +1045,32 @@ int pymc_sweep(pymc_handle *h, int64_t nsweeps) {
                 pu = h->peer_up[k];
                 pd = h->peer_dn[k];
             }
-            if (h->p.model == PYMC_MODEL_ISING)
-                sweep_fused_i8_kernel<MODEL_ISING, Lat><<<fgrid, FUSED_THREADS, 0, h->stream>>>(L, h->i8, h->i8_alt, h->sweep_counter, pu, pd);
-            else
-                sweep_fused_i8_kernel<MODEL_LATGAS, Lat><<<fgrid, FUSED_THREADS, 0, h->stream>>>(L, h->i8, h->i8_alt, h->sweep_counter, pu, pd);
+            SlabSync sync;
+            memset(&sync, 0, sizeof(sync));
+            if (h->slab && h->nslabs > 1 && !h->local_peers) {  // neighbour barrier carried by the sweep kernel
+                sync.mine = h->flags;
+                sync.up = h->peer_up_flags;
+                sync.dn = h->peer_dn_flags;
+                sync.wait_epoch = h->slab_epoch;
+                sync.signal_epoch = ++h->slab_epoch;
+                sync.done = h->slab_done;
+                sync.err = h->slab_error;
+            }
+#define LAUNCH_FUSED(MOD, SLB) \
+    sweep_fused_i8_kernel<MOD, SLB, Lat><<<fgrid, FUSED_THREADS, 0, h->stream>>>(L, h->i8, h->i8_alt, h->sweep_counter, pu, pd, sync)
+            if (h->p.model == PYMC_MODEL_ISING) {
+                if (h->slab) LAUNCH_FUSED(MODEL_ISING, true);
+                else LAUNCH_FUSED(MODEL_ISING, false);
+            } else {
+                if (h->slab) LAUNCH_FUSED(MODEL_LATGAS, true);
+                else LAUNCH_FUSED(MODEL_LATGAS, false);
+            }
+#undef LAUNCH_FUSED
             int8_t *tmp = h->i8;
             h->i8 = h->i8_alt;
             h->i8_alt = tmp;
             h->sweep_counter++;
-            if (h->slab) {
-                int rc = slab_sync_async(h);
-                if (rc) return rc;
-            }
+            if (h->slab) h->dirty_halo = true;  // my halo rows are complete only once the neighbours' step is
         }
         CUDA_TRY(cudaGetLastError());
         return PYMC_OK;
@@ -1110,8 +1127,14 @@ int pymc_set_sweep_counter(pymc_handle *h, uint64_t counter) {
 }
 
 // recompute bond/second into h->reduced and copy them over the tracked values (all async)
+static int slab_wait_async(pymc_handle *h);
+
 static int rebase_tracked(pymc_handle *h) {
     Lat L = make_lat(h);
+    {
+        int rc = slab_wait_async(h);
+        if (rc) return rc;
+    }
     CUDA_TRY(cudaMemsetAsync(h->reduced, 0, (size_t)h->p.nreplicas * 16, h->stream));
     dim3 grid((2 * h->p.lenX * h->nw + 255) / 256, h->p.nreplicas);
 #define CALL_REDUCE(LAY, MOD) reduce_kernel<LAY, MOD><<<grid, 256, 0, h->stream>>>(L, h->reduced)
@@ -1609,6 +1632,27 @@ int pymc_stats_get(pymc_handle *h, double *sums, uint64_t *counts, int ntemps, i
 // ------------------------------------------------------------------------------------------
 // row-slab mode: one lattice split over GPUs
 // ------------------------------------------------------------------------------------------
+__global__ void slab_wait_kernel(volatile unsigned long long *my_flags, unsigned long long epoch, int *err) {
+    const long long t0 = clock64();
+    while (my_flags[0] < epoch || my_flags[1] < epoch) {
+        if (clock64() - t0 > 4000000000LL) {
+            *err = 1;
+            break;
+        }
+    }
+    __threadfence_system();
+}
+
+// Before my halo rows are read outside a sweep (observables): the neighbours must have finished the step
+// in which they wrote them.
+static int slab_wait_async(pymc_handle *h) {
+    if (!h->slab || h->nslabs <= 1 || h->local_peers || !h->dirty_halo) return PYMC_OK;
+    slab_wait_kernel<<<1, 1, 0, h->stream>>>(h->flags, h->slab_epoch, h->slab_error);
+    CUDA_TRY(cudaGetLastError());
+    h->dirty_halo = false;
+    return PYMC_OK;
+}
+
 static int slab_sync_async(pymc_handle *h) {
     if (h->nslabs <= 1 || h->local_peers) return PYMC_OK;
     h->slab_epoch++;
@@ -1650,6 +1694,8 @@ int pymc_create_slab(const pymc_params *p, int slab_index, int nslabs, pymc_hand
     if (e == cudaSuccess) e = cudaMemset(h->flags, 0, 16);
     if (e == cudaSuccess) e = cudaMalloc(&h->slab_error, 4);
     if (e == cudaSuccess) e = cudaMemset(h->slab_error, 0, 4);
+    if (e == cudaSuccess) e = cudaMalloc(&h->slab_done, 8);
+    if (e == cudaSuccess) e = cudaMemset(h->slab_done, 0, 8);
     if (e != cudaSuccess) {
         pymc_destroy(h);
         return fail(PYMC_ERR_CUDA, "pymc_create_slab: %s", cudaGetErrorString(e));
