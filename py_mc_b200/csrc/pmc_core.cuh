@@ -77,7 +77,13 @@ __device__ __forceinline__ uint64_t decide_hard(const uint64_t (&hm)[MAXH], cons
 #pragma unroll
 #endif
     for (uint32_t call = 0; call < HEAD_PLANES / 2; ++call) {
+#ifdef PMC_HEAD_CHECK_EVERY_CALL
         if (!__any_sync(0xFFFFFFFFu, und != 0)) break;
+#else
+        // one check before the first block (a warp whose lanes all accept unconditionally draws nothing);
+        // after that some lane of 2048 is practically always still open, so the test would be wasted work
+        if (call == 0 && !__any_sync(0xFFFFFFFFu, und != 0)) break;
+#endif
         uint64_t pe, po;
         word_planes(word_idx, replica, step, domain, call, key, pe, po);
         const int be = 31 - 2 * (int)call, bo = be - 1;

@@ -216,3 +216,29 @@ def test_fused_two_pass_and_generic_kernels_agree(shape, nrep):
         assert np.array_equal(lat.tracked()[1], lats["generic"].tracked()[1]), name
         b, m = lat.reduce_observables()
         assert np.array_equal(b, lats["generic"].tracked()[0]) and np.array_equal(m, lats["generic"].tracked()[1])
+
+
+def test_large_lattice_against_scalar_c_oracle():
+    """4096 x 4096 (256 fused tiles per colour-row block, 8 tiles wide): all three int8/bit kernels against the
+    independent scalar C restatement, configuration and tracked sums."""
+    from oracle import cbuild
+    c = _cabi()
+    co = cbuild.load()
+    L, seed, kT, nsweeps = 4096, 808, 2.269185314213022, 3
+    thr = o_ising.threshold_table(-1.0, kT)[1]
+    ref = co.init(L, L, seed, 0)
+    B, M = co.observables(ref)
+    lats = []
+    for layout, kernel in ((INT8, c.KERNEL_AUTO), (INT8, c.KERNEL_TWO_PASS), (BITS, c.KERNEL_AUTO)):
+        lat = c.Lattices(c.MODEL_ISING, L, L, seed=seed, layout=layout, kernel=kernel)
+        lat.init_random()
+        lat.set_accept_tables(thr[None, :])
+        lat.sweep(nsweeps)
+        lats.append(lat)
+    for sw in range(nsweeps):
+        _, dB, dM = co.sweep(ref, thr, seed, 0, sw)
+        B, M = B + dB, M + dM
+    for lat in lats:
+        assert np.array_equal(lat.download(0), ref), lat.sweep_kernel_info()
+        b, m = lat.tracked()
+        assert (int(b[0]), int(m[0])) == (B, M)
