@@ -52,7 +52,7 @@ __device__ __forceinline__ uint4 unpack16(uint32_t bits) {
 
 constexpr int TILE_THREADS = 256;
 #ifndef PMC_TILED_MINBLOCKS
-#define PMC_TILED_MINBLOCKS 6
+#define PMC_TILED_MINBLOCKS 5
 #endif
 
 // grid = (nw / TW, ceil(lenX / TH), nrep)
