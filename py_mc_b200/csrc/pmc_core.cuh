@@ -129,6 +129,18 @@ __device__ __forceinline__ uint64_t decide_hard(const uint64_t (&hm)[MAXH], cons
 // ------------------------------------------------------------------------------------------
 constexpr int PLAN_WORDS = 16;  // 32-bit words per temperature in the device plan table
 
+// Where a thread reads its plan row from: the global table (one row per temperature, indexed through
+// replica_to_T), or -- when the handle has a single temperature -- a copy of the row carried in the kernel
+// parameters, i.e. in constant memory, which costs no load instruction and is known to be warp-uniform.
+struct GlobalRow {
+    const uint32_t *p;
+    __device__ __forceinline__ uint32_t operator[](int k) const { return __ldg(p + k); }
+};
+struct ParamRow {
+    const uint32_t (&a)[PLAN_WORDS];
+    __device__ __forceinline__ uint32_t operator[](int k) const { return a[k]; }
+};
+
 template <int MODEL>
 struct Plan;
 
@@ -143,13 +155,14 @@ struct Plan<MODEL_ISING> {
     uint64_t en3, en4;  // ~0 where the class needs a draw
     uint32_t ht[2];
     int sign;           // +1 / -1: orientation of the bond-sum change
-    __device__ __forceinline__ void init(const uint32_t *__restrict__ row) {
-        notmask = __ldg(row + 0) ? ~0ull : 0ull;
-        ht[0] = __ldg(row + 1);
-        ht[1] = __ldg(row + 2);
-        en3 = __ldg(row + 3) ? ~0ull : 0ull;
-        en4 = __ldg(row + 4) ? ~0ull : 0ull;
-        sign = __ldg(row + 5) ? -1 : 1;
+    template <class Row>
+    __device__ __forceinline__ void init(const Row row) {
+        notmask = row[0] ? ~0ull : 0ull;
+        ht[0] = row[1];
+        ht[1] = row[2];
+        en3 = row[3] ? ~0ull : 0ull;
+        en4 = row[4] ? ~0ull : 0ull;
+        sign = row[5] ? -1 : 1;
     }
     static __host__ void build_row(const uint32_t *thr, uint32_t *row) {
         const bool low = thr[0] != THR_ALWAYS || thr[1] != THR_ALWAYS;
@@ -172,12 +185,13 @@ struct Plan<MODEL_LATGAS> {
     uint64_t sel[5];  // XOR-ed with S: result 1 = lane is in the hard occupancy for this nn
     uint64_t en[5];   // ~0 if that nn has a hard class at all
     uint32_t ht[5];
-    __device__ __forceinline__ void init(const uint32_t *__restrict__ row) {
+    template <class Row>
+    __device__ __forceinline__ void init(const Row row) {
 #pragma unroll
         for (int n = 0; n < 5; ++n) {
-            sel[n] = __ldg(row + n) ? ~0ull : 0ull;
-            ht[n] = __ldg(row + 5 + n);
-            en[n] = __ldg(row + 10 + n) ? ~0ull : 0ull;
+            sel[n] = row[n] ? ~0ull : 0ull;
+            ht[n] = row[5 + n];
+            en[n] = row[10 + n] ? ~0ull : 0ull;
         }
     }
     static __host__ void build_row(const uint32_t *thr, uint32_t *row) {

@@ -76,7 +76,7 @@ __global__ void __launch_bounds__(FUSED_THREADS, PMC_FUSED_MINBLOCKS)
         return g < 0 ? g + lenXg : (g >= lenXg ? g - lenXg : g);
     };
     Plan<MODEL> plan;
-    plan.init(L.plans + (size_t)L.rep_to_T[L.rep_offset + rep] * PLAN_WORDS);
+    fetch_plan(L, rep, plan);
     const int8_t *sb = src + (size_t)(rep * 2 + 0) * lenX * nk;
     const int8_t *sw = src + (size_t)(rep * 2 + 1) * lenX * nk;
     auto wrap_row = [lenX](int i) { return i < 0 ? i + lenX : (i >= lenX ? i - lenX : i); };

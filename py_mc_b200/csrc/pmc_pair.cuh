@@ -24,12 +24,13 @@ struct PairPlan {
     uint64_t notmask;  // 0: hard moves lose neighbours (J < 0); ~0: hard moves gain neighbours (J > 0)
     uint64_t en[3];
     uint32_t ht[3];
-    __device__ __forceinline__ void init(const uint32_t *__restrict__ row) {
-        notmask = __ldg(row + 0) ? 0ull : ~0ull;
+    template <class Row>
+    __device__ __forceinline__ void init(const Row row) {
+        notmask = row[0] ? 0ull : ~0ull;
 #pragma unroll
         for (int e = 0; e < 3; ++e) {
-            ht[e] = __ldg(row + 1 + e);
-            en[e] = __ldg(row + 4 + e) ? ~0ull : 0ull;
+            ht[e] = row[1 + e];
+            en[e] = row[4 + e] ? ~0ull : 0ull;
         }
     }
     // thr[d+3], d = -3..3.  Returns false if the table has dE > 0 on both sides or at d = 0.

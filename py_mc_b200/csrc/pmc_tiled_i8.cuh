@@ -75,7 +75,7 @@ __global__ void __launch_bounds__(TILE_THREADS, PMC_TILED_MINBLOCKS) sweep_tiled
     const int cpr_log2 = tw_log2 + 2;
 
     Plan<MODEL> plan;
-    plan.init(L.plans + (size_t)L.rep_to_T[L.rep_offset + rep] * PLAN_WORDS);
+    fetch_plan(L, rep, plan);
 
     const int8_t *tgt = L.i8 + (size_t)(rep * 2 + colour) * L.lenX * L.nk;
     const int8_t *oth = L.i8 + (size_t)(rep * 2 + oc) * L.lenX * L.nk;

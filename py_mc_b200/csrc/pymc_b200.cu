@@ -66,7 +66,20 @@ struct Lat {
     // plus two halo rows on either side; global row = local row + row_shift (mod lenX_global).
     // Whole-lattice mode: own_lo = 0, own_hi = lenX, row_shift = 0, lenX_global = lenX.
     int own_lo, own_hi, row_shift, lenX_global;
+    // Single-temperature handles: the plan row travels in the kernel parameters (constant memory).
+    int single_plan;
+    uint32_t plan0[PLAN_WORDS];
 };
+
+// Plan of the replica this block works on.
+template <class PlanT>
+__device__ __forceinline__ void fetch_plan(const Lat &L, int rep, PlanT &plan) {
+    if (L.single_plan) {
+        plan.init(ParamRow{L.plan0});
+    } else {
+        plan.init(GlobalRow{L.plans + (size_t)L.rep_to_T[L.rep_offset + rep] * PLAN_WORDS});
+    }
+}
 
 template <int LAYOUT>
 struct Loader;
@@ -206,8 +219,7 @@ __device__ __forceinline__ void block_accumulate(int a, int b, unsigned long lon
 
 template <int MODEL>
 __device__ __forceinline__ void load_plan(const Lat &L, int rep, Plan<MODEL> &plan) {
-    const int t = L.rep_to_T[L.rep_offset + rep];
-    plan.init(L.plans + (size_t)t * PLAN_WORDS);
+    fetch_plan(L, rep, plan);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -322,7 +334,7 @@ __global__ void __launch_bounds__(128) pair_class_kernel(Lat L, int cls, uint64_
     const int nrows = L.lenX / rstride;
     const bool on = idx < nrows * L.nw;
     PairPlan plan;
-    plan.init(L.pair_plans + (size_t)L.rep_to_T[L.rep_offset + rep] * PLAN_WORDS);
+    plan.init(GlobalRow{L.pair_plans + (size_t)L.rep_to_T[L.rep_offset + rep] * PLAN_WORDS});
     uint64_t S = 0, Bw = 0, A0 = 0, A1 = 0, B0 = 0, B1 = 0, active = 0;
     int i = 0, w = 0, nvalid = 64, ca = 0, oc = 1, q = 0, i1 = 0;
     if (on) {
@@ -590,6 +602,7 @@ struct pymc_handle {
     int8_t *i8_alt;                // second int8 buffer for the out-of-place fused sweep (allocated on first use)
     uint64_t *bits;
     uint32_t *plans;               // [ntemps][PLAN_WORDS]
+    uint32_t plan0[PLAN_WORDS];    // host copy of row 0 (passed by value to kernels when ntemps == 1)
     uint32_t *pair_plans;          // [ntemps][PLAN_WORDS], allocated by pymc_set_pair_tables
     uint64_t pair_counter;         // pair-exchange sweeps done (random-stream position)
     int32_t *rep_to_T;
@@ -644,6 +657,8 @@ static Lat make_lat(const pymc_handle *h) {
     L.own_hi = h->slab ? h->own_hi : h->p.lenX;
     L.row_shift = h->slab ? h->row_shift : 0;
     L.lenX_global = h->slab ? h->lenX_global : h->p.lenX;
+    L.single_plan = h->p.ntemps == 1 && h->tables_set;
+    memcpy(L.plan0, h->plan0, sizeof(L.plan0));
     return L;
 }
 
@@ -949,6 +964,7 @@ int pymc_set_accept_tables(pymc_handle *h, const uint32_t *thr, int ntemps, int 
         else
             Plan<MODEL_LATGAS>::build_row(thr + (size_t)t * nclass, rows + (size_t)t * PLAN_WORDS);
     }
+    memcpy(h->plan0, rows, sizeof(h->plan0));
     cudaError_t e = cudaMemcpyAsync(h->plans, rows, (size_t)ntemps * PLAN_WORDS * 4, cudaMemcpyHostToDevice, h->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
     delete[] rows;
