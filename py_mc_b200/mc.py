@@ -245,6 +245,22 @@ class CanonicalMonteCarlo:
         self.config._device_changed()
         self._energy = None
 
+    def _run_device_stats(self, lat, nsteps, sample_frequency, observer):
+        """Sampling on the device (py_mc_b200.observers.device_observer): no host round trip per sample."""
+        lat.stats_reset(*self.model._pmc_energy_coeffs())
+        done = 0
+        while done < nsteps:
+            chunk = min(nsteps - done, sample_frequency - done % sample_frequency)
+            self._sweeps(chunk)
+            done += chunk
+            if done % sample_frequency == 0:
+                lat.stats_accumulate()
+        sums, counts = lat.stats_get()
+        observer._finish(sums, counts, [self.kT])
+        self.energy
+        if counts[0]:
+            return [observer.mean_E[0], observer.mean_absM[0]]
+
     def run(self, nsteps, sample_frequency=verylargeint, print_frequency=verylargeint,
             observer=None, save_obs=False):
         if _is_observer(print_frequency):  # run(nsteps, sample_frequency, observer): mc_mpi.py:66
@@ -259,6 +275,8 @@ class CanonicalMonteCarlo:
         else:
             lat.reduce_observables()  # model.energy(config) at the top of run (mc.py:191)
             self._energy = None
+        if getattr(observer, "_pmc_device", False) and not self._is_discs() and sample_frequency <= nsteps:
+            return self._run_device_stats(lat, nsteps, sample_frequency, observer)
         output = open("obs.dat", "a")
         try:
             with open(os.devnull, "w") as devnull:

@@ -115,3 +115,29 @@ def test_device_observer_on_replica_exchange(tmp_path):
         assert np.argmax(obs.specific_heat) not in (0, R - 1)    # C_v peaks inside the ladder (near T_c)
     finally:
         os.chdir(old)
+
+
+def test_device_observer_with_canonical_engine(tmp_path):
+    """Same samples, two observers: the device accumulators must equal the host observer's means exactly
+    (integer-valued sums) when both run the same random stream."""
+    import py_mc_b200
+    from py_mc_b200.ising2D import ising2D, ising2D_config, observer
+    from py_mc_b200.mc import CanonicalMonteCarlo
+    from py_mc_b200.observers import device_observer
+    old = os.getcwd()
+    os.chdir(tmp_path)
+    try:
+        init = o_ising.init_config(9, 0, 16, 16)
+        results = []
+        for obs in (observer(), device_observer()):
+            py_mc_b200.set_seed(9)
+            cfg = ising2D_config(16, 16)
+            cfg.config[:, :] = init
+            calc = CanonicalMonteCarlo(ising2D(-1.0), 2.4, cfg)
+            results.append(calc.run(600, 3, 10 ** 9, obs))
+            last = obs
+        assert results[0][0] == pytest.approx(results[1][0], rel=1e-13)
+        assert results[0][1] == pytest.approx(results[1][1], rel=1e-13)
+        assert last.counts[0] == 200 and last.specific_heat[0] > 0 and 0 < last.binder[0] < 2.0 / 3.0 + 1e-9
+    finally:
+        os.chdir(old)
