@@ -52,7 +52,17 @@ class PymcError(RuntimeError):
 
 def _load():
     global LIBPATH
-    LIBPATH = os.environ.get("PYMC_B200_LIB", LIBPATH)  # alternative build of the same ABI (kernel experiments)
+    override = os.environ.get("PYMC_B200_LIB")  # alternative build of the same ABI (kernel experiments)
+    if override:
+        LIBPATH = override
+    else:
+        try:  # rebuild an absent or out-of-date library when a compiler is at hand (seconds); never silently fall back
+            from . import _build
+            if _build.is_stale():
+                _build.build()
+        except Exception as exc:  # no nvcc, read-only tree ...: use what is there, or fail below
+            if not os.path.exists(LIBPATH):
+                raise ImportError("py_mc_b200: cannot build %s: %s" % (LIBPATH, exc))
     if not os.path.exists(LIBPATH):
         raise ImportError(
             "py_mc_b200: %s is missing. Build it with `python -m py_mc_b200._build` "
