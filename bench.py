@@ -167,8 +167,9 @@ def pick_workload(args, world):
 def workload_name(args, world=None):
     world = args.gpus if world is None else world
     if pick_workload(args, world) == "rx":
-        return ("ising2d_replica_exchange_%d_replicas_of_%dx%d_per_gpu_kT=%.2f..%.2f_exchange_every_%d_sweeps"
-                % (args.rx_replicas, args.rx_L, args.rx_L, args.rx_kT_lo, args.rx_kT_hi, args.rx_every))
+        name = ("ising2d" if args.rx_model == "ising" else "hardcore_lattice_gas_mu=%g" % args.rx_mu)
+        return ("%s_replica_exchange_%d_replicas_of_%dx%d_per_gpu_kT=%.2f..%.2f_exchange_every_%d_sweeps"
+                % (name, args.rx_replicas, args.rx_L, args.rx_L, args.rx_kT_lo, args.rx_kT_hi, args.rx_every))
     return "ising2d_%dx%d_single_replica_checkerboard_kT=Tc_J=-1" % (args.L, args.L)
 
 
@@ -192,14 +193,20 @@ def run_rx(args):
     R = nloc * world
     layout = _cabi.LAYOUT_BITS if args.layout == "bits" else _cabi.LAYOUT_INT8
     kTs = np.linspace(args.rx_kT_lo, args.rx_kT_hi, R)
-    model = ising2D(-1.0)
-    lat = _cabi.Lattices(_cabi.MODEL_ISING, L, L, nreplicas=nloc, ntemps=R, seed=SEED, layout=layout,
+    if args.rx_model == "hardcore":
+        # BASELINE config 5 read as a lattice model: nearest-neighbour exclusion, ladder over kT at fixed mu
+        # (e.g. --rx-model hardcore --rx-replicas 8 on 8 GPUs = 64 temperatures)
+        from py_mc_b200.latgas import hardcore_latticegas
+        model = hardcore_latticegas(mu=args.rx_mu)
+    else:
+        model = ising2D(-1.0)
+    lat = _cabi.Lattices(model._pmc_model, L, L, nreplicas=nloc, ntemps=R, seed=SEED, layout=layout,
                          device=local_rank, replica_offset=rank * nloc, nreplicas_global=R)
     stream = torch.cuda.current_stream()
     lat.set_stream(stream.cuda_stream)
     lat.init_random()
     lat.set_accept_tables(np.array([model._pmc_thresholds(kT) for kT in kTs]))
-    lat.rx_setup(1.0 / kTs, -1.0)
+    lat.rx_setup(1.0 / kTs, *model._pmc_energy_coeffs())
     eptr, _ = lat.rx_buffers()
     e_all = torch.as_tensor(_DeviceArray(eptr, R, "<f8"), device="cuda")
     e_mine = e_all[rank * nloc:(rank + 1) * nloc]
@@ -574,6 +581,8 @@ def main():
     ap.add_argument("--rx-replicas", type=int, default=256, help="replicas per GPU (weak scaling)")
     ap.add_argument("--rx-L", type=int, default=1024)
     ap.add_argument("--rx-every", type=int, default=10, help="sweeps between exchanges")
+    ap.add_argument("--rx-model", default="ising", choices=["ising", "hardcore"])
+    ap.add_argument("--rx-mu", type=float, default=1.0, help="chemical potential of the hard-core lattice gas")
     ap.add_argument("--rx-kT-lo", type=float, default=2.0)
     ap.add_argument("--rx-kT-hi", type=float, default=2.6)
     ap.add_argument("--e2e-full", action="store_true", help="rx e2e uploads a distinct host image per replica")

@@ -49,14 +49,23 @@ def build(force=False, verbose=False, extra_flags=()):
     if not force and not is_stale():
         return LIBPATH
     os.makedirs(LIBDIR, exist_ok=True)
-    cmd = [_nvcc(), *NVCC_FLAGS, *extra_flags, "-I", INCLUDE, "-o", LIBPATH] + [os.path.join(CSRC, s) for s in SOURCES]
-    if verbose:
-        print(" ".join(cmd), flush=True)
-    res = subprocess.run(cmd, capture_output=True, text=True)
-    if res.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
-    if verbose and (res.stdout or res.stderr):
-        print(res.stdout + res.stderr)
+    import fcntl
+    with open(os.path.join(LIBDIR, ".build.lock"), "w") as lock:  # ranks of one job may get here together
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        if not force and not is_stale():  # somebody else built it while we waited
+            return LIBPATH
+        tmp = LIBPATH + ".tmp.%d" % os.getpid()
+        cmd = [_nvcc(), *NVCC_FLAGS, *extra_flags, "-I", INCLUDE, "-o", tmp] + [os.path.join(CSRC, s) for s in SOURCES]
+        if verbose:
+            print(" ".join(cmd), flush=True)
+        res = subprocess.run(cmd, capture_output=True, text=True)
+        if res.returncode != 0:
+            if os.path.exists(tmp):
+                os.remove(tmp)
+            raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
+        os.replace(tmp, LIBPATH)  # a process that has the old file mapped keeps its copy
+        if verbose and (res.stdout or res.stderr):
+            print(res.stdout + res.stderr)
     return LIBPATH
 
 

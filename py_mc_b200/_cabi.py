@@ -56,13 +56,12 @@ def _load():
     if override:
         LIBPATH = override
     else:
-        try:  # rebuild an absent or out-of-date library when a compiler is at hand (seconds); never silently fall back
-            from . import _build
-            if _build.is_stale():
+        if not os.path.exists(LIBPATH):  # build an absent library when a compiler is at hand; never fall back
+            try:
+                from . import _build
                 _build.build()
-        except Exception as exc:  # no nvcc, read-only tree ...: use what is there, or fail below
-            if not os.path.exists(LIBPATH):
-                raise ImportError("py_mc_b200: cannot build %s: %s" % (LIBPATH, exc))
+            except Exception as exc:
+                raise ImportError("py_mc_b200: %s is missing and cannot be built: %s" % (LIBPATH, exc))
     if not os.path.exists(LIBPATH):
         raise ImportError(
             "py_mc_b200: %s is missing. Build it with `python -m py_mc_b200._build` "

@@ -80,6 +80,30 @@ class latticegas(model):
         return latgas_config
 
 
+HARD_J = 1.0e30
+"""Pair energy standing in for "infinite" nearest-neighbour repulsion: exp(-HARD_J/kT) underflows to exactly 0.0
+for any kT < 1e27, while HARD_J * 0 neighbours stays 0.0 (a true ``inf`` would give ``inf * 0 = nan`` in the
+reference's dE formula, latgas.py:48-50)."""
+
+
+def hardcore_latticegas(mu, Eads=0.0):
+    """Nearest-neighbour-exclusion ("hard-core", hard-square) lattice gas: BASELINE config 5 read as a lattice
+    model (note on C5).  It is the reference's own ``latticegas`` (latgas.py:7-57) with a
+    pair energy so large that an insertion next to a particle is accepted only if the uniform draw is exactly
+    0.0 -- the reference's ``random() <= exp(-dE/kT)`` has the same 2**-32 corner.  On the exclusion manifold
+    E = (Eads - mu) * N, so temperature replica exchange (``TemperatureRX_MPI``) over a kT ladder is replica
+    exchange over the activity z = exp(-(Eads - mu)/kT).  Start from the empty lattice (``config[:] = 0``) to stay
+    on the manifold from the first sweep; a random start leaves it within a few sweeps, because removing a particle
+    that has a neighbour is always accepted.
+
+    Do not simulate at exactly Eads == mu (z = 1): then every acceptance probability of the reference's Metropolis
+    rule is 0 or 1, and a sweep in fixed site order becomes a deterministic map (from the empty lattice it
+    alternates between the two fully occupied sub-lattices).  The reference avoids this only through its random
+    site selection; any z != 1 is fine (tests/test_gpu_hardcore_lattice.py checks densities against the exact
+    transfer-matrix values)."""
+    return latticegas(Eads=Eads, J=HARD_J, mu=mu)
+
+
 class latgas_config(LatticeConfig):
     """Occupancy holder; ``config`` is float64 0/1 like the reference (latgas.py:61-75)."""
 

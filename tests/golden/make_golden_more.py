@@ -156,6 +156,10 @@ LATGAS_CASES = [
     ("lg_repulse", 8, 8, 1.0, -2.0, 0.0, 0.5, 13, 2, 10),
     ("lg_word_6x128", 6, 128, -0.5, 0.25, -0.75, 0.75, 14, 0, 5),
     ("lg_partial_4x132", 4, 132, 0.25, -0.5, 0.0, 0.3, 15, 3, 5),
+    # nearest-neighbour exclusion ("hard-core lattice gas", BASELINE config 5 read as a lattice model): J so large
+    # that exp(-dE/kT) underflows to 0.0 for an insertion next to a particle; random start relaxes into the
+    # exclusion manifold, then only nn = 0 insertions / any removal are accepted
+    ("lg_hardcore", 8, 8, 1.0e6, 0.0, 0.5, 1.0, 16, 1, 10),
 ]
 
 
