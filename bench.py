@@ -158,6 +158,9 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+KERNELS = {"auto": 0, "generic": 1, "two_pass": 2, "resident": 3}  # PYMC_KERNEL_* of include/pymc_b200.h
+
+
 def pick_workload(args, world):
     if args.workload != "auto":
         return args.workload
@@ -201,7 +204,7 @@ def run_rx(args):
     else:
         model = ising2D(-1.0)
     lat = _cabi.Lattices(model._pmc_model, L, L, nreplicas=nloc, ntemps=R, seed=SEED, layout=layout,
-                         device=local_rank, replica_offset=rank * nloc, nreplicas_global=R)
+                         device=local_rank, replica_offset=rank * nloc, nreplicas_global=R, kernel=KERNELS[args.kernel])
     stream = torch.cuda.current_stream()
     lat.set_stream(stream.cuda_stream)
     lat.init_random()
@@ -210,12 +213,15 @@ def run_rx(args):
     eptr, _ = lat.rx_buffers()
     e_all = torch.as_tensor(_DeviceArray(eptr, R, "<f8"), device="cuda")
     e_mine = e_all[rank * nloc:(rank + 1) * nloc]
-    state = {"scheme": 0, "done": 0, "exchanges": 0}
+    state = {"scheme": 0, "done": 0, "exchanges": 0, "calls": 0}
 
     def steps(n):
-        for _ in range(n):
-            lat.sweep(1)
-            state["done"] += 1
+        while n > 0:  # the sweeps up to the next exchange are one call (one launch on the resident kernel)
+            chunk = min(n, args.rx_every - state["done"] % args.rx_every)
+            lat.sweep(chunk)
+            state["calls"] += 1
+            state["done"] += chunk
+            n -= chunk
             if state["done"] % args.rx_every == 0:
                 lat.rx_energies()
                 if dist is not None:
@@ -232,10 +238,10 @@ def run_rx(args):
     sampler = ClockSampler(local_rank)
     sampler.start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ex0 = state["exchanges"]
+    ex0, calls0 = state["exchanges"], state["calls"]
     ev0.record(stream)
     steps(args.steps)
-    ex1 = state["exchanges"]
+    ex1, ncalls = state["exchanges"], state["calls"] - calls0
     ev1.record(stream)
     torch.cuda.synchronize()
     ms = ev0.elapsed_time(ev1)
@@ -277,8 +283,10 @@ def run_rx(args):
 
     bytes_per_site = 1.0 if layout == _cabi.LAYOUT_INT8 else 0.125
     lps, kname = lat.sweep_kernel_info()
-    alg = 2.0 * bytes_per_site * nsites / lps
-    launch_ms = ms / (lps * args.steps)  # exchange kernels are ~microseconds; stated in config
+    nlaunch = ncalls if kname == "resident_kernel" else lps * args.steps  # resident: one launch per call
+    # algorithmic bytes: 2 x bytes_per_site per attempt, whatever the kernel really moves
+    alg = 2.0 * bytes_per_site * nsites * args.steps / nlaunch
+    launch_ms = ms / nlaunch  # exchange kernels are ~microseconds; stated in config
     peak, peak_src = measured_peak_hbm()
     achieved = alg / (launch_ms * 1e-3) / 1e9
     if rank == 0:
@@ -302,11 +310,14 @@ def run_rx(args):
                     "d2h_bytes_per_step": 16 * nloc + 4 * R, "sweeps_per_step": args.e2e_sweeps,
                     "note": "C-ABI: upload every replica from host int8, sweeps+exchanges, read back tracked "
                             "observables and the replica->T map"},
-            "gpu_launches": lps * args.steps + 2 * nex,
+            "gpu_launches": nlaunch + 2 * nex,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": None, "kernel": kname, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg},
         }
+        if kname == "resident_kernel":
+            line["roofline"]["note"] = ("not HBM-bound: the lattice stays in shared memory for the %d sweeps of a launch; "
+                                        "HBM moves 2 x bytes_per_site per launch, not per sweep" % args.rx_every)
         print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()
@@ -322,7 +333,8 @@ def run_latgas(args):
     L, R = args.lg_L, args.lg_replicas
     layout = _cabi.LAYOUT_BITS if args.layout == "bits" else _cabi.LAYOUT_INT8
     model = latticegas(Eads=0.0, J=-1.0, mu=0.0)
-    lat = _cabi.Lattices(_cabi.MODEL_LATGAS, L, L, nreplicas=R, ntemps=1, seed=SEED, layout=layout)
+    lat = _cabi.Lattices(_cabi.MODEL_LATGAS, L, L, nreplicas=R, ntemps=1, seed=SEED, layout=layout,
+                         kernel=KERNELS[args.kernel])
     lat.init_random()
     lat.set_accept_tables(model._pmc_thresholds(1.0)[None, :])
     lat.set_pair_tables(model._pmc_pair_thresholds(1.0)[None, :])
@@ -344,7 +356,8 @@ def run_latgas(args):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": {"workload": "latgas_%d_replicas_of_%dx%d_J=-1_kT=1" % (R, L, L), "layout": args.layout,
                        "flip_kernel": kname, "seed": SEED},
-            "pair_exchange": out["pair_exchange"], "gpu_launches": lps * args.steps}
+            "pair_exchange": out["pair_exchange"],
+            "gpu_launches": 2 * ((args.steps + 4095) // 4096) if kname == "resident_kernel" else (lps + 16) * args.steps}
     print(json.dumps(line), flush=True)
 
 
@@ -581,6 +594,8 @@ def main():
     ap.add_argument("--rx-replicas", type=int, default=256, help="replicas per GPU (weak scaling)")
     ap.add_argument("--rx-L", type=int, default=1024)
     ap.add_argument("--rx-every", type=int, default=10, help="sweeps between exchanges")
+    ap.add_argument("--kernel", default="auto", choices=["auto", "generic", "two_pass", "resident"],
+                    help="sweep kernel of the handle (PYMC_KERNEL_*); resident = one block keeps one replica in shared memory")
     ap.add_argument("--rx-model", default="ising", choices=["ising", "hardcore"])
     ap.add_argument("--rx-mu", type=float, default=1.0, help="chemical potential of the hard-core lattice gas")
     ap.add_argument("--rx-kT-lo", type=float, default=2.0)

@@ -49,7 +49,10 @@ typedef enum {
 typedef enum {
     PYMC_KERNEL_AUTO = 0,    /* fastest kernel that supports the shape                     */
     PYMC_KERNEL_GENERIC = 1, /* the simple one-thread-per-word kernel (any even lenX, lenY) */
-    PYMC_KERNEL_TWO_PASS = 2 /* one launch per colour even where the fused int8 sweep kernel applies */
+    PYMC_KERNEL_TWO_PASS = 2, /* one launch per colour even where the fused int8 sweep kernel applies */
+    PYMC_KERNEL_RESIDENT = 3  /* one block keeps one replica in shared memory for a whole call; needs    */
+                              /* lenY % 128 == 0 and 2*lenX*lenY/16 bytes of shared memory.  AUTO takes */
+                              /* it for batches of small lattices (>= one replica per SM, <= 32 KiB)    */
 } pymc_kernel;
 
 /* Number of acceptance-table entries per temperature: Ising 5 (index = number of aligned
@@ -186,6 +189,11 @@ int pymc_slab_status(pymc_handle *h, int *status);
  * 0xFFFF all, 0x00FF horizontal, 0xFF00 vertical).  Needs lenX % 4 == 0 and lenY % 4 == 0. */
 int pymc_set_pair_tables(pymc_handle *h, const uint32_t *thr, int ntemps, int nclass);
 int pymc_pair_sweep(pymc_handle *h, int64_t nsweeps, uint32_t class_mask);
+/* nsteps times: one flip sweep (pymc_sweep), then one pair pass over the classes of mask_even or mask_odd,
+ * whichever the parity of the pair counter selects (0 = no pair pass in that step).  The mixed flip / move
+ * trial of latticegas.trialstep (examples/latgas_move.py:31-60) batched: (0x00FF, 0xFF00) alternates
+ * horizontal and vertical bonds.  Same trajectory as the separate calls; one launch on resident handles. */
+int pymc_mixed_sweep(pymc_handle *h, int64_t nsteps, uint32_t mask_even, uint32_t mask_odd);
 int pymc_get_pair_counter(pymc_handle *h, uint64_t *counter);
 int pymc_set_pair_counter(pymc_handle *h, uint64_t counter);
 

@@ -13,7 +13,7 @@ from ._build import LIBPATH
 ABI_VERSION = 1
 MODEL_ISING, MODEL_LATGAS = 0, 1
 LAYOUT_INT8, LAYOUT_BITS = 0, 1
-KERNEL_AUTO, KERNEL_GENERIC, KERNEL_TWO_PASS = 0, 1, 2
+KERNEL_AUTO, KERNEL_GENERIC, KERNEL_TWO_PASS, KERNEL_RESIDENT = 0, 1, 2, 3
 NCLASS = {MODEL_ISING: 5, MODEL_LATGAS: 10}
 
 # every symbol include/pymc_b200.h declares (tests check the library exports all of them)
@@ -26,7 +26,7 @@ SYMBOLS = [
     "pymc_rx_setup", "pymc_rx_energies", "pymc_rx_buffers", "pymc_rx_exchange", "pymc_rx_cycle",
     "pymc_rx_get_energies", "pymc_rx_get_stats", "pymc_rx_get_round", "pymc_rx_set_round",
     "pymc_host_alloc", "pymc_host_free", "pymc_reduce_observables_static", "pymc_sweep_kernel_info",
-    "pymc_set_pair_tables", "pymc_pair_sweep", "pymc_get_pair_counter", "pymc_set_pair_counter",
+    "pymc_set_pair_tables", "pymc_pair_sweep", "pymc_mixed_sweep", "pymc_get_pair_counter", "pymc_set_pair_counter",
     "pymc_discs_create", "pymc_discs_destroy", "pymc_discs_upload", "pymc_discs_download", "pymc_discs_run",
     "pymc_discs_propose", "pymc_discs_observe", "pymc_discs_counters", "pymc_discs_set_trial_counter",
     "pymc_create_slab", "pymc_slab_ipc_export", "pymc_slab_connect", "pymc_slab_connect_local",
@@ -93,6 +93,7 @@ def _load():
         "pymc_propose": [P, I, P, P, I, P, P],
         "pymc_set_pair_tables": [P, P, I, I],
         "pymc_pair_sweep": [P, I64, C.c_uint32],
+        "pymc_mixed_sweep": [P, I64, C.c_uint32, C.c_uint32],
         "pymc_get_pair_counter": [P, C.POINTER(C.c_uint64)],
         "pymc_set_pair_counter": [P, C.c_uint64],
         "pymc_discs_create": [I, I, I, I, C.c_double, C.c_double, C.c_double, C.c_uint64, I, C.POINTER(P)],
@@ -326,6 +327,11 @@ class Lattices:
     def pair_sweep(self, nsweeps=1, class_mask=0xFFFF):
         self._tracked_cache = None
         check(lib.pymc_pair_sweep(self._h, int(nsweeps), int(class_mask)))
+
+    def mixed_sweep(self, nsteps=1, mask_even=0x00FF, mask_odd=0xFF00):
+        """nsteps x (flip sweep + pair pass over the classes the parity of the pair counter selects)."""
+        self._tracked_cache = None
+        check(lib.pymc_mixed_sweep(self._h, int(nsteps), int(mask_even), int(mask_odd)))
 
     @property
     def pair_counter(self):

@@ -19,7 +19,11 @@
 #include "pmc_layout.cuh"
 #include "pmc_fused_i8.cuh"
 #include "pmc_pair.cuh"
+#include "pmc_resident.cuh"
 #include "pmc_discs.cuh"
+
+// largest bit image (bytes) for which PYMC_KERNEL_AUTO takes the resident kernel: several blocks per SM
+static const size_t RESIDENT_AUTO_MAX_IMAGE = 32 * 1024;
 
 using namespace pmc;
 
@@ -633,6 +637,10 @@ struct pymc_handle {
     unsigned int *slab_done;              // block counter used by the in-kernel barrier
     bool dirty_halo;                      // neighbours may still be writing my halo rows (wait before reading them)
     bool local_peers;                     // neighbours are handles of this process (pymc_slab_connect_local)
+    bool resident;                 // sweeps run on the whole-lattice-resident kernel (pmc_resident.cuh)
+    bool resident_big;             // ... only calls of >= 2 sweeps do (large int8 images: packing must be amortised)
+    int resident_threads;
+    bool resident_attr[2];         // dynamic shared memory limit raised for this handle's instantiation (flip model)
     bool tables_set;
     bool dirty;                    // configurations changed since the tracked observables were based
     uint64_t sweep_counter;
@@ -782,9 +790,43 @@ int pymc_create(const pymc_params *p, pymc_handle **out) {
     h->nw = (h->nk + 63) / 64;
     h->nclass = p->model == PYMC_MODEL_ISING ? PYMC_NCLASS_ISING : PYMC_NCLASS_LATGAS;
     REQUIRE((uint64_t)p->lenX * h->nw < (1ull << 31), PYMC_ERR_UNSUPPORTED, "pymc_create: lattice too large");
+    REQUIRE(p->kernel >= PYMC_KERNEL_AUTO && p->kernel <= PYMC_KERNEL_RESIDENT, PYMC_ERR_BADARG, "pymc_create: kernel %d",
+            p->kernel);
 
     DeviceGuard guard(p->device);
     int rc = PYMC_OK;
+    if (guard.ok) {
+        // K9 (pmc_resident.cuh): one block keeps one replica in shared memory for a whole call.  Chosen for batches
+        // that give every SM a replica and whose bit image is small; PYMC_KERNEL_RESIDENT forces it wherever it fits.
+        int sms = 0, smem = 0;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, p->device);
+        cudaDeviceGetAttribute(&smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, p->device);
+        const size_t image = (size_t)16 * p->lenX * h->nw;
+        const bool fits = p->lenY % 128 == 0 && image + 2048 <= (size_t)smem;
+        if (p->kernel == PYMC_KERNEL_RESIDENT && !fits) {
+            delete h;
+            return fail(PYMC_ERR_UNSUPPORTED,
+                        "pymc_create: the resident kernel needs lenY %% 128 == 0 and a bit image (%zu bytes) within the "
+                        "%d bytes of shared memory of a block", image, smem);
+        }
+        h->resident = p->kernel == PYMC_KERNEL_RESIDENT ||
+                      (p->kernel == PYMC_KERNEL_AUTO && fits && image <= RESIDENT_AUTO_MAX_IMAGE && p->nreplicas >= sms);
+        // Larger int8 images (config 3: 1024 x 1024 = 128 KiB, one block per SM): the fused kernel packs and unpacks
+        // bytes every sweep, the resident one once per call -- it wins from 2 sweeps per call on (measured: 0.134 vs
+        // 0.173 ms per sweep of 256 replicas at 10 sweeps per call), provided the replicas fill whole waves of blocks.
+        if (!h->resident && p->kernel == PYMC_KERNEL_AUTO && fits && p->layout == PYMC_LAYOUT_INT8 && p->nreplicas >= sms) {
+            int smem_sm = 0;
+            cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, p->device);
+            long per_sm = (long)(smem_sm / (image + 2048));
+            if (per_sm > 2048 / RESIDENT_MAX_THREADS) per_sm = 2048 / RESIDENT_MAX_THREADS;
+            if (per_sm >= 1) {
+                const long slots = per_sm * sms, waves = (p->nreplicas + slots - 1) / slots;
+                h->resident_big = (double)p->nreplicas / (double)(waves * slots) >= 0.8;
+            }
+        }
+        int threads = (int)(((size_t)p->lenX * h->nw / 2 + 31) / 32 * 32);
+        h->resident_threads = threads < 128 ? 128 : (threads > RESIDENT_MAX_THREADS ? RESIDENT_MAX_THREADS : threads);
+    }
     auto check = [&](cudaError_t e, const char *what) {
         if (e != cudaSuccess && rc == PYMC_OK)
             rc = fail(PYMC_ERR_CUDA, "pymc_create: %s failed: %s", what, cudaGetErrorString(e));
@@ -1008,9 +1050,61 @@ int pymc_get_replica_to_T(pymc_handle *h, int32_t *map, int n) {
     return PYMC_OK;
 }
 
+// K9: nsteps steps (flip sweep and / or pair pass each) of every replica in one launch per <= 4096 steps.
+static int launch_resident(pymc_handle *h, int64_t nsteps, bool flip, uint32_t mask_even, uint32_t mask_odd) {
+    REQUIRE(!flip || h->tables_set, PYMC_ERR_STATE, "sweep: call pymc_set_accept_tables first");
+    REQUIRE(!(mask_even | mask_odd) || h->pair_plans, PYMC_ERR_STATE, "pair sweep: call pymc_set_pair_tables first");
+    if (h->dirty) {
+        int rc = rebase_tracked(h);
+        if (rc) return rc;
+    }
+    const size_t image = (size_t)16 * h->p.lenX * h->nw;
+    const int m = h->p.model == PYMC_MODEL_ISING ? 0 : 1;
+#define RESIDENT_INST(MOD, LAY) resident_kernel<MOD, LAY, Lat>
+    if (!h->resident_attr[m] && image > 48 * 1024) {
+        cudaError_t e;
+        if (h->p.layout == PYMC_LAYOUT_INT8)
+            e = m ? cudaFuncSetAttribute(RESIDENT_INST(MODEL_LATGAS, PYMC_LAYOUT_INT8), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)image)
+                  : cudaFuncSetAttribute(RESIDENT_INST(MODEL_ISING, PYMC_LAYOUT_INT8), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)image);
+        else
+            e = m ? cudaFuncSetAttribute(RESIDENT_INST(MODEL_LATGAS, PYMC_LAYOUT_BITS), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)image)
+                  : cudaFuncSetAttribute(RESIDENT_INST(MODEL_ISING, PYMC_LAYOUT_BITS), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)image);
+        CUDA_TRY(e);
+    }
+    h->resident_attr[m] = true;
+    Lat L = make_lat(h);
+    while (nsteps > 0) {
+        ResidentArgs a;
+        a.nsteps = nsteps > 4096 ? 4096 : nsteps;
+        a.flip = flip ? 1 : 0;
+        a.mask_even = mask_even;
+        a.mask_odd = mask_odd;
+        a.sweep0 = h->sweep_counter;
+        a.pair0 = h->pair_counter;
+        const int T = h->resident_threads, G = h->p.nreplicas;
+        if (h->p.layout == PYMC_LAYOUT_INT8) {
+            if (m) RESIDENT_INST(MODEL_LATGAS, PYMC_LAYOUT_INT8)<<<G, T, image, h->stream>>>(L, a);
+            else RESIDENT_INST(MODEL_ISING, PYMC_LAYOUT_INT8)<<<G, T, image, h->stream>>>(L, a);
+        } else {
+            if (m) RESIDENT_INST(MODEL_LATGAS, PYMC_LAYOUT_BITS)<<<G, T, image, h->stream>>>(L, a);
+            else RESIDENT_INST(MODEL_ISING, PYMC_LAYOUT_BITS)<<<G, T, image, h->stream>>>(L, a);
+        }
+        // the counters move exactly as in the kernel
+        for (int64_t s = 0; s < a.nsteps; ++s) {
+            if (flip) h->sweep_counter++;
+            if ((h->pair_counter & 1ull) ? mask_odd : mask_even) h->pair_counter++;
+            else if (!flip) break;  // nothing can change any more
+        }
+        nsteps -= a.nsteps;
+    }
+#undef RESIDENT_INST
+    CUDA_TRY(cudaGetLastError());
+    return PYMC_OK;
+}
+
 static bool uses_fused(const pymc_handle *h) {
     const int nown = h->slab ? h->own_hi - h->own_lo : h->p.lenX;
-    return h->p.layout == PYMC_LAYOUT_INT8 && h->p.kernel == PYMC_KERNEL_AUTO && h->nk % 64 == 0 &&
+    return !h->resident && h->p.layout == PYMC_LAYOUT_INT8 && h->p.kernel == PYMC_KERNEL_AUTO && h->nk % 64 == 0 &&
            h->nw % FUSED_TW == 0 && nown % FUSED_TH == 0;
 }
 
@@ -1020,7 +1114,11 @@ int pymc_sweep_kernel_info(pymc_handle *h, int *launches_per_sweep, const char *
     REQUIRE(h, PYMC_ERR_BADARG, "pymc_sweep_kernel_info: null handle");
     const char *name;
     int n = 2;
-    if (uses_fused(h)) {
+    if (h->resident || h->resident_big) {
+        // one launch per call (up to 4096 sweeps), not per sweep; resident_big: calls of a single sweep take the fused kernel
+        name = "resident_kernel";
+        n = 1;
+    } else if (uses_fused(h)) {
         name = "sweep_fused_i8_kernel";
         n = 1;
     } else if (h->p.layout == PYMC_LAYOUT_BITS && h->p.kernel != PYMC_KERNEL_GENERIC) {
@@ -1040,6 +1138,7 @@ int pymc_sweep(pymc_handle *h, int64_t nsweeps) {
     REQUIRE(nsweeps >= 0, PYMC_ERR_BADARG, "pymc_sweep: nsweeps %lld", (long long)nsweeps);
     REQUIRE(h->tables_set, PYMC_ERR_STATE, "pymc_sweep: call pymc_set_accept_tables first");
     REQUIRE(!h->slab || h->peer_up[0], PYMC_ERR_STATE, "pymc_sweep: connect the slab to its neighbours first");
+    if (h->resident || (h->resident_big && nsweeps >= 2)) return launch_resident(h, nsweeps, true, 0, 0);
     if (h->dirty) {
         int rc = rebase_tracked(h);
         if (rc) return rc;
@@ -1391,6 +1490,7 @@ int pymc_pair_sweep(pymc_handle *h, int64_t nsweeps, uint32_t class_mask) {
     REQUIRE(!h->slab, PYMC_ERR_UNSUPPORTED, "pymc_pair_sweep: not available on slab handles");
     REQUIRE((class_mask & 0xFFFFu) != 0 && (class_mask >> 16) == 0, PYMC_ERR_BADARG, "pymc_pair_sweep: class mask %#x",
             class_mask);
+    if (h->resident) return launch_resident(h, nsweeps, false, class_mask, class_mask);
     if (h->dirty) {
         int rc = rebase_tracked(h);
         if (rc) return rc;
@@ -1410,6 +1510,23 @@ int pymc_pair_sweep(pymc_handle *h, int64_t nsweeps, uint32_t class_mask) {
         h->pair_counter++;
     }
     CUDA_TRY(cudaGetLastError());
+    return PYMC_OK;
+}
+
+int pymc_mixed_sweep(pymc_handle *h, int64_t nsteps, uint32_t mask_even, uint32_t mask_odd) {
+    ENTER(h);
+    REQUIRE(nsteps >= 0, PYMC_ERR_BADARG, "pymc_mixed_sweep: nsteps %lld", (long long)nsteps);
+    REQUIRE((mask_even >> 16) == 0 && (mask_odd >> 16) == 0, PYMC_ERR_BADARG, "pymc_mixed_sweep: class masks %#x %#x",
+            mask_even, mask_odd);
+    REQUIRE(h->pair_plans || !(mask_even | mask_odd), PYMC_ERR_STATE, "pymc_mixed_sweep: call pymc_set_pair_tables first");
+    REQUIRE(!h->slab, PYMC_ERR_UNSUPPORTED, "pymc_mixed_sweep: not available on slab handles");
+    if (h->resident) return launch_resident(h, nsteps, true, mask_even, mask_odd);
+    for (int64_t s = 0; s < nsteps; ++s) {
+        int rc = pymc_sweep(h, 1);
+        if (rc) return rc;
+        const uint32_t mask = (h->pair_counter & 1ull) ? mask_odd : mask_even;
+        if (mask && (rc = pymc_pair_sweep(h, 1, mask))) return rc;
+    }
     return PYMC_OK;
 }
 

@@ -237,9 +237,8 @@ class CanonicalMonteCarlo:
             self.config._device_changed()
             return
         if getattr(self.model, "_pmc_pair_moves", False):
-            for _ in range(n):  # flip sweep, then half of the bond classes (horizontal / vertical in turn)
-                lat.sweep(1)
-                lat.pair_sweep(1, 0x00FF if lat.pair_counter % 2 == 0 else 0xFF00)
+            # per step: flip sweep, then half of the bond classes (horizontal / vertical in turn)
+            lat.mixed_sweep(n, 0x00FF, 0xFF00)
         else:
             lat.sweep(n)
         self.config._device_changed()
