@@ -42,7 +42,9 @@ def profiled_traffic(kernel_name, nsites_expected):
     ncu --set full summary of this workload (profiles/); None if there is no capture for this kernel/size."""
     import csv
     table = {"sweep_fused_i8_kernel": ("r1_fused_final_summary.csv", 268435456),
-             "sweep_bits_rows_kernel": ("r1_bits_final_summary.csv", 268435456)}
+             "sweep_bits_rows_kernel": ("r1_bits_final_summary.csv", 268435456),
+             # 256 replicas of 1024^2 int8, 10 sweeps per launch (the default replica-exchange workload)
+             "resident_kernel": ("r1_resident_rx_summary.csv", 268435456)}
     if kernel_name not in table or table[kernel_name][1] != nsites_expected:
         return None, None
     path = os.path.join(ROOT, "profiles", table[kernel_name][0])
@@ -289,6 +291,10 @@ def run_rx(args):
     launch_ms = ms / nlaunch  # exchange kernels are ~microseconds; stated in config
     peak, peak_src = measured_peak_hbm()
     achieved = alg / (launch_ms * 1e-3) / 1e9
+    traffic = traffic_src = None
+    if (kname == "resident_kernel" and layout == _cabi.LAYOUT_INT8 and args.rx_model == "ising" and (L, nloc) == (1024, 256)
+            and args.rx_every == 10):  # the capture is of exactly this launch shape
+        traffic, traffic_src = profiled_traffic(kname, nsites)
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -312,7 +318,7 @@ def run_rx(args):
                             "observables and the replica->T map"},
             "gpu_launches": nlaunch + 2 * nex,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "kernel": kname, "peak_source": peak_src,
+                         "traffic": traffic, "traffic_source": traffic_src, "kernel": kname, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg},
         }
         if kname == "resident_kernel":
