@@ -1,0 +1,142 @@
+// hostemu.cpp -- drives the device core (update_word, pair_update: py_mc_b200/csrc/pmc_core.cuh, pmc_pair.cuh)
+// on the host, one 64-site word at a time, over a natural [lenX][lenY] int8 image.
+//
+// TEST INFRASTRUCTURE ONLY (see cuda_host_shim.h).  The neighbour words are gathered site by site from the
+// image, so the kernels' own tiling and addressing are NOT exercised here (the GPU tests do that); what is
+// exercised is everything a kernel calls per word: class masks, plan rows, Philox bit planes, the bit-serial
+// comparison, the per-lane tail and the tracked-observable deltas.
+#include "cuda_host_shim.h"
+
+#include "../../py_mc_b200/csrc/pmc_pair.cuh"
+
+using namespace pmc;
+
+namespace {
+
+struct Image {
+    int8_t *p;
+    int lenX, lenY;
+    int at(int i, int j) const {
+        i = ((i % lenX) + lenX) % lenX;
+        j = ((j % lenY) + lenY) % lenY;
+        return p[(size_t)i * lenY + j] > 0;
+    }
+    int8_t *site(int i, int j) const { return p + (size_t)(((i % lenX) + lenX) % lenX) * lenY + (((j % lenY) + lenY) % lenY); }
+};
+
+// word of the values at offset (di, dj) from the sites of word w of `colour` in row i; lane l = site k = 64w + l
+uint64_t gather(const Image &im, int colour, int i, int w, int di, int dj) {
+    const int nk = im.lenY / 2, q = (i + colour) & 1;
+    uint64_t v = 0;
+    for (int l = 0; l < 64 && 64 * w + l < nk; ++l) v |= (uint64_t)im.at(i + di, 2 * (64 * w + l) + q + dj) << l;
+    return v;
+}
+
+uint64_t valid_mask(const Image &im, int w) {
+    const int n = im.lenY / 2 - 64 * w;
+    return n >= 64 ? ~0ull : ((1ull << n) - 1);
+}
+
+template <int MODEL>
+void flip_sweep(const Image &im, const uint32_t *thr, uint64_t seed, uint32_t replica, uint64_t sweep, long long *dB,
+                long long *dS) {
+    uint32_t row[PLAN_WORDS];
+    Plan<MODEL>::build_row(thr, row);
+    const uint32_t(&rowref)[PLAN_WORDS] = row;
+    Plan<MODEL> plan;
+    plan.init(ParamRow{rowref});
+    const int nw = (im.lenY / 2 + 63) / 64;
+    const PhiloxKey key = make_key(seed);
+    for (int colour = 0; colour < 2; ++colour)
+        for (int i = 0; i < im.lenX; ++i)
+            for (int w = 0; w < nw; ++w) {
+                const uint64_t S = gather(im, colour, i, w, 0, 0), valid = valid_mask(im, w);
+                int b = 0, s2 = 0;
+                const uint64_t Snew =
+                    update_word<MODEL>(S, gather(im, colour, i, w, -1, 0), gather(im, colour, i, w, 1, 0),
+                                       gather(im, colour, i, w, 0, -1), gather(im, colour, i, w, 0, 1), valid, plan,
+                                       (uint32_t)(i * nw + w), replica, 2 * sweep + colour, key, b, s2);
+                *dB += b;
+                *dS += s2;
+                const uint64_t flip = (S ^ Snew) & valid;
+                const int q = (i + colour) & 1;
+                for (int l = 0; l < 64; ++l)
+                    if ((flip >> l) & 1ull) {
+                        int8_t *s = im.site(i, 2 * (64 * w + l) + q);
+                        *s = MODEL == MODEL_ISING ? (int8_t)-*s : (int8_t)(1 - *s);
+                    }
+            }
+}
+
+}  // namespace
+
+extern "C" {
+
+// thr: 5 (Ising, by aligned neighbours) or 10 (lattice gas, 5*c + nn) class thresholds.  In place.
+int hostemu_flip_sweep(int model, int8_t *img, int lenX, int lenY, const uint32_t *thr, uint64_t seed, uint32_t replica,
+                       uint64_t sweep, long long *dB, long long *dS) {
+    if (lenX < 2 || lenY < 2 || (lenX & 1) || (lenY & 1)) return -1;
+    Image im = {img, lenX, lenY};
+    *dB = *dS = 0;
+    if (model == MODEL_ISING)
+        flip_sweep<MODEL_ISING>(im, thr, seed, replica, sweep, dB, dS);
+    else if (model == MODEL_LATGAS)
+        flip_sweep<MODEL_LATGAS>(im, thr, seed, replica, sweep, dB, dS);
+    else
+        return -1;
+    return 0;
+}
+
+// thr7[d + 3], d = -3..3.  Bond classes as in pmc_pair.cuh.  In place.
+int hostemu_pair_sweep(int8_t *img, int lenX, int lenY, const uint32_t *thr7, uint64_t seed, uint32_t replica,
+                       uint64_t sweep, uint32_t class_mask, long long *dB) {
+    if (lenX % 4 || lenY % 4) return -1;
+    Image im = {img, lenX, lenY};
+    uint32_t row[PLAN_WORDS];
+    if (!PairPlan::build_row(thr7, row)) return -2;
+    const uint32_t(&rowref)[PLAN_WORDS] = row;
+    PairPlan plan;
+    plan.init(ParamRow{rowref});
+    const int nw = (lenY / 2 + 63) / 64;
+    const PhiloxKey key = make_key(seed);
+    *dB = 0;
+    for (int cls = 0; cls < 16; ++cls) {
+        if (!((class_mask >> cls) & 1u)) continue;
+        const bool horiz = cls < 8;
+        const int ri = horiz ? cls >> 2 : (cls - 8) >> 1, cj = horiz ? cls & 3 : (cls - 8) & 1;
+        for (int i = ri; i < lenX; i += horiz ? 2 : 4) {
+            const int ca = (i + cj) & 1, q = (i + ca) & 1;
+            for (int w = 0; w < nw; ++w) {
+                uint64_t active = valid_mask(im, w);
+                if (horiz)
+                    for (int l = 0; l < 64; ++l)
+                        if ((2 * (64 * w + l) + q) % 4 != cj) active &= ~(1ull << l);
+                const int bi = horiz ? 0 : 1, bj = horiz ? 1 : 0;  // offset of the partner
+                const uint64_t S = gather(im, ca, i, w, 0, 0), Bw = gather(im, ca, i, w, bi, bj);
+                uint64_t A0, A1, B0, B1;
+                if (horiz) {
+                    add3(gather(im, ca, i, w, -1, 0), gather(im, ca, i, w, 1, 0), gather(im, ca, i, w, 0, -1), A0, A1);
+                    add3(gather(im, ca, i, w, -1, 1), gather(im, ca, i, w, 1, 1), gather(im, ca, i, w, 0, 2), B0, B1);
+                } else {
+                    add3(gather(im, ca, i, w, -1, 0), gather(im, ca, i, w, 0, -1), gather(im, ca, i, w, 0, 1), A0, A1);
+                    add3(gather(im, ca, i, w, 2, 0), gather(im, ca, i, w, 1, -1), gather(im, ca, i, w, 1, 1), B0, B1);
+                }
+                int b = 0;
+                const uint64_t acc = pair_update(S, Bw, A0, A1, B0, B1, active, plan, (uint32_t)(i * nw + w), replica,
+                                                 16 * sweep + cls, key, b);
+                *dB += b;
+                for (int l = 0; l < 64; ++l)
+                    if ((acc >> l) & 1ull) {
+                        const int j = 2 * (64 * w + l) + q;
+                        int8_t *a = im.site(i, j), *p = im.site(i + bi, j + bj);
+                        const int8_t t = *a;
+                        *a = *p;
+                        *p = t;
+                    }
+            }
+        }
+    }
+    return 0;
+}
+
+}  // extern "C"

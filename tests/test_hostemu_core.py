@@ -1,0 +1,83 @@
+"""CPU: the kernels' per-word core (py_mc_b200/csrc/pmc_stream.cuh, pmc_core.cuh, pmc_pair.cuh) compiled for the
+host with a thin shim (tests/hostemu/) and checked against the fixtures recorded from the unmodified reference and
+against the numpy specification -- the same source the GPU executes, tested without a GPU.  The kernels' tiling and
+addressing are not covered here (tests/test_gpu_*.py do that)."""
+import numpy as np
+import pytest
+
+from oracle import ising as o_ising
+from oracle import latgas as o_latgas
+from oracle import pairmove as o_pair
+from py_mc_b200 import accept
+from hostemu import HostCore  # tests/hostemu (tests/ is on sys.path through conftest.py)
+
+
+@pytest.fixture(scope="module")
+def core():
+    return HostCore()
+
+
+def ising_table(J, kT):
+    """Thresholds by number of aligned neighbours a = 0..4, as py_mc_b200.ising2D builds them."""
+    return accept.table([-2.0 * J * 1.0 * float(2 * a - 4) for a in range(5)], kT)
+
+
+def test_ising_core_reproduces_reference_trajectories(core, golden_ising):
+    z, meta = golden_ising
+    for m in meta:
+        cfg = np.ascontiguousarray(z[m["name"] + "_init"], dtype=np.int8).copy()
+        thr = ising_table(m["J"], m["kT"])
+        B = o_ising.bond_sum(cfg)
+        for sw in range(m["nsweeps"]):
+            dB, dM = core.flip_sweep(core.MODEL_ISING, cfg, thr, m["seed"], m["replica"], sw)
+            B += dB
+            assert np.array_equal(cfg, z[m["name"] + "_configs"][sw]), (m["name"], sw)
+            assert B == o_ising.bond_sum(cfg)                       # the tracked bond sum the kernels keep
+            assert int(cfg.astype(np.int64).sum()) == z[m["name"] + "_mag"][sw]
+
+
+def test_latgas_core_reproduces_reference_trajectories(core, golden_latgas):
+    z, meta = golden_latgas
+    for m in meta:                                                   # includes the hard-core case lg_hardcore
+        cfg = np.ascontiguousarray(z[m["name"] + "_init"], dtype=np.int8).copy()
+        thr = o_latgas.threshold_table(m["J"], m["Eads"], m["mu"], m["kT"])
+        B, N = o_latgas.bond_sum(cfg), int(cfg.sum())
+        for sw in range(m["nsweeps"]):
+            dB, dN = core.flip_sweep(core.MODEL_LATGAS, cfg, thr, m["seed"], m["replica"], sw)
+            B, N = B + dB, N + dN
+            assert np.array_equal(cfg, z[m["name"] + "_configs"][sw]), (m["name"], sw)
+            assert (B, N) == (o_latgas.bond_sum(cfg), int(cfg.sum()))
+
+
+@pytest.mark.parametrize("shape,J,kT", [((6, 130), 1.0, 1.7), ((4, 256), -1.0, 2.269185314213022), ((8, 36), -0.37, 0.9),
+                                        ((2, 2), -1.0, 1.0), ((4, 128), -1.0, 0.05)])
+def test_ising_core_matches_specification_on_word_boundaries(core, shape, J, kT):
+    """Partial last words, exactly one / two words per row, both signs of J, thresholds that underflow to 0."""
+    seed, replica = 424242, 3
+    ref = o_ising.init_config(seed, replica, *shape)
+    cfg = ref.copy()
+    thr = ising_table(J, kT)
+    for sw in range(6):
+        o_ising.sweep(ref, J, kT, seed, replica, sw)
+        core.flip_sweep(core.MODEL_ISING, cfg, thr, seed, replica, sw)
+        assert np.array_equal(cfg, ref), (shape, sw)
+
+
+@pytest.mark.parametrize("shape,J,kT", [((8, 12), -1.0, 1.0), ((4, 260), 1.0, 0.7), ((12, 132), -0.5, 0.6), ((4, 4), 2.0, 1.5)])
+def test_pair_core_matches_specification(core, shape, J, kT):
+    seed = 909
+    thr = o_pair.threshold_table(J, kT)
+    ref = o_latgas.init_config(seed, 0, *shape)
+    cfg = ref.copy()
+    B = o_latgas.bond_sum(cfg)
+    for sw in range(4):
+        _, nacc, dB_ref = o_pair.sweep_classes(ref, thr, seed, 0, sw)
+        dB = core.pair_sweep(cfg, thr, seed, 0, sw)
+        B += dB
+        assert nacc > 0 and dB == dB_ref
+        assert np.array_equal(cfg, ref), (shape, sw)
+        assert B == o_latgas.bond_sum(cfg) and int(cfg.sum()) == int(ref.sum())
+    # a subset of the classes
+    o_pair.sweep_classes(ref, thr, seed, 0, 4, classes=[1, 6, 9, 14])
+    core.pair_sweep(cfg, thr, seed, 0, 4, class_mask=(1 << 1) | (1 << 6) | (1 << 9) | (1 << 14))
+    assert np.array_equal(cfg, ref)
