@@ -128,7 +128,7 @@ def cpu_baseline(seconds_target=12.0):
     calib, _ = cpu_port.time_all_cores(1024, -1.0, TC, 100000, 1)
     ntrials = int(max(calib, 5e4) * seconds_target)
     value, wall = cpu_port.time_all_cores(1024, -1.0, TC, ntrials, cores)
-    return {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
+    return {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "wall_s": wall,
             "sample": "%d single-site MCstep trials per core on a 1024x1024 float64 lattice at kT=Tc, one replica "
                       "per core (%d cores, %.1f s); per-trial cost of the reference loop does not depend on "
                       "lattice size" % (ntrials, cores, wall)}
@@ -143,17 +143,18 @@ def run_reference(args):
     args.warmup = min(args.warmup, 1)
     t_per_step = max(2.0, 20.0 / max(1, args.steps + args.warmup))
     cb = None
-    vals = []
+    vals, walls = [], []
     for i in range(args.warmup + args.steps):
         c = cpu_baseline(seconds_target=t_per_step)
         if i >= args.warmup:
             vals.append(c["value"])
+            walls.append(c["wall_s"])
             cb = c
     value = sum(vals) / len(vals)
     cb["value"] = value
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": None, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sum(walls) / len(walls),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload_name(args)}, "cpu_baseline": cb,
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
