@@ -141,3 +141,33 @@ def test_device_observer_with_canonical_engine(tmp_path):
         assert last.counts[0] == 200 and last.specific_heat[0] > 0 and 0 < last.binder[0] < 2.0 / 3.0 + 1e-9
     finally:
         os.chdir(old)
+
+
+@pytest.mark.parametrize("layout", [0, 1])
+def test_onsager_energy_and_spontaneous_magnetisation_1024(layout):
+    """Large lattice, independent stream, below T_c: <E>/N against the exact value (Kaufman at L = 512 equals the
+    Onsager limit to 1e-9) and <|M|>/N against Onsager-Yang m = (1 - sinh(2/kT)^-4)^(1/8).  Error bars: the sample
+    standard deviation of e is sqrt(kT^2 c_v / N) = 1.7e-3, of m about 1e-3; 64 samples 20 sweeps apart."""
+    from py_mc_b200 import _cabi
+    from py_mc_b200.ising2D import ising2D
+    L, kT, nsamp = 1024, 2.0, 64
+    lat = _cabi.Lattices(_cabi.MODEL_ISING, L, L, seed=777, layout=layout)
+    lat.upload(0, np.ones((L, L), dtype=np.int8))          # cold start
+    lat.set_accept_tables(ising2D(-1.0)._pmc_thresholds(kT)[None, :])
+    lat.sweep(300)
+    e, m = [], []
+    for _ in range(nsamp):
+        lat.sweep(20)
+        b, mag = lat.tracked()
+        e.append(-float(b[0]) / (L * L))
+        m.append(abs(float(mag[0])) / (L * L))
+    b2, m2 = lat.reduce_observables()
+    assert int(b2[0]) == int(b[0]) and int(m2[0]) == int(mag[0])   # tracked sums stayed exact over 1580 sweeps
+    lat.close()
+    e_exact, _ = kaufman.energy_and_cv_per_site(512, 512, kT)
+    m_exact = (1.0 - np.sinh(2.0 / kT) ** -4) ** 0.125
+    e_err = np.std(e, ddof=1) / np.sqrt(nsamp)
+    m_err = np.std(m, ddof=1) / np.sqrt(nsamp)
+    assert abs(np.mean(e) - e_exact) < 6 * e_err + 2e-4, (np.mean(e), e_exact, e_err)
+    assert abs(np.mean(m) - m_exact) < 6 * m_err + 2e-4, (np.mean(m), m_exact, m_err)
+    assert e_err < 1e-3 and m_err < 1e-3
