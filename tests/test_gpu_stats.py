@@ -171,3 +171,45 @@ def test_onsager_energy_and_spontaneous_magnetisation_1024(layout):
     assert abs(np.mean(e) - e_exact) < 6 * e_err + 2e-4, (np.mean(e), e_exact, e_err)
     assert abs(np.mean(m) - m_exact) < 6 * m_err + 2e-4, (np.mean(m), m_exact, m_err)
     assert e_err < 1e-3 and m_err < 1e-3
+
+
+def test_binder_cumulants_cross_at_the_onsager_temperature(tmp_path):
+    """T_c from the crossing of U4(T) for L = 16 and L = 32 (replica exchange over a ladder around T_c, device-side
+    accumulators): the crossing of this pair of sizes lies within 0.02 of 2/ln(1+sqrt 2) = 2.269185 and the crossing
+    value near the universal U* = 0.61 of periodic square lattices."""
+    import py_mc_b200
+    from py_mc_b200.ising2D import ising2D, ising2D_config
+    from py_mc_b200.mc import CanonicalMonteCarlo
+    from py_mc_b200.mc_mpi import TemperatureRX_MPI
+    from py_mc_b200.observers import device_observer
+    old = os.getcwd()
+    os.chdir(tmp_path)
+    try:
+        R = 16
+        kTs = np.linspace(2.15, 2.40, R)
+        U = {}
+        for L in (16, 32):
+            py_mc_b200.set_seed(1000 + L)
+            configs = []
+            for _ in range(R):
+                c = ising2D_config(L, L)
+                c.prepare_random()
+                configs.append(c)
+            sub = tmp_path / ("L%d" % L)
+            sub.mkdir()
+            os.chdir(sub)
+            rx = TemperatureRX_MPI(None, CanonicalMonteCarlo, ising2D(-1.0), configs, kTs)
+            rx.run(3000, 5)
+            obs = device_observer()
+            rx.run(40000, 5, 5, observer=obs)
+            assert np.all(obs.counts == 8000)
+            U[L] = np.array(obs.binder)
+        d = U[16] - U[32]                       # > 0 above T_c (the smaller lattice stays more ordered), < 0 below
+        assert d[0] < 0 < d[-1], d
+        k = int(np.where((d[:-1] <= 0) & (d[1:] > 0))[0][0])
+        t_cross = kTs[k] - d[k] * (kTs[k + 1] - kTs[k]) / (d[k + 1] - d[k])
+        u_cross = U[32][k] + (U[32][k + 1] - U[32][k]) * (t_cross - kTs[k]) / (kTs[k + 1] - kTs[k])
+        assert abs(t_cross - 2.269185314213022) < 0.02, (t_cross, d)
+        assert 0.58 < u_cross < 0.63, u_cross
+    finally:
+        os.chdir(old)
