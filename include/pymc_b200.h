@@ -50,9 +50,12 @@ typedef enum {
     PYMC_KERNEL_AUTO = 0,    /* fastest kernel that supports the shape                     */
     PYMC_KERNEL_GENERIC = 1, /* the simple one-thread-per-word kernel (any even lenX, lenY) */
     PYMC_KERNEL_TWO_PASS = 2, /* one launch per colour even where the fused int8 sweep kernel applies */
-    PYMC_KERNEL_RESIDENT = 3  /* one block keeps one replica in shared memory for a whole call; needs    */
+    PYMC_KERNEL_RESIDENT = 3, /* one block keeps one replica in shared memory for a whole call; needs    */
                               /* lenY % 128 == 0 and 2*lenX*lenY/16 bytes of shared memory.  AUTO takes */
                               /* it for batches of small lattices (>= one replica per SM, <= 32 KiB)    */
+    PYMC_KERNEL_PERSISTENT = 4 /* one lattice spread over the shared memory of all SMs (one row slab per  */
+                               /* block of a cooperative launch) for all sweeps of a call; needs         */
+                               /* lenY % 128 == 0 and lenX*lenY/8 bytes within the GPU's shared memory   */
 } pymc_kernel;
 
 /* Number of acceptance-table entries per temperature: Ising 5 (index = number of aligned

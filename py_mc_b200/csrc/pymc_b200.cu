@@ -20,10 +20,18 @@
 #include "pmc_fused_i8.cuh"
 #include "pmc_pair.cuh"
 #include "pmc_resident.cuh"
+#include "pmc_persist.cuh"
 #include "pmc_discs.cuh"
 
 // largest bit image (bytes) for which PYMC_KERNEL_AUTO takes the resident kernel: several blocks per SM
 static const size_t RESIDENT_AUTO_MAX_IMAGE = 32 * 1024;
+// smallest lattice (sites) for which PYMC_KERNEL_AUTO takes the persistent kernel.  Measured at 16384 x 16384 only
+// (0.104 ms per sweep against 0.174 for the fused kernel); two grid barriers per sweep cost a few microseconds, so the
+// bound is kept where a sweep is at least ten times that.
+static const size_t PERSIST_AUTO_MIN_SITES = (size_t)16384 * 8192;
+#ifndef PMC_PERSIST_AUTO
+#define PMC_PERSIST_AUTO 1  // 0: only PYMC_KERNEL_PERSISTENT selects the persistent kernel
+#endif
 
 using namespace pmc;
 
@@ -641,6 +649,14 @@ struct pymc_handle {
     bool resident_big;             // ... only calls of >= 2 sweeps do (large int8 images: packing must be amortised)
     int resident_threads;
     bool resident_attr[2];         // dynamic shared memory limit raised for this handle's instantiation (flip model)
+    // K11 (pmc_persist.cuh): one lattice resident in the shared memory of all SMs
+    bool persist;                  // calls of >= 2 sweeps run on the persistent kernel
+    int persist_blocks, persist_threads;
+    size_t persist_smem;
+    unsigned int *persist_counter; // grid barrier arrivals (zeroed before every launch)
+    int *persist_err;              // device flag: a block timed out at the barrier
+    uint64_t *persist_halo;        // [2][blocks][2][nw]
+    bool persist_attr[2];
     bool tables_set;
     bool dirty;                    // configurations changed since the tracked observables were based
     uint64_t sweep_counter;
@@ -726,6 +742,9 @@ int pymc_destroy(pymc_handle *h) {
         cudaFree(h->rep_to_T);
         cudaFree(h->tracked);
         cudaFree(h->reduced);
+        cudaFree(h->persist_counter);
+        cudaFree(h->persist_err);
+        cudaFree(h->persist_halo);
         cudaFree(h->staging);
         cudaFree(h->qbuf);
         cudaFree(h->betas);
@@ -790,7 +809,7 @@ int pymc_create(const pymc_params *p, pymc_handle **out) {
     h->nw = (h->nk + 63) / 64;
     h->nclass = p->model == PYMC_MODEL_ISING ? PYMC_NCLASS_ISING : PYMC_NCLASS_LATGAS;
     REQUIRE((uint64_t)p->lenX * h->nw < (1ull << 31), PYMC_ERR_UNSUPPORTED, "pymc_create: lattice too large");
-    REQUIRE(p->kernel >= PYMC_KERNEL_AUTO && p->kernel <= PYMC_KERNEL_RESIDENT, PYMC_ERR_BADARG, "pymc_create: kernel %d",
+    REQUIRE(p->kernel >= PYMC_KERNEL_AUTO && p->kernel <= PYMC_KERNEL_PERSISTENT, PYMC_ERR_BADARG, "pymc_create: kernel %d",
             p->kernel);
 
     DeviceGuard guard(p->device);
@@ -823,6 +842,29 @@ int pymc_create(const pymc_params *p, pymc_handle **out) {
                 const long slots = per_sm * sms, waves = (p->nreplicas + slots - 1) / slots;
                 h->resident_big = (double)p->nreplicas / (double)(waves * slots) >= 0.8;
             }
+        }
+        // K11 (pmc_persist.cuh): one lattice over the shared memory of all SMs, one row slab per block
+        {
+            int coop = 0;
+            cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, p->device);
+            const int blocks = p->lenX < sms ? p->lenX : sms;
+            const int max_rows = (p->lenX + blocks - 1) / blocks;
+            const size_t slab = (size_t)16 * (max_rows + 2) * h->nw;
+            // 512 bytes of static shared memory ride along; 16384 x 16384 on 148 SMs needs 231 424 of the 232 448 bytes
+            const bool pfits = coop && p->lenY % 128 == 0 && slab + 1024 <= (size_t)smem;
+            if (p->kernel == PYMC_KERNEL_PERSISTENT && !pfits) {
+                delete h;
+                return fail(PYMC_ERR_UNSUPPORTED,
+                            "pymc_create: the persistent kernel needs lenY %% 128 == 0, cooperative launches and row slabs "
+                            "(%zu bytes) within the %d bytes of shared memory of a block", slab, smem);
+            }
+            h->persist = p->kernel == PYMC_KERNEL_PERSISTENT ||
+                         (PMC_PERSIST_AUTO && p->kernel == PYMC_KERNEL_AUTO && pfits && p->nreplicas == 1 &&
+                          (size_t)p->lenX * p->lenY >= PERSIST_AUTO_MIN_SITES);
+            h->persist_blocks = blocks;
+            h->persist_smem = slab;
+            int pthreads = (int)(((size_t)max_rows * h->nw + 31) / 32 * 32);
+            h->persist_threads = pthreads < 128 ? 128 : (pthreads > PERSIST_MAX_THREADS ? PERSIST_MAX_THREADS : pthreads);
         }
         int threads = (int)(((size_t)p->lenX * h->nw / 2 + 31) / 32 * 32);
         h->resident_threads = threads < 128 ? 128 : (threads > RESIDENT_MAX_THREADS ? RESIDENT_MAX_THREADS : threads);
@@ -889,6 +931,11 @@ int pymc_reset_stream(pymc_handle *h) {
 int pymc_synchronize(pymc_handle *h) {
     ENTER(h);
     CUDA_TRY(cudaStreamSynchronize(h->stream));
+    if (h->persist_err) {
+        int flag = 0;
+        CUDA_TRY(cudaMemcpy(&flag, h->persist_err, sizeof(int), cudaMemcpyDeviceToHost));
+        REQUIRE(!flag, PYMC_ERR_CUDA, "pymc_synchronize: a block of the persistent sweep kernel timed out at the grid barrier");
+    }
     return PYMC_OK;
 }
 
@@ -1050,6 +1097,59 @@ int pymc_get_replica_to_T(pymc_handle *h, int32_t *map, int n) {
     return PYMC_OK;
 }
 
+// K11: nsweeps sweeps of every replica of the handle, one cooperative launch per replica and <= 4096 sweeps.
+// Returns PYMC_ERR_UNSUPPORTED (and switches the handle back to the per-sweep kernels) if the device refuses the
+// cooperative launch, e.g. because the SMs are shared with another context.
+static int launch_persistent(pymc_handle *h, int64_t nsweeps) {
+    REQUIRE(h->tables_set, PYMC_ERR_STATE, "pymc_sweep: call pymc_set_accept_tables first");
+    if (h->dirty) {
+        int rc = rebase_tracked(h);
+        if (rc) return rc;
+    }
+    const int m = h->p.model == PYMC_MODEL_ISING ? 0 : 1;
+    const void *fn;
+    if (h->p.layout == PYMC_LAYOUT_INT8)
+        fn = m ? (const void *)persistent_kernel<MODEL_LATGAS, PYMC_LAYOUT_INT8, Lat> : (const void *)persistent_kernel<MODEL_ISING, PYMC_LAYOUT_INT8, Lat>;
+    else
+        fn = m ? (const void *)persistent_kernel<MODEL_LATGAS, PYMC_LAYOUT_BITS, Lat> : (const void *)persistent_kernel<MODEL_ISING, PYMC_LAYOUT_BITS, Lat>;
+    if (!h->persist_attr[m]) {
+        if (h->persist_smem > 48 * 1024)
+            CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->persist_smem));
+        h->persist_attr[m] = true;
+    }
+    if (!h->persist_counter) {
+        CUDA_TRY(cudaMalloc(&h->persist_counter, sizeof(unsigned int)));
+        CUDA_TRY(cudaMalloc(&h->persist_err, sizeof(int)));
+        CUDA_TRY(cudaMalloc(&h->persist_halo, (size_t)2 * h->persist_blocks * 2 * h->nw * 8));
+        CUDA_TRY(cudaMemsetAsync(h->persist_err, 0, sizeof(int), h->stream));
+    }
+    Lat L = make_lat(h);
+    while (nsweeps > 0) {
+        const int64_t chunk = nsweeps > 4096 ? 4096 : nsweeps;
+        for (int rep = 0; rep < h->p.nreplicas; ++rep) {
+            PersistArgs a;
+            a.nsweeps = chunk;
+            a.sweep0 = h->sweep_counter;
+            a.rep = rep;
+            a.counter = h->persist_counter;
+            a.err = h->persist_err;
+            a.halo = h->persist_halo;
+            CUDA_TRY(cudaMemsetAsync(h->persist_counter, 0, sizeof(unsigned int), h->stream));
+            void *args[] = {(void *)&L, (void *)&a};
+            cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3(h->persist_blocks), dim3(h->persist_threads), args,
+                                                        h->persist_smem, h->stream);
+            if (e != cudaSuccess) {
+                cudaGetLastError();
+                h->persist = false;  // nothing has run for this replica yet: the caller falls back
+                return fail(PYMC_ERR_UNSUPPORTED, "cooperative launch refused: %s", cudaGetErrorString(e));
+            }
+        }
+        h->sweep_counter += chunk;
+        nsweeps -= chunk;
+    }
+    return PYMC_OK;
+}
+
 // K9: nsteps steps (flip sweep and / or pair pass each) of every replica in one launch per <= 4096 steps.
 static int launch_resident(pymc_handle *h, int64_t nsteps, bool flip, uint32_t mask_even, uint32_t mask_odd) {
     REQUIRE(!flip || h->tables_set, PYMC_ERR_STATE, "sweep: call pymc_set_accept_tables first");
@@ -1114,7 +1214,10 @@ int pymc_sweep_kernel_info(pymc_handle *h, int *launches_per_sweep, const char *
     REQUIRE(h, PYMC_ERR_BADARG, "pymc_sweep_kernel_info: null handle");
     const char *name;
     int n = 2;
-    if (h->resident || h->resident_big) {
+    if (h->persist) {
+        name = "persistent_kernel";  // one cooperative launch per call of >= 2 sweeps
+        n = 1;
+    } else if (h->resident || h->resident_big) {
         // one launch per call (up to 4096 sweeps), not per sweep; resident_big: calls of a single sweep take the fused kernel
         name = "resident_kernel";
         n = 1;
@@ -1139,6 +1242,12 @@ int pymc_sweep(pymc_handle *h, int64_t nsweeps) {
     REQUIRE(h->tables_set, PYMC_ERR_STATE, "pymc_sweep: call pymc_set_accept_tables first");
     REQUIRE(!h->slab || h->peer_up[0], PYMC_ERR_STATE, "pymc_sweep: connect the slab to its neighbours first");
     if (h->resident || (h->resident_big && nsweeps >= 2)) return launch_resident(h, nsweeps, true, 0, 0);
+    if (h->persist && nsweeps >= 2) {
+        // Several replicas: one launch each, in turn.  If the first launch is refused nothing has run and the
+        // per-sweep kernels take over; a refusal later cannot happen (same launch shape).
+        const int rc = launch_persistent(h, nsweeps);
+        if (rc != PYMC_ERR_UNSUPPORTED) return rc;
+    }
     if (h->dirty) {
         int rc = rebase_tracked(h);
         if (rc) return rc;
@@ -1811,6 +1920,7 @@ int pymc_create_slab(const pymc_params *p, int slab_index, int nslabs, pymc_hand
     q.lenX = Xl + 4;  // two halo rows above and below the owned rows
     pymc_handle *h = nullptr;
     int rc = pymc_create(&q, &h);
+    if (rc == PYMC_OK) h->persist = h->resident = h->resident_big = false;  // slabs run the fused kernel only
     if (rc) return rc;
     h->slab = true;
     h->own_lo = 2;

@@ -13,7 +13,7 @@ SRC = os.path.join(HERE, "hostemu.cpp")
 OUTDIR = os.path.join(HERE, "_build")
 LIB = os.path.join(OUTDIR, "libhostemu.so")
 DEPS = [SRC, os.path.join(HERE, "cuda_host_shim.h")] + [os.path.join(CSRC, f) for f in
-                                                         ("pmc_stream.cuh", "pmc_core.cuh", "pmc_pair.cuh")]
+                                                         ("pmc_stream.cuh", "pmc_core.cuh", "pmc_pair.cuh", "pmc_persist.cuh")]
 
 
 def build(force=False):
@@ -37,8 +37,20 @@ class HostCore:
         LL = C.POINTER(C.c_longlong)
         self.lib.hostemu_flip_sweep.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_uint32,
                                                 C.c_uint64, LL, LL]
+        self.lib.hostemu_persist_sweeps.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_uint32,
+                                                    C.c_uint64, C.c_int, C.c_int, C.c_int, LL, LL]
         self.lib.hostemu_pair_sweep.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_uint32,
                                                 C.c_uint64, C.c_uint32, LL]
+
+    def persist_sweeps(self, model, img, thr, seed, replica, sweep0, nsweeps, nblocks, nthreads):
+        """nsweeps sweeps through the persistent kernel's slab logic with nblocks emulated blocks; returns (dB, dS)."""
+        assert img.dtype == np.int8 and img.flags.c_contiguous
+        t = np.ascontiguousarray(thr, dtype=np.uint32)
+        dB, dS = C.c_longlong(0), C.c_longlong(0)
+        rc = self.lib.hostemu_persist_sweeps(model, img.ctypes.data, img.shape[0], img.shape[1], t.ctypes.data, seed,
+                                             replica, sweep0, nsweeps, nblocks, nthreads, C.byref(dB), C.byref(dS))
+        assert rc == 0, rc
+        return dB.value, dS.value
 
     def flip_sweep(self, model, img, thr, seed, replica, sweep):
         """One checkerboard sweep of the int8 image, in place; returns (dB, dS)."""

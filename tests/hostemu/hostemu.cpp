@@ -8,6 +8,9 @@
 #include "cuda_host_shim.h"
 
 #include "../../py_mc_b200/csrc/pmc_pair.cuh"
+#include "../../py_mc_b200/csrc/pmc_persist.cuh"
+
+#include <vector>
 
 using namespace pmc;
 
@@ -140,3 +143,74 @@ int hostemu_pair_sweep(int8_t *img, int lenX, int lenY, const uint32_t *thr7, ui
 }
 
 }  // extern "C"
+
+namespace {
+
+// The persistent kernel's per-thread pieces (pmc_persist.cuh), block after block and thread after thread: checks the
+// slab geometry, the halo rows and their exchange buffer -- everything but the barriers themselves.
+template <int MODEL>
+void persist_sweeps(const Image &im, const uint32_t *thr, uint64_t seed, uint32_t replica, uint64_t sweep0, int nsweeps,
+                    int nblocks, int T, long long *dB, long long *dS) {
+    uint32_t row[PLAN_WORDS];
+    Plan<MODEL>::build_row(thr, row);
+    const uint32_t(&rowref)[PLAN_WORDS] = row;
+    Plan<MODEL> plan;
+    plan.init(ParamRow{rowref});
+    const int lenX = im.lenX, nw = im.lenY / 128;
+    const PhiloxKey key = make_key(seed);
+    std::vector<std::vector<uint64_t>> slab(nblocks);
+    std::vector<uint64_t> halo((size_t)2 * nblocks * 2 * nw, 0xDEADBEEFDEADBEEFull);
+    auto r0 = [&](int b) { return persist_row0(b, lenX, nblocks); };
+    for (int b = 0; b < nblocks; ++b) {  // load: own rows and one row either side, both colours
+        const int nrows = r0(b + 1) - r0(b);
+        slab[b].assign((size_t)2 * (nrows + 2) * nw, 0);
+        for (int colour = 0; colour < 2; ++colour)
+            for (int lr = -1; lr <= nrows; ++lr)
+                for (int w = 0; w < nw; ++w)
+                    persist_word(slab[b].data(), nrows, nw, colour, lr, w) =
+                        gather(im, colour, ((r0(b) + lr) % lenX + lenX) % lenX, w, 0, 0);
+    }
+    for (int sw = 0; sw < nsweeps; ++sw)
+        for (int colour = 0; colour < 2; ++colour) {
+            for (int b = 0; b < nblocks; ++b)
+                for (int t = 0; t < T; ++t)
+                    persist_pass<MODEL>(slab[b].data(), r0(b + 1) - r0(b), nw, r0(b), colour, plan, replica,
+                                        2 * (sweep0 + sw) + colour, key, t, T, *dB, *dS);
+            for (int b = 0; b < nblocks; ++b)
+                for (int t = 0; t < T; ++t)
+                    persist_publish(slab[b].data(), r0(b + 1) - r0(b), nw, colour, b, nblocks, halo.data(), t, T);
+            for (int b = 0; b < nblocks; ++b)
+                for (int t = 0; t < T; ++t)
+                    persist_collect(slab[b].data(), r0(b + 1) - r0(b), nw, colour, b, nblocks, halo.data(), t, T);
+        }
+    for (int b = 0; b < nblocks; ++b) {  // store
+        const int nrows = r0(b + 1) - r0(b);
+        for (int colour = 0; colour < 2; ++colour)
+            for (int lr = 0; lr < nrows; ++lr)
+                for (int w = 0; w < nw; ++w) {
+                    const uint64_t v = persist_word(slab[b].data(), nrows, nw, colour, lr, w);
+                    const int i = r0(b) + lr, q = (i + colour) & 1;
+                    for (int l = 0; l < 64; ++l) {
+                        const int bit = (int)((v >> l) & 1ull);
+                        *im.site(i, 2 * (64 * w + l) + q) = MODEL == MODEL_ISING ? (int8_t)(2 * bit - 1) : (int8_t)bit;
+                    }
+                }
+    }
+}
+
+}  // namespace
+
+extern "C" int hostemu_persist_sweeps(int model, int8_t *img, int lenX, int lenY, const uint32_t *thr, uint64_t seed,
+                                      uint32_t replica, uint64_t sweep0, int nsweeps, int nblocks, int nthreads,
+                                      long long *dB, long long *dS) {
+    if (lenY % 128 || (lenX & 1) || nblocks < 1 || nblocks > lenX || nthreads < 1) return -1;
+    Image im = {img, lenX, lenY};
+    *dB = *dS = 0;
+    if (model == MODEL_ISING)
+        persist_sweeps<MODEL_ISING>(im, thr, seed, replica, sweep0, nsweeps, nblocks, nthreads, dB, dS);
+    else if (model == MODEL_LATGAS)
+        persist_sweeps<MODEL_LATGAS>(im, thr, seed, replica, sweep0, nsweeps, nblocks, nthreads, dB, dS);
+    else
+        return -1;
+    return 0;
+}

@@ -81,3 +81,26 @@ def test_pair_core_matches_specification(core, shape, J, kT):
     o_pair.sweep_classes(ref, thr, seed, 0, 4, classes=[1, 6, 9, 14])
     core.pair_sweep(cfg, thr, seed, 0, 4, class_mask=(1 << 1) | (1 << 6) | (1 << 9) | (1 << 14))
     assert np.array_equal(cfg, ref)
+
+
+@pytest.mark.parametrize("shape,nblocks,nthreads", [((8, 128), 1, 32), ((8, 128), 8, 32), ((10, 256), 3, 64),
+                                                    ((22, 384), 7, 32), ((16, 128), 5, 96)])
+def test_persistent_kernel_slab_logic_matches_specification(core, shape, nblocks, nthreads):
+    """pmc_persist.cuh block after block on the host: uneven slabs, one-row slabs, a single block that is its own
+    neighbour, more threads than words; Ising against the numpy specification, lattice gas against it too."""
+    seed, replica, J, kT = 99, 2, -1.0, 2.3
+    ref = o_ising.init_config(seed, replica, *shape)
+    cfg = ref.copy()
+    B = o_ising.bond_sum(cfg)
+    dB, dM = core.persist_sweeps(core.MODEL_ISING, cfg, ising_table(J, kT), seed, replica, 3, 4, nblocks, nthreads)
+    for sw in range(3, 7):
+        o_ising.sweep(ref, J, kT, seed, replica, sw)
+    assert np.array_equal(cfg, ref)
+    assert B + dB == o_ising.bond_sum(cfg) and dM == int(cfg.astype(np.int64).sum()) - int(o_ising.init_config(seed, replica, *shape).astype(np.int64).sum())
+    thr = o_latgas.threshold_table(-0.7, -0.2, 0.1, 0.8)
+    ref = o_latgas.init_config(seed, replica, *shape)
+    cfg = ref.copy()
+    core.persist_sweeps(core.MODEL_LATGAS, cfg, thr, seed, replica, 0, 3, nblocks, nthreads)
+    for sw in range(3):
+        o_latgas.sweep(ref, thr, seed, replica, sw)
+    assert np.array_equal(cfg, ref)
