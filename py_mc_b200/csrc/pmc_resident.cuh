@@ -1,4 +1,4 @@
-// pmc_resident.cuh -- K9: whole-lattice-resident kernel for batches of small lattices.
+// pmc_resident.cuh -- K10: whole-lattice-resident kernel for batches of small lattices.
 //
 // The reference runs one replica per MPI rank and touches its lattice one site at a time
 // (py_mc/mc.py:170-185, py_mc/mc_mpi.py:47-56).  When a handle holds many replicas whose bit image fits

@@ -815,7 +815,7 @@ int pymc_create(const pymc_params *p, pymc_handle **out) {
     DeviceGuard guard(p->device);
     int rc = PYMC_OK;
     if (guard.ok) {
-        // K9 (pmc_resident.cuh): one block keeps one replica in shared memory for a whole call.  Chosen for batches
+        // K10 (pmc_resident.cuh): one block keeps one replica in shared memory for a whole call.  Chosen for batches
         // that give every SM a replica and whose bit image is small; PYMC_KERNEL_RESIDENT forces it wherever it fits.
         int sms = 0, smem = 0;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, p->device);
@@ -1150,7 +1150,7 @@ static int launch_persistent(pymc_handle *h, int64_t nsweeps) {
     return PYMC_OK;
 }
 
-// K9: nsteps steps (flip sweep and / or pair pass each) of every replica in one launch per <= 4096 steps.
+// K10: nsteps steps (flip sweep and / or pair pass each) of every replica in one launch per <= 4096 steps.
 static int launch_resident(pymc_handle *h, int64_t nsteps, bool flip, uint32_t mask_even, uint32_t mask_odd) {
     REQUIRE(!flip || h->tables_set, PYMC_ERR_STATE, "sweep: call pymc_set_accept_tables first");
     REQUIRE(!(mask_even | mask_odd) || h->pair_plans, PYMC_ERR_STATE, "pair sweep: call pymc_set_pair_tables first");

@@ -1,4 +1,4 @@
-"""GPU: the whole-lattice-resident kernel (K9, pmc_resident.cuh) against the CPU specification and against
+"""GPU: the whole-lattice-resident kernel (K10, pmc_resident.cuh) against the CPU specification and against
 the per-pass kernels: flip sweeps of both models, pair-exchange passes, the mixed step, several steps per
 launch, both layouts, per-replica temperatures, and the automatic choice for batches of small lattices."""
 import numpy as np
