@@ -11,7 +11,7 @@
 // layout, a quarter of the fused kernel's instructions, is paid once per call instead of once per sweep.
 //
 // Same random-stream indexing (word = global row * nw + w), so the trajectory is that of every other
-// sweep kernel (tests/test_gpu_persist.py; the per-block logic also runs on the host in
+// sweep kernel (tests/test_zy_gpu_persist.py; the per-block logic also runs on the host in
 // tests/test_hostemu_core.py, block after block, which checks the slab geometry and the halo plumbing).
 //
 // The per-thread pieces are plain functions of (thread index t, thread count T) so that they can be driven

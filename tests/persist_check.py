@@ -12,7 +12,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 from py_mc_b200 import _cabi  # noqa: E402
 from py_mc_b200.ising2D import ising2D  # noqa: E402
-import test_gpu_persist as T  # noqa: E402
+import test_zy_gpu_persist as T  # noqa: E402
 
 res = {}
 t0 = time.time()
