@@ -9,6 +9,7 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -858,8 +859,9 @@ int pymc_create(const pymc_params *p, pymc_handle **out) {
                             "pymc_create: the persistent kernel needs lenY %% 128 == 0, cooperative launches and row slabs "
                             "(%zu bytes) within the %d bytes of shared memory of a block", slab, smem);
             }
+            const char *off = getenv("PYMC_NO_PERSISTENT");  // escape hatch: keep AUTO on the per-sweep kernels
             h->persist = p->kernel == PYMC_KERNEL_PERSISTENT ||
-                         (PMC_PERSIST_AUTO && p->kernel == PYMC_KERNEL_AUTO && pfits && p->nreplicas == 1 &&
+                         (PMC_PERSIST_AUTO && !(off && off[0] == '1') && p->kernel == PYMC_KERNEL_AUTO && pfits && p->nreplicas == 1 &&
                           (size_t)p->lenX * p->lenY >= PERSIST_AUTO_MIN_SITES);
             h->persist_blocks = blocks;
             h->persist_smem = slab;
