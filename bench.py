@@ -176,7 +176,7 @@ def workload_name(args, world=None):
         name = ("ising2d" if args.rx_model == "ising" else "hardcore_lattice_gas_mu=%g" % args.rx_mu)
         return ("%s_replica_exchange_%d_replicas_of_%dx%d_per_gpu_kT=%.2f..%.2f_exchange_every_%d_sweeps"
                 % (name, args.rx_replicas, args.rx_L, args.rx_L, args.rx_kT_lo, args.rx_kT_hi, args.rx_every))
-    return "ising2d_%dx%d_single_replica_checkerboard_kT=Tc_J=-1" % (args.L, args.L)
+    return "ising2d_%dx%d_single_replica_checkerboard_kT=%s_J=-1" % (args.L, args.L, "Tc" if args.kT == TC else "%g" % args.kT)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -470,7 +470,7 @@ def run_ours(args):
 
     L = args.L
     layout = _cabi.LAYOUT_BITS if args.layout == "bits" else _cabi.LAYOUT_INT8
-    thr = ising2D(-1.0)._pmc_thresholds(TC)[None, :]
+    thr = ising2D(-1.0)._pmc_thresholds(args.kT)[None, :]
     nsites = L * L
 
     def make(lay):
@@ -622,6 +622,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--layout", default="int8", choices=["int8", "bits"])
     ap.add_argument("--L", type=int, default=16384)
+    ap.add_argument("--kT", type=float, default=TC, help="temperature of the single-lattice workload (default T_c; "
+                    "SURVEY 8d also asks for 2.0 and 5.0)")
     ap.add_argument("--e2e-sweeps", type=int, default=64)
     ap.add_argument("--also-bits", action="store_true", default=True)
     ap.add_argument("--no-also-bits", dest="also_bits", action="store_false")
