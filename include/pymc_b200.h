@@ -96,6 +96,13 @@ int pymc_destroy(pymc_handle *h);
 int pymc_set_stream(pymc_handle *h, void *cuda_stream);
 int pymc_reset_stream(pymc_handle *h);
 int pymc_synchronize(pymc_handle *h);
+/* Barriers inside kernels (persistent sweep kernel, slab neighbour barrier) wait a bounded time.  If one gives up,
+ * the lattices of the handle are no longer valid: the next call that synchronises and returns data
+ * (pymc_synchronize, pymc_download_config, pymc_get_tracked, pymc_reduce_observables[_static], pymc_get_replica_to_T,
+ * pymc_rx_get_*, pymc_stats_get, pymc_timer_stop) returns PYMC_ERR_CUDA with a message instead of data, once.
+ * No counterpart in the reference.  pymc_debug_raise_async_error raises that condition artificially
+ * (which = 0 persistent kernel, 1 slab barrier) so that the error path can be tested. */
+int pymc_debug_raise_async_error(pymc_handle *h, int which);
 
 /* ---- configurations ---------------------------------------------------------------
  * Host format: int8 row-major [lenX][lenY], +1/-1 (Ising) or 0/1 (lattice gas): the

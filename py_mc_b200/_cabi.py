@@ -32,6 +32,7 @@ SYMBOLS = [
     "pymc_create_slab", "pymc_slab_ipc_export", "pymc_slab_connect", "pymc_slab_connect_local",
     "pymc_slab_push_halos", "pymc_slab_status",
     "pymc_discs_timer", "pymc_stats_reset", "pymc_stats_accumulate", "pymc_stats_get",
+    "pymc_debug_raise_async_error",
 ]
 
 
@@ -77,6 +78,7 @@ def _load():
         "pymc_set_stream": [P, P],
         "pymc_reset_stream": [P],
         "pymc_synchronize": [P],
+        "pymc_debug_raise_async_error": [P, I],
         "pymc_upload_config": [P, I, P, C.c_size_t],
         "pymc_download_config": [P, I, P, C.c_size_t],
         "pymc_init_random": [P],
@@ -227,6 +229,10 @@ class Lattices:
 
     def synchronize(self):
         check(lib.pymc_synchronize(self._h))
+
+    def debug_raise_async_error(self, which):
+        """Test hook: raise the flag a timed-out in-kernel barrier raises (0 persistent kernel, 1 slab barrier)."""
+        check(lib.pymc_debug_raise_async_error(self._h, int(which)))
 
     # -- configurations
     def _local_shape(self):

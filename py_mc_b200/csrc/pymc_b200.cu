@@ -640,7 +640,7 @@ struct pymc_handle {
     int8_t *peer_up[2], *peer_dn[2];      // neighbours' two lattice buffers (CUDA IPC mappings); [k] pairs with my buffer k
     unsigned long long *flags;            // [2] epochs written by the up / down neighbour
     unsigned long long *peer_up_flags, *peer_dn_flags;
-    int *slab_error;                      // device flag: set if a neighbour did not arrive in time
+    int *slab_error;                      // device view of err_host[1]: set if a neighbour did not arrive in time
     int8_t *buf[2];                       // the two ping-pong buffers by fixed index (i8 / i8_alt swap)
     uint64_t slab_epoch;
     unsigned int *slab_done;              // block counter used by the in-kernel barrier
@@ -655,9 +655,12 @@ struct pymc_handle {
     int persist_blocks, persist_threads;
     size_t persist_smem;
     unsigned int *persist_counter; // grid barrier arrivals (zeroed before every launch)
-    int *persist_err;              // device flag: a block timed out at the barrier
+    int *persist_err;              // device view of err_host[0]: a block timed out at the barrier
     uint64_t *persist_halo;        // [2][blocks][2][nw]
     bool persist_attr[2];
+    // Time-outs of the in-kernel barriers are raised by the kernels in two ints of mapped pinned host memory, so
+    // that every entry point which synchronises and returns data can look at them for free (check_async_errors).
+    volatile int *err_host;        // [0] persistent kernel, [1] slab neighbour barrier
     bool tables_set;
     bool dirty;                    // configurations changed since the tracked observables were based
     uint64_t sweep_counter;
@@ -718,6 +721,31 @@ struct DeviceGuard {
         }                                                                                            \
     } while (0)
 
+// Call after the handle's stream has been synchronised.  A barrier inside a kernel that gave up waiting leaves
+// the lattices of the handle in an undefined state: report it (once) instead of returning their contents.
+static int check_async_errors(pymc_handle *h, const char *where) {
+    if (!h->err_host) return PYMC_OK;
+    if (h->err_host[0]) {
+        h->err_host[0] = 0;
+        return fail(PYMC_ERR_CUDA,
+                    "%s: a block of the persistent sweep kernel timed out at a barrier; the configurations and "
+                    "tracked sums of this handle are invalid (upload or initialise them again)", where);
+    }
+    if (h->err_host[1]) {
+        h->err_host[1] = 0;
+        return fail(PYMC_ERR_CUDA,
+                    "%s: a neighbouring slab did not reach a barrier in time; the configurations and tracked sums of "
+                    "this handle are invalid", where);
+    }
+    return PYMC_OK;
+}
+
+#define CHECK_ASYNC(h)                                   \
+    do {                                                 \
+        int _rc = check_async_errors((h), __func__);     \
+        if (_rc) return _rc;                             \
+    } while (0)
+
 extern "C" {
 
 int pymc_abi_version(void) { return PYMC_ABI_VERSION; }
@@ -744,8 +772,8 @@ int pymc_destroy(pymc_handle *h) {
         cudaFree(h->tracked);
         cudaFree(h->reduced);
         cudaFree(h->persist_counter);
-        cudaFree(h->persist_err);
         cudaFree(h->persist_halo);
+        if (h->err_host) cudaFreeHost((void *)h->err_host);
         cudaFree(h->staging);
         cudaFree(h->qbuf);
         cudaFree(h->betas);
@@ -756,7 +784,6 @@ int pymc_destroy(pymc_handle *h) {
         cudaFree(h->stats);
         cudaFree(h->stats_count);
         cudaFree(h->flags);
-        cudaFree(h->slab_error);
         cudaFree(h->slab_done);
         if (h->slab && h->nslabs > 1 && h->peer_up[0] && !h->local_peers) {
             cudaIpcCloseMemHandle(h->peer_up[0]);
@@ -881,6 +908,17 @@ int pymc_create(const pymc_params *p, pymc_handle **out) {
         h->stream = h->own_stream;
         check(cudaEventCreate(&h->ev0), "cudaEventCreate");
         check(cudaEventCreate(&h->ev1), "cudaEventCreate");
+        {
+            void *eh = nullptr, *ed = nullptr;
+            check(cudaHostAlloc(&eh, 2 * sizeof(int), cudaHostAllocMapped), "cudaHostAlloc(error flags)");
+            if (eh) {
+                memset(eh, 0, 2 * sizeof(int));
+                check(cudaHostGetDevicePointer(&ed, eh, 0), "cudaHostGetDevicePointer(error flags)");
+            }
+            h->err_host = (volatile int *)eh;
+            h->persist_err = (int *)ed;
+            h->slab_error = ed ? (int *)ed + 1 : nullptr;
+        }
         const size_t nrep = p->nreplicas;
         if (p->layout == PYMC_LAYOUT_INT8) {
             check(cudaMalloc(&h->i8, nrep * 2 * p->lenX * (size_t)h->nk), "cudaMalloc(spins)");
@@ -933,11 +971,7 @@ int pymc_reset_stream(pymc_handle *h) {
 int pymc_synchronize(pymc_handle *h) {
     ENTER(h);
     CUDA_TRY(cudaStreamSynchronize(h->stream));
-    if (h->persist_err) {
-        int flag = 0;
-        CUDA_TRY(cudaMemcpy(&flag, h->persist_err, sizeof(int), cudaMemcpyDeviceToHost));
-        REQUIRE(!flag, PYMC_ERR_CUDA, "pymc_synchronize: a block of the persistent sweep kernel timed out at the grid barrier");
-    }
+    CHECK_ASYNC(h);
     return PYMC_OK;
 }
 
@@ -997,6 +1031,7 @@ int pymc_download_config(pymc_handle *h, int replica, int8_t *host, size_t nsite
     CUDA_TRY(cudaGetLastError());
     CUDA_TRY(cudaMemcpyAsync(host, h->staging, nsites, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(cudaStreamSynchronize(h->stream));
+    CHECK_ASYNC(h);
     return PYMC_OK;
 }
 
@@ -1096,6 +1131,7 @@ int pymc_get_replica_to_T(pymc_handle *h, int32_t *map, int n) {
             h->p.nreplicas_global, n);
     CUDA_TRY(cudaMemcpyAsync(map, h->rep_to_T, (size_t)n * 4, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(cudaStreamSynchronize(h->stream));
+    CHECK_ASYNC(h);
     return PYMC_OK;
 }
 
@@ -1121,9 +1157,7 @@ static int launch_persistent(pymc_handle *h, int64_t nsweeps) {
     }
     if (!h->persist_counter) {
         CUDA_TRY(cudaMalloc(&h->persist_counter, sizeof(unsigned int)));
-        CUDA_TRY(cudaMalloc(&h->persist_err, sizeof(int)));
         CUDA_TRY(cudaMalloc(&h->persist_halo, (size_t)2 * h->persist_blocks * 2 * h->nw * 8));
-        CUDA_TRY(cudaMemsetAsync(h->persist_err, 0, sizeof(int), h->stream));
     }
     Lat L = make_lat(h);
     while (nsweeps > 0) {
@@ -1387,6 +1421,7 @@ static int fetch_pairs(pymc_handle *h, const unsigned long long *dev, int64_t *b
         if (second) second[r] = tmp[2 * r + 1];
     }
     delete[] tmp;
+    CHECK_ASYNC(h);
     return PYMC_OK;
 }
 
@@ -1537,6 +1572,7 @@ int pymc_rx_get_energies(pymc_handle *h, double *energies, int n) {
             h->p.nreplicas_global);
     CUDA_TRY(cudaMemcpyAsync(energies, h->energies, (size_t)n * 8, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(cudaStreamSynchronize(h->stream));
+    CHECK_ASYNC(h);
     return PYMC_OK;
 }
 
@@ -1547,6 +1583,7 @@ int pymc_rx_get_stats(pymc_handle *h, uint64_t *tried, uint64_t *accepted, int n
     CUDA_TRY(cudaMemcpyAsync(tried, h->rx_tried, (size_t)n * 8, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(cudaMemcpyAsync(accepted, h->rx_accepted, (size_t)n * 8, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(cudaStreamSynchronize(h->stream));
+    CHECK_ASYNC(h);
     return PYMC_OK;
 }
 
@@ -1869,6 +1906,7 @@ int pymc_stats_get(pymc_handle *h, double *sums, uint64_t *counts, int ntemps, i
     CUDA_TRY(cudaMemcpyAsync(sums, h->stats, (size_t)ntemps * NSTAT * 8, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(cudaMemcpyAsync(counts, h->stats_count, (size_t)ntemps * 8, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(cudaStreamSynchronize(h->stream));
+    CHECK_ASYNC(h);
     return PYMC_OK;
 }
 
@@ -1917,6 +1955,9 @@ int pymc_create_slab(const pymc_params *p, int slab_index, int nslabs, pymc_hand
             PYMC_ERR_UNSUPPORTED,
             "pymc_create_slab: need lenX/nslabs %% %d == 0 and lenY %% %d == 0 (got %dx%d over %d slabs)", FUSED_TH,
             128 * FUSED_TW, p->lenX, p->lenY, nslabs);
+    // slab_push_halos_kernel puts 2 * nreplicas colour planes into gridDim.z (limit 65535)
+    REQUIRE(p->nreplicas <= 32767, PYMC_ERR_UNSUPPORTED, "pymc_create_slab: at most 32767 replicas per slab handle (got %d)",
+            p->nreplicas);
     const int Xl = p->lenX / nslabs;
     pymc_params q = *p;
     q.lenX = Xl + 4;  // two halo rows above and below the owned rows
@@ -1937,8 +1978,6 @@ int pymc_create_slab(const pymc_params *p, int slab_index, int nslabs, pymc_hand
     if (e == cudaSuccess) e = cudaMemset(h->i8_alt, 0, bytes);
     if (e == cudaSuccess) e = cudaMalloc(&h->flags, 16);
     if (e == cudaSuccess) e = cudaMemset(h->flags, 0, 16);
-    if (e == cudaSuccess) e = cudaMalloc(&h->slab_error, 4);
-    if (e == cudaSuccess) e = cudaMemset(h->slab_error, 0, 4);
     if (e == cudaSuccess) e = cudaMalloc(&h->slab_done, 8);
     if (e == cudaSuccess) e = cudaMemset(h->slab_done, 0, 8);
     if (e != cudaSuccess) {
@@ -2028,8 +2067,21 @@ int pymc_slab_push_halos(pymc_handle *h) {
 int pymc_slab_status(pymc_handle *h, int *status) {
     ENTER(h);
     REQUIRE(h->slab && status, PYMC_ERR_BADARG, "pymc_slab_status: bad arguments");
-    CUDA_TRY(cudaMemcpyAsync(status, h->slab_error, 4, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(cudaStreamSynchronize(h->stream));
+    *status = h->err_host ? h->err_host[1] : 0;  // reported here without being cleared
+    return PYMC_OK;
+}
+
+// Test hook for the error path of the in-kernel barriers: raises the same flag a timed-out barrier raises
+// (which = 0 persistent kernel, 1 slab neighbour barrier) from a kernel on the handle's stream.
+__global__ void raise_flag_kernel(int *flag) { *flag = 1; }
+
+int pymc_debug_raise_async_error(pymc_handle *h, int which) {
+    ENTER(h);
+    REQUIRE(which == 0 || which == 1, PYMC_ERR_BADARG, "pymc_debug_raise_async_error: which = %d", which);
+    REQUIRE(h->persist_err, PYMC_ERR_STATE, "pymc_debug_raise_async_error: no error flags");
+    raise_flag_kernel<<<1, 1, 0, h->stream>>>(which ? h->slab_error : h->persist_err);
+    CUDA_TRY(cudaGetLastError());
     return PYMC_OK;
 }
 
@@ -2057,6 +2109,7 @@ int pymc_timer_stop(pymc_handle *h, float *elapsed_ms) {
     CUDA_TRY(cudaEventRecord(h->ev1, h->stream));
     CUDA_TRY(cudaEventSynchronize(h->ev1));
     CUDA_TRY(cudaEventElapsedTime(elapsed_ms, h->ev0, h->ev1));
+    CHECK_ASYNC(h);
     return PYMC_OK;
 }
 
@@ -2109,6 +2162,10 @@ extern "C" int pymc_reduce_observables_static(pymc_handle *h, int64_t *bond, int
     int rc = static_obs_address(h->p.device, &acc);
     if (rc) return rc;
     const size_t nrep = (size_t)h->p.nreplicas;
+    // Row slabs: the reduction reads one halo row, which a neighbouring GPU may still be writing (same wait as
+    // in pymc_reduce_observables; a one-thread kernel, no allocation).
+    rc = slab_wait_async(h);
+    if (rc) return rc;
     // The array still holds whatever the previous call (of any handle on this GPU) left in it, and the
     // kernel adds into it: the part used now has to start from zero.
     CUDA_TRY(cudaMemsetAsync(acc, 0, nrep * 16, h->stream));
@@ -2125,5 +2182,6 @@ extern "C" int pymc_reduce_observables_static(pymc_handle *h, int64_t *bond, int
     CUDA_TRY(cudaMemcpy2DAsync(bond, 8, acc, 16, 8, nrep, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(cudaMemcpy2DAsync(second, 8, acc + 1, 16, 8, nrep, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(cudaStreamSynchronize(h->stream));
+    CHECK_ASYNC(h);
     return PYMC_OK;
 }

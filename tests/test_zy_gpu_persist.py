@@ -1,15 +1,10 @@
 """GPU: the persistent kernel (K11, pmc_persist.cuh) -- one lattice spread over the shared memory of all SMs for all
 sweeps of a call -- against the per-sweep kernels: same trajectory, same tracked sums, both layouts and models,
 uneven slabs, fewer rows than SMs, and the 4096 x 4096 case against the fused kernel."""
-import os
-
 import numpy as np
 import pytest
 
 pytestmark = pytest.mark.gpu
-# Cases beyond those already run on a B200 (see profiles/README.md) wait for PYMC_EXTENDED=1: the GPU budget of the
-# round in which this kernel was written ran out after the first, successful, parity and timing run.
-extended = pytest.mark.skipif(os.environ.get("PYMC_EXTENDED") != "1", reason="set PYMC_EXTENDED=1 (not yet run on a GPU)")
 
 
 def run_pair(model, shape, layout, thr, seed=5, calls=(2, 3), nreplicas=1):
@@ -74,7 +69,6 @@ def test_headline_lattice_matches_the_fused_kernel_and_is_the_automatic_choice()
     b.close()
 
 
-@extended
 @pytest.mark.parametrize("shape", [(148, 384), (1024, 1024)])
 @pytest.mark.parametrize("layout", [0, 1])
 def test_ising_more_shapes(shape, layout):
@@ -83,7 +77,6 @@ def test_ising_more_shapes(shape, layout):
     check_pair(run_pair(_cabi.MODEL_ISING, shape, layout, ising2D(-1.0)._pmc_thresholds(2.269185314213022)))
 
 
-@extended
 @pytest.mark.parametrize("layout", [0, 1])
 def test_lattice_gas_and_several_replicas(layout):
     from py_mc_b200 import _cabi
@@ -92,7 +85,6 @@ def test_lattice_gas_and_several_replicas(layout):
     check_pair(run_pair(_cabi.MODEL_LATGAS, (200, 256), layout, thr, calls=(4, 2), nreplicas=3))
 
 
-@extended
 def test_4096_against_the_fused_kernel():
     from py_mc_b200 import _cabi
     from py_mc_b200.ising2D import ising2D
@@ -109,6 +101,54 @@ def test_4096_against_the_fused_kernel():
     assert got[0][2] == "persistent_kernel"
     assert np.array_equal(got[0][0], got[1][0])
     assert int(got[0][1][0][0]) == int(got[1][1][0][0]) and int(got[0][1][1][0]) == int(got[1][1][1][0])
+
+
+def test_headline_lattice_bit_packed_matches_the_row_kernel():
+    """16384 x 16384 on the 1-bit layout: the persistent kernel (forced) against sweep_bits_rows_kernel (what
+    PYMC_KERNEL_TWO_PASS selects for this layout), which is pinned to the scalar C oracle at 4096 x 4096 in
+    test_gpu_ising.py -- the pin of this case to the reference is through that chain."""
+    from py_mc_b200 import _cabi
+    from py_mc_b200.ising2D import ising2D
+    thr = ising2D(-1.0)._pmc_thresholds(2.269185314213022)
+    L = 16384
+    got = []
+    for kernel in (_cabi.KERNEL_PERSISTENT, _cabi.KERNEL_TWO_PASS):
+        lat = _cabi.Lattices(_cabi.MODEL_ISING, L, L, seed=77, layout=_cabi.LAYOUT_BITS, kernel=kernel)
+        lat.init_random()
+        lat.set_accept_tables(thr[None, :])
+        lat.sweep(4)
+        lat.sweep(3)
+        lat.synchronize()
+        got.append((lat.download(0), lat.tracked(), lat.reduce_observables(), lat.sweep_kernel_info()[1]))
+        lat.close()
+    assert got[0][3] == "persistent_kernel" and got[1][3] == "sweep_bits_rows_kernel"
+    assert np.array_equal(got[0][0], got[1][0])
+    for k in (0, 1):
+        assert int(got[0][1][k][0]) == int(got[1][1][k][0]) == int(got[0][2][k][0])
+
+
+@pytest.mark.parametrize("layout", [0, 1])
+def test_lattice_gas_at_the_automatic_threshold(layout):
+    """MODEL_LATGAS on a single lattice of 2^27 sites: PYMC_KERNEL_AUTO takes the persistent kernel for calls of two
+    sweeps or more; same trajectory and tracked sums as the per-colour kernels."""
+    from py_mc_b200 import _cabi
+    from py_mc_b200.latgas import latticegas
+    thr = latticegas(Eads=-0.3, J=-1.0, mu=0.2)._pmc_thresholds(0.9)
+    shape = (8192, 16384)
+    got = []
+    for kernel in (_cabi.KERNEL_AUTO, _cabi.KERNEL_TWO_PASS):
+        lat = _cabi.Lattices(_cabi.MODEL_LATGAS, shape[0], shape[1], seed=31, layout=layout, kernel=kernel)
+        lat.init_random()
+        lat.set_accept_tables(thr[None, :])
+        lat.sweep(3)
+        lat.sweep(2)
+        lat.synchronize()
+        got.append((lat.download(0), lat.tracked(), lat.reduce_observables(), lat.sweep_kernel_info()[1]))
+        lat.close()
+    assert got[0][3] == "persistent_kernel" and got[1][3] != "persistent_kernel"
+    assert np.array_equal(got[0][0], got[1][0])
+    for k in (0, 1):
+        assert int(got[0][1][k][0]) == int(got[1][1][k][0]) == int(got[0][2][k][0])
 
 
 def test_refused_where_it_cannot_run():

@@ -7,7 +7,9 @@ GPU, 4096 replicas at most, shared by every handle on that GPU).  This file chec
 that the entry point returns exactly what pymc_reduce_observables returns (the sums are integers:
 tolerance zero) on consecutive calls, that what one call leaves in the shared array never shows up in
 the next result, and that a batch beyond the maximum is refused with a message instead of overrunning
-the array.  It is named to be collected last, and it must pass both on its own in a fresh process and
+the array; that the free device memory reported by the driver is the same before and after the calls
+(the property the name promises); and that a row-slab handle, whose reduction reads a halo row, gives the
+allocating entry point's numbers too.  It is named to be collected last, and it must pass both on its own in a fresh process and
 after the rest of the suite.
 """
 import numpy as np
@@ -69,3 +71,58 @@ def test_batch_beyond_static_maximum_is_refused():
     got = lat.reduce_observables_static()
     assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
     lat.close()
+
+
+def _free_device_memory():
+    """cudaMemGetInfo through the CUDA runtime the library itself is linked against."""
+    import ctypes as C
+    rt = C.CDLL("libcudart.so.12")
+    free, total = C.c_size_t(0), C.c_size_t(0)
+    assert rt.cudaMemGetInfo(C.byref(free), C.byref(total)) == 0
+    return free.value
+
+
+def test_device_memory_is_untouched_by_the_call():
+    """A host that may not allocate needs more than equal numbers: no device allocation may happen inside the call.
+    The first call on the device has already been made above or is made here before measuring (it only looks up
+    the static array's address)."""
+    from py_mc_b200 import _cabi
+    lat = _lattice(5, (64, 256), _cabi.LAYOUT_INT8, seed=3)
+    lat.sweep(2)
+    lat.reduce_observables_static()          # warm: address look-up, module fully loaded
+    lat.sweep(1)
+    lat.synchronize()
+    before = _free_device_memory()
+    for _ in range(3):
+        got = lat.reduce_observables_static()
+    after = _free_device_memory()
+    assert after == before, (before, after)
+    want = lat.reduce_observables()
+    assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+    lat.close()
+
+
+def test_row_slab_handles_agree_with_the_allocating_entry_point():
+    """Two row slabs of one 128 x 1024 lattice driven by this process (pymc_slab_connect_local): the reduction of a
+    slab reads the halo row above its first owned row."""
+    from py_mc_b200 import _cabi
+    from py_mc_b200.ising2D import ising2D
+    thr = ising2D(-1.0)._pmc_thresholds(2.3)[None, :]
+    slabs = [_cabi.Lattices(_cabi.MODEL_ISING, 128, 1024, seed=9, slab=(k, 2)) for k in range(2)]
+    for k, s in enumerate(slabs):
+        s.set_stream(0)  # one stream for both slabs: the sweeps below are ordered by issue order
+        s.slab_connect_local(slabs[(k - 1) % 2], slabs[(k + 1) % 2])
+    for s in slabs:
+        s.init_random()
+        s.set_accept_tables(thr)
+    for _ in range(3):
+        for s in slabs:
+            s.sweep(1)
+    for s in slabs:
+        s.synchronize()
+    for s in slabs:
+        want = s.reduce_observables()
+        got = s.reduce_observables_static()
+        assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+    for s in slabs:
+        s.close()
