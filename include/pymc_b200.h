@@ -53,9 +53,15 @@ typedef enum {
     PYMC_KERNEL_RESIDENT = 3, /* one block keeps one replica in shared memory for a whole call; needs    */
                               /* lenY % 128 == 0 and 2*lenX*lenY/16 bytes of shared memory.  AUTO takes */
                               /* it for batches of small lattices (>= one replica per SM, <= 32 KiB)    */
-    PYMC_KERNEL_PERSISTENT = 4 /* one lattice spread over the shared memory of all SMs (one row slab per  */
-                               /* block of a cooperative launch) for all sweeps of a call; needs         */
-                               /* lenY % 128 == 0 and lenX*lenY/8 bytes within the GPU's shared memory   */
+    PYMC_KERNEL_PERSISTENT = 4, /* one lattice spread over the shared memory of all SMs (one row slab per  */
+                                /* block of a cooperative launch, grid barrier per colour pass) for all   */
+                                /* sweeps of a call; needs lenY % 128 == 0 and lenX*lenY/8 bytes within    */
+                                /* the GPU's shared memory                                                */
+    PYMC_KERNEL_PBATCH = 5      /* the rows of ALL replicas of the handle cut into one piece per SM and    */
+                                /* kept in shared memory for all sweeps -- and, on one GPU, all replica   */
+                                /* exchanges -- of a call; neighbour flags instead of grid barriers.      */
+                                /* Needs lenY % 128 == 0 and nreplicas*lenX*lenY/8 bytes within the GPU's  */
+                                /* shared memory.  AUTO takes it from 2^20 sites on (calls of >= 2 sweeps) */
 } pymc_kernel;
 
 /* Number of acceptance-table entries per temperature: Ising 5 (index = number of aligned

@@ -13,7 +13,7 @@ from ._build import LIBPATH
 ABI_VERSION = 1
 MODEL_ISING, MODEL_LATGAS = 0, 1
 LAYOUT_INT8, LAYOUT_BITS = 0, 1
-KERNEL_AUTO, KERNEL_GENERIC, KERNEL_TWO_PASS, KERNEL_RESIDENT, KERNEL_PERSISTENT = 0, 1, 2, 3, 4
+KERNEL_AUTO, KERNEL_GENERIC, KERNEL_TWO_PASS, KERNEL_RESIDENT, KERNEL_PERSISTENT, KERNEL_PBATCH = 0, 1, 2, 3, 4, 5
 NCLASS = {MODEL_ISING: 5, MODEL_LATGAS: 10}
 
 # every symbol include/pymc_b200.h declares (tests check the library exports all of them)

@@ -1,0 +1,630 @@
+// pmc_pbatch.cuh -- K12: ALL replicas of a handle resident in the shared memory of the whole GPU for all sweeps
+// (and all replica exchanges) of a call.
+//
+// What it replaces: the run loop of the reference -- MCstep after MCstep with an exchange every
+// RXtrial_frequency steps (py_mc/mc_mpi.py:165-169, Xtrial :102-140) -- for a whole batch of replicas, or
+// CanonicalMonteCarlo.run's loop (py_mc/mc.py:198-199) for one large lattice.
+//
+// The rows of all replicas of the handle form one list of nrep * lenX rows; it is cut into B contiguous pieces
+// of (almost) equal length, one per block of a cooperative launch (B = number of SMs), whatever the replica
+// boundaries are.  A block loads its rows once (int8 -> bits, or bits as stored), keeps them in shared memory,
+// runs every sweep of the call on them and stores them once.  256 replicas of 1024 x 1024 are 32 MiB of bits,
+// exactly as much as one 16384 x 16384 lattice: both fill the 148 x 227 KiB of a B200 to 97 %, and 32 or 8
+// replicas (replica exchange spread over 8 GPUs) use all SMs just the same, which a one-block-per-replica
+// kernel cannot.
+//
+// Rows a block needs from other blocks (at most four per colour: the row above its first row, the row below its
+// last row, and -- because lattices are periodic -- row 0 / row lenX-1 of a replica that starts / ends in
+// another block) travel through a small exchange buffer in global memory.  There is NO grid barrier in a sweep:
+//   * the rows other blocks need ("export rows") are updated FIRST in every colour pass and written straight to
+//     the exchange buffer by the threads that computed them; the last of those warps then raises the block's
+//     flag (a pass counter) -- all of this while the rest of the block is already working on the other rows;
+//   * the only readers of remote rows are those same first items of the NEXT pass; each polls the flag of the
+//     block it depends on (already raised, unless that block lags a whole pass behind) and reads the word
+//     from L2.
+// So the neighbour exchange is fully overlapped with the update and costs no block-wide synchronisation beyond
+// the one __syncthreads that ends a colour pass.  (The single-lattice kernel K11, pmc_persist.cuh, meets at a
+// grid barrier twice per sweep: measured 2.9 us per pass, 5.5 % of a 16384^2 sweep and half of a 1024^2 one.)
+//
+// Replica exchange inside the kernel (one GPU holds all replicas): after the sweeps of an exchange interval the
+// blocks recompute the exact bond sum and magnetisation of their rows per replica, publish them, meet at ONE grid
+// barrier, and every block evaluates the same pair decisions as rx_decide_kernel (pmc_rx.cuh) from the same
+// inputs; block 0 also writes the new replica <-> temperature maps (double-buffered by exchange parity).  The
+// lattices never leave the chip between exchanges.
+//
+// Observables: the update loop keeps no running sums at all (the per-word popcounts of the other kernels are
+// gone); the exact sums are recomputed from the resident lattice where they are needed -- at an exchange and at
+// the end of the launch.
+//
+// Random-stream indexing is that of every other sweep kernel (word = row-in-replica * nw + w, replica, step), so
+// the trajectories are identical (tests/test_gpu_pbatch.py; the per-thread pieces below also run on the host,
+// block after block, in tests/test_hostemu_core.py, which checks the geometry and the exchange-buffer plumbing).
+#pragma once
+#include "pmc_core.cuh"
+#ifdef __CUDACC__
+#include "pmc_tiled_i8.cuh"  // pack16 / unpack16
+#endif
+
+#ifndef PMC_WARP
+#define PMC_WARP 32  // the host shim compiles with 1: a "warp" of one thread
+#endif
+
+namespace pmc {
+
+constexpr int PB_MAXSEG = 8;  // replicas a block may hold rows of
+constexpr int PB_MAXX = 4;    // rows a block takes from / gives to other blocks, per colour
+constexpr int PB_MAX_THREADS = 1024;
+
+// ---- geometry of block b (pure function of b, B, nrep, lenX) -------------------------------------------------
+struct PBGeom {
+    int R0, nrows;             // first row (in the list of all rows of all replicas) and number of rows
+    int rep_first, nseg;       // first replica with rows here; number of replicas with rows here
+    int i0;                    // row-in-replica of local row 0
+    int nimp;                  // rows taken from other blocks
+    int imp_slot[PB_MAXX];     // ... their slot in the exchange buffer
+    int imp_blk[PB_MAXX];      // ... the block that writes it
+    int up0, dn1, h2, h3;      // import index of: row above local row 0, row below the last local row, row 0 of the
+                               // first replica (it began in an earlier block), last row of the last replica; or -1
+    int nexp;                  // (local row -> slot) pairs given to other blocks
+    int exp_row[PB_MAXX], exp_slot[PB_MAXX];
+    int nxrow;                 // distinct export rows, ascending
+    int xrow[PB_MAXX];
+};
+
+__host__ __device__ __forceinline__ int pb_row0(int b, long long NR, int B) { return (int)(((long long)b * NR) / B); }
+__host__ __device__ __forceinline__ int pb_block_of_row(long long g, long long NR, int B) {
+    return (int)(((g + 1) * B - 1) / NR);
+}
+// exchange-buffer slots: first / last row of block b, row 0 / row lenX-1 of replica r
+__host__ __device__ __forceinline__ int pb_bslot(int b, int last) { return 2 * b + last; }
+__host__ __device__ __forceinline__ int pb_rslot(int B, int r, int last) { return 2 * B + 2 * r + last; }
+__host__ __device__ __forceinline__ int pb_nslots(int B, int nrep) { return 2 * B + 2 * nrep; }
+
+__host__ __device__ inline void pb_geometry(int b, int B, int nrep, int lenX, PBGeom &g) {
+    const long long NR = (long long)nrep * lenX;
+    g.R0 = pb_row0(b, NR, B);
+    const int R1 = pb_row0(b + 1, NR, B);
+    g.nrows = R1 - g.R0;
+    g.rep_first = g.R0 / lenX;
+    const int rep_last = (R1 - 1) / lenX;
+    g.nseg = rep_last - g.rep_first + 1;
+    g.i0 = g.R0 - g.rep_first * lenX;
+    const int i1 = (R1 - 1) - rep_last * lenX;
+    g.nimp = g.nexp = g.nxrow = 0;
+    g.up0 = g.dn1 = g.h2 = g.h3 = -1;
+    for (int k = 0; k < PB_MAXX; ++k) g.imp_slot[k] = g.imp_blk[k] = g.exp_row[k] = g.exp_slot[k] = g.xrow[k] = 0;
+    const long long first_last = (long long)g.rep_first * lenX + lenX - 1;  // last row of the first replica
+    const long long last_first = (long long)rep_last * lenX;                // row 0 of the last replica
+#define PB_IMP(slot, blk) (g.imp_slot[g.nimp] = (slot), g.imp_blk[g.nimp] = (blk), g.nimp++)
+#define PB_EXP(row, slot) (g.exp_row[g.nexp] = (row), g.exp_slot[g.nexp] = (slot), g.nexp++)
+    // local row 0: its upper neighbour
+    if (g.i0 > 0) {  // ... is the last row of the block before
+        g.up0 = PB_IMP(pb_bslot(b - 1, 1), b - 1);
+        PB_EXP(0, pb_bslot(b, 0));
+    } else if (first_last >= R1) {  // ... is the last row of this replica, which lives in a later block
+        g.up0 = PB_IMP(pb_rslot(B, g.rep_first, 1), pb_block_of_row(first_last, NR, B));
+        PB_EXP(0, pb_rslot(B, g.rep_first, 0));
+    }
+    // last local row: its lower neighbour
+    if (i1 < lenX - 1) {
+        g.dn1 = PB_IMP(pb_bslot(b + 1, 0), b + 1);
+        PB_EXP(g.nrows - 1, pb_bslot(b, 1));
+    } else if (last_first < g.R0) {  // row 0 of this replica, in an earlier block
+        g.dn1 = PB_IMP(pb_rslot(B, rep_last, 0), pb_block_of_row(last_first, NR, B));
+        PB_EXP(g.nrows - 1, pb_rslot(B, rep_last, 1));
+    }
+    // the first replica began in an earlier block and ends inside this one (not on my last row: that is the case above)
+    if (g.i0 > 0 && first_last < R1 - 1) {
+        g.h2 = PB_IMP(pb_rslot(B, g.rep_first, 0), pb_block_of_row((long long)g.rep_first * lenX, NR, B));
+        PB_EXP((int)(first_last - g.R0), pb_rslot(B, g.rep_first, 1));
+    }
+    // the last replica begins inside this block (not on my first row) and ends in a later one
+    if (i1 < lenX - 1 && last_first > g.R0) {
+        g.h3 = PB_IMP(pb_rslot(B, rep_last, 1), pb_block_of_row(last_first + lenX - 1, NR, B));
+        PB_EXP((int)(last_first - g.R0), pb_rslot(B, rep_last, 0));
+    }
+#undef PB_IMP
+#undef PB_EXP
+    // distinct export rows, ascending (insertion into a list of at most four)
+    for (int e = 0; e < g.nexp; ++e) {
+        const int r = g.exp_row[e];
+        int pos = 0;
+        bool dup = false;
+        for (int k = 0; k < g.nxrow; ++k) {
+            if (g.xrow[k] == r) dup = true;
+            if (g.xrow[k] < r) pos = k + 1;
+        }
+        if (dup) continue;
+        for (int k = g.nxrow; k > pos; --k) g.xrow[k] = g.xrow[k - 1];
+        g.xrow[pos] = r;
+        ++g.nxrow;
+    }
+}
+
+// What a thread needs besides the geometry: everything that sits in shared or global memory.
+struct PBCtx {
+    uint64_t *s;                 // [2 colours][nrows][nw] resident rows of this block
+    const int *segoff;           // [nseg] row-in-replica minus local row, per replica of this block
+    const int *segstart;         // [nseg] first local row of each replica of this block (segstart[0] = 0)
+    const uint32_t *splan;       // [nseg][PLAN_WORDS] plan row of each replica (its current temperature)
+    uint64_t *xbuf;              // [2 colours][nslots][nw] exchange buffer (global)
+    unsigned int *flags;         // [B] number of export events of each block (1 after the load)
+    unsigned int *cnt;           // shared: export warps that have finished, summed over all passes
+    int *err;
+    int lenX, nw, nw_shift;      // nw_shift >= 0: nw is that power of two
+    int nslots, b;
+    uint32_t rep_offset;
+    PhiloxKey key;
+};
+
+struct SmemRow {
+    const uint32_t *p;
+    __device__ __forceinline__ uint32_t operator[](int k) const { return p[k]; }
+};
+
+__device__ __forceinline__ uint64_t pb_ldcg(const uint64_t *p) {
+#ifdef __CUDA_ARCH__
+    return __ldcg(p);
+#else
+    return *p;
+#endif
+}
+
+// Wait until block `blk` has published `need` export events.  Bounded: a time-out raises *err.
+__device__ __forceinline__ void pb_wait(const unsigned int *flag, unsigned int need, int *err) {
+#ifdef __CUDA_ARCH__
+    if (*(volatile const unsigned int *)flag < need && !*(volatile int *)err) {  // after one time-out nobody waits again
+        const long long t0 = clock64();
+        while (*(volatile const unsigned int *)flag < need) {
+            if (clock64() - t0 > 4000000000LL) {
+                *err = 1;
+                break;
+            }
+        }
+    }
+    __threadfence();  // what that block wrote before raising its flag is visible to the loads that follow
+#else
+    if (*flag < need) *err = 1;  // the host drives the blocks in lock step: the flag must be there already
+#endif
+}
+
+// local row, word column, replica segment and row-in-replica of ordinal `o` when the export rows come first
+__device__ __forceinline__ void pb_locate(const PBGeom &g, const PBCtx &c, int o, bool exports_first, int &lr, int &w, int &seg,
+                                          int &i) {
+    int ro;
+    if (c.nw_shift >= 0) {
+        ro = o >> c.nw_shift;
+        w = o & (c.nw - 1);
+    } else {
+        ro = o / c.nw;
+        w = o - ro * c.nw;
+    }
+    if (!exports_first) {
+        lr = ro;
+    } else if (ro < g.nxrow) {
+        lr = ro == 0 ? g.xrow[0] : (ro == 1 ? g.xrow[1] : (ro == 2 ? g.xrow[2] : g.xrow[3]));
+    } else {
+        lr = ro - g.nxrow;
+#pragma unroll
+        for (int k = 0; k < PB_MAXX; ++k)
+            if (k < g.nxrow && lr >= g.xrow[k]) ++lr;
+    }
+    seg = 0;
+    for (int k = 1; k < g.nseg; ++k) seg += lr >= c.segstart[k];
+    i = lr + c.segoff[seg];
+}
+
+// rows above / below local row lr (row-in-replica i): a local row (>= 0) or -1 - import index
+__device__ __forceinline__ void pb_neighbours(const PBGeom &g, int lenX, int lr, int i, int &up, int &dn) {
+    up = lr - 1;
+    dn = lr + 1;
+    if (i == 0) {
+        const int G = lr + lenX - 1;  // the replica's last row
+        up = G < g.nrows ? G : -1 - (lr == 0 ? g.up0 : g.h3);
+    } else if (lr == 0) {
+        up = -1 - g.up0;
+    }
+    if (i == lenX - 1) {
+        const int G = lr - (lenX - 1);  // the replica's row 0
+        dn = G >= 0 ? G : -1 - (lr == g.nrows - 1 ? g.dn1 : g.h2);
+    } else if (lr == g.nrows - 1) {
+        dn = -1 - g.dn1;
+    }
+}
+
+// word w of the other colour in the row above / below: shared memory, or the exchange buffer once its writer is there
+__device__ __forceinline__ uint64_t pb_row_word(const PBGeom &g, const PBCtx &c, int oc, int row, int w, unsigned int need) {
+    if (row >= 0) return c.s[((size_t)oc * g.nrows + row) * c.nw + w];
+    const int k = -1 - row;
+    pb_wait(c.flags + g.imp_blk[k], need, c.err);
+    return pb_ldcg(c.xbuf + ((size_t)oc * c.nslots + g.imp_slot[k]) * c.nw + w);
+}
+
+// One colour pass of one thread.  `events` = export events every block has completed before this pass (1 + number
+// of passes since the load).  Every thread of a warp must call this together (update_word votes).
+template <int MODEL>
+__device__ __forceinline__ void pb_pass(const PBGeom &g, const PBCtx &c, int colour, uint64_t step, unsigned int events, int t,
+                                        int T) {
+    const int oc = colour ^ 1, items = g.nrows * c.nw, nexport = g.nxrow * c.nw;
+    Plan<MODEL> plan;
+    int cur = -1;
+#pragma unroll 1
+    for (int base = 0; base < items; base += T) {
+        const bool on = base + t < items;
+        const int o = on ? base + t : items - 1;
+        int lr, w, seg, i, up, dn;
+        pb_locate(g, c, o, true, lr, w, seg, i);
+        pb_neighbours(g, c.lenX, lr, i, up, dn);
+        if (seg != cur) {
+            plan.init(SmemRow{c.splan + seg * PLAN_WORDS});
+            cur = seg;
+        }
+        uint64_t *row_c = c.s + ((size_t)colour * g.nrows + lr) * c.nw;
+        const uint64_t *row_o = c.s + ((size_t)oc * g.nrows + lr) * c.nw;
+        const uint64_t S = row_c[w], C = row_o[w];
+        uint64_t Sd;
+        if ((i + colour) & 1)
+            Sd = (C >> 1) | (row_o[w == c.nw - 1 ? 0 : w + 1] << 63);
+        else
+            Sd = (C << 1) | (row_o[w == 0 ? c.nw - 1 : w - 1] >> 63);
+        const uint64_t U = pb_row_word(g, c, oc, up, w, events), D = pb_row_word(g, c, oc, dn, w, events);
+        int dB, dS;  // unused: the sums are recomputed where they are needed (pb_reduce)
+        const uint64_t Snew = update_word<MODEL>(S, U, D, C, Sd, on ? ~0ull : 0ull, plan, (uint32_t)(i * c.nw + w),
+                                                 c.rep_offset + (uint32_t)(g.rep_first + seg), step, c.key, dB, dS);
+        if (on) {
+            row_c[w] = Snew;
+            if (o < nexport) {
+                for (int e = 0; e < g.nexp; ++e)
+                    if (g.exp_row[e] == lr) c.xbuf[((size_t)colour * c.nslots + g.exp_slot[e]) * c.nw + w] = Snew;
+#ifdef __CUDA_ARCH__
+                __threadfence();
+#endif
+            }
+        }
+        if (base == 0 && nexport > 0 && (t - t % PMC_WARP) < nexport) {
+            // this warp held export items: once all such warps are through, the block's flag goes up
+#ifdef __CUDA_ARCH__
+            __syncwarp();
+#endif
+            if (t % PMC_WARP == 0) {
+                const unsigned int nwarps = (unsigned int)((nexport + PMC_WARP - 1) / PMC_WARP);
+#ifdef __CUDA_ARCH__
+                const unsigned int arrived = atomicAdd(c.cnt, 1u) + 1u;
+#else
+                const unsigned int arrived = ++*c.cnt;
+#endif
+                if (arrived == events * nwarps) {  // cnt counts over all passes; the load was event 1
+#ifdef __CUDA_ARCH__
+                    __threadfence();
+                    *(volatile unsigned int *)(c.flags + c.b) = events + 1u;
+#else
+                    c.flags[c.b] = events + 1u;
+#endif
+                }
+            }
+        }
+    }
+}
+
+// After the load: the export rows of both colours go to the exchange buffer (event 1).  The caller synchronises the
+// block and raises the flag.
+__device__ __forceinline__ void pb_publish_loaded(const PBGeom &g, const PBCtx &c, int t, int T) {
+    for (int k = t; k < 2 * g.nexp * c.nw; k += T) {
+        const int colour = k / (g.nexp * c.nw), r = k - colour * g.nexp * c.nw;
+        const int e = r / c.nw, w = r - e * c.nw;
+        c.xbuf[((size_t)colour * c.nslots + g.exp_slot[e]) * c.nw + w] = c.s[((size_t)colour * g.nrows + g.exp_row[e]) * c.nw + w];
+    }
+}
+
+// Exact bond sum and second observable (magnetisation / particle number) of the rows of this block, per replica,
+// added into acc[seg][2] (shared memory, zeroed by the caller).  Same definition as reduce_kernel: every word
+// contributes its bonds to the row above and to the site on its left.  Warps take contiguous runs of items so that
+// a warp changes replica at most nseg - 1 times.  `events` as in pb_pass (the remote rows must be current).
+template <int MODEL>
+__device__ __forceinline__ void pb_reduce(const PBGeom &g, const PBCtx &c, unsigned int events, long long *acc, int t, int T) {
+    const int items = g.nrows * c.nw;
+    const int nwarps = T / PMC_WARP, wid = t / PMC_WARP, lane = t % PMC_WARP;
+    const int per_warp = ((items + nwarps - 1) / nwarps + PMC_WARP - 1) / PMC_WARP * PMC_WARP;
+    const int lo = wid * per_warp, hi = lo + per_warp < items ? lo + per_warp : items;
+    int aB = 0, aS = 0, cur = 0;
+    auto flush = [&]() {
+#ifdef __CUDA_ARCH__
+        const int b = __reduce_add_sync(0xFFFFFFFFu, aB), s = __reduce_add_sync(0xFFFFFFFFu, aS);
+        if (lane == 0) {
+            if (b) atomicAdd((unsigned long long *)&acc[2 * cur], (unsigned long long)(long long)b);
+            if (s) atomicAdd((unsigned long long *)&acc[2 * cur + 1], (unsigned long long)(long long)s);
+        }
+#else
+        acc[2 * cur] += aB;
+        acc[2 * cur + 1] += aS;
+#endif
+        aB = aS = 0;
+    };
+    for (int colour = 0; colour < 2; ++colour) {
+        const int oc = colour ^ 1;
+#pragma unroll 1
+        for (int base = lo; base < hi; base += PMC_WARP) {
+            const bool on = base + lane < hi;
+            const int o = on ? base + lane : hi - 1;
+            int lr, w, seg, i, up, dn;
+            pb_locate(g, c, o, false, lr, w, seg, i);
+            pb_neighbours(g, c.lenX, lr, i, up, dn);
+            int dB = 0, dS = 0;
+            if (on) {
+                const uint64_t *row_o = c.s + ((size_t)oc * g.nrows + lr) * c.nw;
+                const uint64_t S = c.s[((size_t)colour * g.nrows + lr) * c.nw + w], C = row_o[w];
+                const uint64_t U = pb_row_word(g, c, oc, up, w, events);
+                // the site at column y-1: same k of the other colour, or k-1
+                const uint64_t Lw = ((i + colour) & 1) ? C : ((C << 1) | (row_o[w == 0 ? c.nw - 1 : w - 1] >> 63));
+                if (MODEL == MODEL_ISING) {
+                    dB = 128 - 2 * (__popcll(S ^ U) + __popcll(S ^ Lw));
+                    dS = 2 * __popcll(S) - 64;
+                } else {
+                    dB = __popcll(S & U) + __popcll(S & Lw);
+                    dS = __popcll(S);
+                }
+            }
+#ifdef __CUDA_ARCH__
+            const int seg0 = __shfl_sync(0xFFFFFFFFu, seg, 0);
+            const bool uniform = __all_sync(0xFFFFFFFFu, seg == seg0);
+#else
+            const int seg0 = seg;
+            const bool uniform = true;
+#endif
+            if (uniform) {
+                if (seg0 != cur) {
+                    flush();
+                    cur = seg0;
+                }
+                aB += dB;
+                aS += dS;
+            } else {  // the 32 items straddle a replica boundary: every lane adds its own
+                flush();
+#ifdef __CUDA_ARCH__
+                if (dB) atomicAdd((unsigned long long *)&acc[2 * seg], (unsigned long long)(long long)dB);
+                if (dS) atomicAdd((unsigned long long *)&acc[2 * seg + 1], (unsigned long long)(long long)dS);
+#endif
+            }
+        }
+    }
+    flush();
+}
+
+// ---- replica exchange ----------------------------------------------------------------------------------------
+// Partial sums of the blocks: part[parity][block][seg][2].  Energy of global replica r from them, evaluated like
+// rx_energy_kernel (no FMA contraction) so that it equals the host expression J*B + (Eads-mu)*N bit for bit.
+__device__ __forceinline__ double pb_energy(const long long *part, int r_local, int B, int nrep, int lenX, double c_bond,
+                                            double c_second) {
+    const long long NR = (long long)nrep * lenX;
+    const int b0 = pb_block_of_row((long long)r_local * lenX, NR, B), b1 = pb_block_of_row((long long)r_local * lenX + lenX - 1, NR, B);
+    long long Bs = 0, Ss = 0;
+    for (int bb = b0; bb <= b1; ++bb) {
+        const int seg = r_local - pb_row0(bb, NR, B) / lenX;
+        const long long *p = part + ((size_t)bb * PB_MAXSEG + seg) * 2;
+#ifdef __CUDA_ARCH__
+        Bs += __ldcg(p);
+        Ss += __ldcg(p + 1);
+#else
+        Bs += p[0];
+        Ss += p[1];
+#endif
+    }
+#ifdef __CUDA_ARCH__
+    double e = __dmul_rn(c_bond, (double)Bs);
+    if (c_second != 0.0) e = __dadd_rn(e, __dmul_rn((double)Ss, c_second));
+#else
+    double e = c_bond * (double)Bs;
+    if (c_second != 0.0) e = e + (double)Ss * c_second;
+#endif
+    return e;
+}
+
+#ifdef __CUDACC__
+
+struct PBatchArgs {
+    long long nsweeps;
+    unsigned long long sweep0;     // the handle's sweep counter at entry
+    int xchg_every;                // exchange after every xchg_every sweeps; 0 = never
+    int xchg_phase;                // sweeps already done since the last exchange
+    int scheme0;                   // XCscheme of the first exchange of this launch (alternates from there)
+    unsigned long long round0;     // the handle's exchange round at entry
+    unsigned int *flags;           // [B] zeroed by the host before the launch
+    unsigned int *bar;             // grid barrier arrivals, zeroed by the host before the launch
+    int *err;
+    uint64_t *xbuf;                // [2][nslots][nw]
+    long long *part;               // [2][B][PB_MAXSEG][2]
+    unsigned long long *out;       // [nrep][2] zeroed by the host: the exact sums at the end of the launch
+    const double *betas;
+    double c_bond, c_second;
+    int32_t *rep_to_T[2], *T_to_rep[2];  // maps double-buffered by exchange parity; [0] holds the maps at entry
+    unsigned long long *tried, *accepted;
+    double *energies;              // [R] energies as of the last exchange (what pymc_rx_get_energies returns)
+    int ntemps;
+};
+
+__device__ __forceinline__ void pb_grid_barrier(unsigned int *counter, unsigned int target, int *err) {
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        atomicAdd(counter, 1u);
+        const long long t0 = clock64();
+        while (*(volatile unsigned int *)counter < target) {
+            if (clock64() - t0 > 4000000000LL || (((clock64() - t0) & 0xFFFFF) == 0 && *(volatile int *)err)) {
+                *err = 1;
+                break;
+            }
+        }
+        __threadfence();
+    }
+    __syncthreads();
+}
+
+// grid = B blocks (<= number of SMs, cooperative launch: all resident), block = multiple of 32 threads with
+// 4 * nw <= threads, dynamic shared memory = 2 * (largest nrows) * nw * 8 bytes.
+template <int MODEL, int LAYOUT, class LatT>
+__global__ void __launch_bounds__(PB_MAX_THREADS, 1) pbatch_kernel(LatT L, PBatchArgs a) {
+    extern __shared__ __align__(16) uint64_t s_rows[];
+    __shared__ uint32_t s_plan[PB_MAXSEG * PLAN_WORDS];
+    __shared__ int s_segoff[PB_MAXSEG], s_segstart[PB_MAXSEG], s_T[PB_MAXSEG];
+    __shared__ long long s_acc[PB_MAXSEG * 2];
+    __shared__ unsigned int s_cnt;
+    __shared__ PBGeom s_geom;
+    const int b = blockIdx.x, B = gridDim.x, t = threadIdx.x, T = blockDim.x;
+    const int lenX = L.lenX, nw = L.nw, nk = L.nk, nrep = L.nrep;
+
+    if (t == 0) {
+        pb_geometry(b, B, nrep, lenX, s_geom);
+        s_cnt = 0;
+    }
+    __syncthreads();
+    const PBGeom &g = s_geom;  // stays in shared memory: block-uniform, read where needed
+    if (t < g.nseg) {
+        s_segstart[t] = t == 0 ? 0 : (g.rep_first + t) * lenX - g.R0;
+        s_segoff[t] = t == 0 ? g.i0 : -((g.rep_first + t) * lenX - g.R0);
+        s_T[t] = L.single_plan ? 0 : a.rep_to_T[0][L.rep_offset + g.rep_first + t];
+    }
+    PBCtx c;
+    c.s = s_rows;
+    c.segoff = s_segoff;
+    c.segstart = s_segstart;
+    c.splan = s_plan;
+    c.xbuf = a.xbuf;
+    c.flags = a.flags;
+    c.cnt = &s_cnt;
+    c.err = a.err;
+    c.lenX = lenX;
+    c.nw = nw;
+    c.nw_shift = (nw & (nw - 1)) == 0 ? 31 - __clz(nw) : -1;
+    c.nslots = pb_nslots(B, nrep);
+    c.b = b;
+    c.rep_offset = (uint32_t)L.rep_offset;
+    c.key = L.key;
+
+    // ---- load my rows (both colours) ---------------------------------------------------------------------
+    for (int colour = 0; colour < 2; ++colour) {
+        if (LAYOUT == PYMC_LAYOUT_BITS) {
+            for (int idx = t; idx < g.nrows * nw; idx += T) {
+                const int lr = idx / nw, w = idx - lr * nw;
+                const int gr = g.R0 + lr, rep = gr / lenX, i = gr - rep * lenX;
+                s_rows[((size_t)colour * g.nrows + lr) * nw + w] = L.bits[((size_t)(rep * 2 + colour) * lenX + i) * nw + w];
+            }
+        } else {
+            uint16_t *s16 = reinterpret_cast<uint16_t *>(s_rows + (size_t)colour * g.nrows * nw);
+            for (int lr = t >> 5; lr < g.nrows; lr += T >> 5) {  // a warp takes one row at a time: 16-byte chunks, 4 per word
+                const int gr = g.R0 + lr, rep = gr / lenX, i = gr - rep * lenX;
+                const uint4 *src = reinterpret_cast<const uint4 *>(L.i8 + ((size_t)(rep * 2 + colour) * lenX + i) * nk);
+                for (int cc = t & 31; cc < nw * 4; cc += 32) s16[lr * nw * 4 + cc] = (uint16_t)pack16<MODEL>(__ldg(src + cc));
+            }
+        }
+    }
+    __syncthreads();
+    auto load_plans = [&]() {  // plan rows of my replicas at their current temperatures
+        for (int k = t; k < g.nseg * PLAN_WORDS; k += T) {
+            const int seg = k / PLAN_WORDS, j = k - seg * PLAN_WORDS;
+            s_plan[k] = L.single_plan ? L.plan0[j] : __ldg(L.plans + (size_t)s_T[seg] * PLAN_WORDS + j);
+        }
+    };
+    load_plans();
+    pb_publish_loaded(g, c, t, T);
+    __threadfence();
+    __syncthreads();
+    if (t == 0) *(volatile unsigned int *)(a.flags + b) = 1u;
+
+    unsigned int events = 1, arrivals = 0;
+    int scheme = a.scheme0, cur = 0;
+    unsigned long long round = a.round0;
+    for (long long sw = 0; sw < a.nsweeps; ++sw) {
+#pragma unroll 1
+        for (int colour = 0; colour < 2; ++colour) {
+            pb_pass<MODEL>(g, c, colour, 2 * (a.sweep0 + sw) + colour, events, t, T);
+            ++events;
+            __syncthreads();
+        }
+        const bool last = sw == a.nsweeps - 1;
+        const bool xch = a.xchg_every > 0 && (a.xchg_phase + sw + 1) % a.xchg_every == 0;
+        if (!last && !xch) continue;
+
+        // ---- exact sums of my rows per replica ------------------------------------------------------------
+        if (t < 2 * g.nseg) s_acc[t] = 0;
+        __syncthreads();
+        pb_reduce<MODEL>(g, c, events, s_acc, t, T);
+        __syncthreads();
+        if (xch) {
+            const int par = (int)(round & 1ull);
+            long long *part = a.part + (size_t)par * B * PB_MAXSEG * 2;
+            if (t < 2 * g.nseg) part[(size_t)b * PB_MAXSEG * 2 + t] = s_acc[t];
+            arrivals += (unsigned int)B;
+            pb_grid_barrier(a.bar, arrivals, a.err);  // every block's sums are in `part`
+            // ---- the pair decisions of Xtrial (py_mc/mc_mpi.py:102-140), identical in every block -------------
+            const int nxt = cur ^ 1, R = a.ntemps;
+            const int32_t *t2r = a.T_to_rep[cur];
+            if (b == 0)  // temperatures without a partner this round keep their replica
+                for (int tt = t; tt < R; tt += T) {
+                    const bool paired = tt >= scheme && (((tt - scheme) & 1) ? true : tt + 1 < R);
+                    if (!paired) {
+                        const int r = t2r[tt];
+                        a.T_to_rep[nxt][tt] = r;
+                        a.rep_to_T[nxt][r] = tt;
+                    }
+                }
+            if (b == 0)
+                for (int r = t; r < nrep; r += T)
+                    a.energies[L.rep_offset + r] = pb_energy(part, r, B, nrep, lenX, a.c_bond, a.c_second);
+            const int g_first = (int)L.rep_offset + g.rep_first;
+            for (int p = t; 2 * p + scheme + 1 < R; p += T) {
+                const int tl = 2 * p + scheme;  // lower temperature index of the pair
+                const int r_lo = t2r[tl], r_hi = t2r[tl + 1];
+                const double e_lo = pb_energy(part, r_lo - (int)L.rep_offset, B, nrep, lenX, a.c_bond, a.c_second);
+                const double e_hi = pb_energy(part, r_hi - (int)L.rep_offset, B, nrep, lenX, a.c_bond, a.c_second);
+                const double delta = __dmul_rn(__dsub_rn(a.betas[tl + 1], a.betas[tl]), __dsub_rn(e_lo, e_hi));
+                bool accept = delta < 0.0;
+                if (!accept) {
+                    const uint4 o = philox4x32_10((uint32_t)tl, 0u, (uint32_t)round, ctr3(DOMAIN_RX, 0, round), L.key);
+                    accept = (double)o.x * (1.0 / 4294967296.0) <= exp(-delta);
+                }
+                const int T_lo = accept ? tl + 1 : tl, T_hi = accept ? tl : tl + 1;  // new temperatures of r_lo, r_hi
+                if (r_lo >= g_first && r_lo < g_first + g.nseg) s_T[r_lo - g_first] = T_lo;
+                if (r_hi >= g_first && r_hi < g_first + g.nseg) s_T[r_hi - g_first] = T_hi;
+                if (b == 0) {
+                    a.rep_to_T[nxt][r_lo] = T_lo;
+                    a.rep_to_T[nxt][r_hi] = T_hi;
+                    a.T_to_rep[nxt][T_lo] = r_lo;
+                    a.T_to_rep[nxt][T_hi] = r_hi;
+                    a.tried[tl] += 1;
+                    if (accept) a.accepted[tl] += 1;
+                }
+            }
+            __syncthreads();
+            load_plans();
+            __syncthreads();
+            cur = nxt;
+            scheme ^= 1;
+            ++round;
+        }
+        if (last && t < 2 * g.nseg && s_acc[t])
+            atomicAdd(a.out + 2 * (size_t)(g.rep_first + t / 2) + (t & 1), (unsigned long long)s_acc[t]);
+    }
+    __syncthreads();
+
+    // ---- store my rows ---------------------------------------------------------------------------------------
+    for (int colour = 0; colour < 2; ++colour) {
+        if (LAYOUT == PYMC_LAYOUT_BITS) {
+            for (int idx = t; idx < g.nrows * nw; idx += T) {
+                const int lr = idx / nw, w = idx - lr * nw;
+                const int gr = g.R0 + lr, rep = gr / lenX, i = gr - rep * lenX;
+                L.bits[((size_t)(rep * 2 + colour) * lenX + i) * nw + w] = s_rows[((size_t)colour * g.nrows + lr) * nw + w];
+            }
+        } else {
+            const uint16_t *s16 = reinterpret_cast<const uint16_t *>(s_rows + (size_t)colour * g.nrows * nw);
+            for (int lr = t >> 5; lr < g.nrows; lr += T >> 5) {
+                const int gr = g.R0 + lr, rep = gr / lenX, i = gr - rep * lenX;
+                uint4 *dst = reinterpret_cast<uint4 *>(L.i8 + ((size_t)(rep * 2 + colour) * lenX + i) * nk);
+                for (int cc = t & 31; cc < nw * 4; cc += 32) dst[cc] = unpack16<MODEL>(s16[lr * nw * 4 + cc]);
+            }
+        }
+    }
+}
+
+#endif  // __CUDACC__
+
+}  // namespace pmc

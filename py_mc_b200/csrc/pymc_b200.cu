@@ -22,6 +22,7 @@
 #include "pmc_pair.cuh"
 #include "pmc_resident.cuh"
 #include "pmc_persist.cuh"
+#include "pmc_pbatch.cuh"
 #include "pmc_discs.cuh"
 
 // largest bit image (bytes) for which PYMC_KERNEL_AUTO takes the resident kernel: several blocks per SM
@@ -30,6 +31,9 @@ static const size_t RESIDENT_AUTO_MAX_IMAGE = 32 * 1024;
 // (0.104 ms per sweep against 0.174 for the fused kernel); two grid barriers per sweep cost a few microseconds, so the
 // bound is kept where a sweep is at least ten times that.
 static const size_t PERSIST_AUTO_MIN_SITES = (size_t)16384 * 8192;
+// smallest batch (sites of all replicas together) for which PYMC_KERNEL_AUTO takes the batch-resident kernel K12
+// on calls of >= 2 sweeps: from 1024 x 1024 on the resident kernels beat the per-sweep ones (profiles/README.md)
+static const size_t PBATCH_AUTO_MIN_SITES = (size_t)1024 * 1024;
 #ifndef PMC_PERSIST_AUTO
 #define PMC_PERSIST_AUTO 1  // 0: only PYMC_KERNEL_PERSISTENT selects the persistent kernel
 #endif
@@ -658,6 +662,15 @@ struct pymc_handle {
     int *persist_err;              // device view of err_host[0]: a block timed out at the barrier
     uint64_t *persist_halo;        // [2][blocks][2][nw]
     bool persist_attr[2];
+    // K12 (pmc_pbatch.cuh): all replicas of the handle resident in the shared memory of all SMs
+    bool pbatch;                   // calls of >= 2 sweeps (and single-GPU exchange cycles) run on the batch kernel
+    int pb_blocks, pb_threads;
+    size_t pb_smem;
+    unsigned int *pb_sync;         // [pb_blocks] export-event flags + [1] grid-barrier counter (zeroed per launch)
+    uint64_t *pb_xbuf;             // [2][2*blocks + 2*nrep][nw] rows exchanged between blocks
+    long long *pb_part;            // [2][blocks][PB_MAXSEG][2] partial sums of an exchange
+    int32_t *pb_maps;              // [2 maps][2 parities][ntemps] replica <-> temperature maps of the kernel
+    bool pb_attr[2];
     // Time-outs of the in-kernel barriers are raised by the kernels in two ints of mapped pinned host memory, so
     // that every entry point which synchronises and returns data can look at them for free (check_async_errors).
     volatile int *err_host;        // [0] persistent kernel, [1] slab neighbour barrier
@@ -773,6 +786,10 @@ int pymc_destroy(pymc_handle *h) {
         cudaFree(h->reduced);
         cudaFree(h->persist_counter);
         cudaFree(h->persist_halo);
+        cudaFree(h->pb_sync);
+        cudaFree(h->pb_xbuf);
+        cudaFree(h->pb_part);
+        cudaFree(h->pb_maps);
         if (h->err_host) cudaFreeHost((void *)h->err_host);
         cudaFree(h->staging);
         cudaFree(h->qbuf);
@@ -837,7 +854,7 @@ int pymc_create(const pymc_params *p, pymc_handle **out) {
     h->nw = (h->nk + 63) / 64;
     h->nclass = p->model == PYMC_MODEL_ISING ? PYMC_NCLASS_ISING : PYMC_NCLASS_LATGAS;
     REQUIRE((uint64_t)p->lenX * h->nw < (1ull << 31), PYMC_ERR_UNSUPPORTED, "pymc_create: lattice too large");
-    REQUIRE(p->kernel >= PYMC_KERNEL_AUTO && p->kernel <= PYMC_KERNEL_PERSISTENT, PYMC_ERR_BADARG, "pymc_create: kernel %d",
+    REQUIRE(p->kernel >= PYMC_KERNEL_AUTO && p->kernel <= PYMC_KERNEL_PBATCH, PYMC_ERR_BADARG, "pymc_create: kernel %d",
             p->kernel);
 
     DeviceGuard guard(p->device);
@@ -894,6 +911,49 @@ int pymc_create(const pymc_params *p, pymc_handle **out) {
             h->persist_smem = slab;
             int pthreads = (int)(((size_t)max_rows * h->nw + 31) / 32 * 32);
             h->persist_threads = pthreads < 128 ? 128 : (pthreads > PERSIST_MAX_THREADS ? PERSIST_MAX_THREADS : pthreads);
+        }
+        // K12 (pmc_pbatch.cuh): the rows of ALL replicas cut into one piece per SM
+        {
+            int coop = 0;
+            cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, p->device);
+            const long long NR = (long long)p->nreplicas * p->lenX;
+            const int blocks = NR < sms ? (int)NR : sms;
+            bool ok = coop && p->lenY % 128 == 0 && NR < (1ll << 31) / (h->nw > 0 ? h->nw : 1);
+            int max_rows = 0, max_x = 0;
+            for (int b = 0; ok && b < blocks; ++b) {
+                PBGeom g;
+                pb_geometry(b, blocks, p->nreplicas, p->lenX, g);
+                ok = g.nseg <= PB_MAXSEG;
+                if (g.nrows > max_rows) max_rows = g.nrows;
+                if (g.nxrow > max_x) max_x = g.nxrow;
+            }
+            const size_t rows_bytes = (size_t)16 * max_rows * h->nw;
+            ok = ok && rows_bytes + 2048 <= (size_t)smem;  // ~1.2 KiB of static shared memory ride along
+            const long long items = (long long)max_rows * h->nw;
+            const long long npass = (items + PB_MAX_THREADS - 1) / PB_MAX_THREADS;
+            long long threads = npass ? ((items + npass - 1) / npass + 31) / 32 * 32 : 32;
+            const long long need = ((long long)max_x * h->nw + 31) / 32 * 32;  // all export items sit in the first round
+            if (threads < need) threads = need;
+            if (threads < 64) threads = 64;
+            ok = ok && threads <= PB_MAX_THREADS;
+            if (p->kernel == PYMC_KERNEL_PBATCH && !ok) {
+                delete h;
+                return fail(PYMC_ERR_UNSUPPORTED,
+                            "pymc_create: the batch-resident kernel needs lenY %% 128 == 0, cooperative launches, at most %d "
+                            "replicas per block and row pieces (%zu bytes) within the %d bytes of shared memory of a block",
+                            PB_MAXSEG, rows_bytes, smem);
+            }
+            const char *off = getenv("PYMC_NO_PERSISTENT");
+            const bool allowed = !(off && off[0] == '1');
+            // AUTO: one lattice of >= 2^20 sites, or a batch that the one-block-per-replica kernel does not already
+            // serve with several blocks per SM (small images, >= one replica per SM)
+            const bool auto_ok = p->kernel == PYMC_KERNEL_AUTO && allowed && ok && !h->resident &&
+                                 (size_t)p->nreplicas * p->lenX * p->lenY >= PBATCH_AUTO_MIN_SITES;
+            h->pbatch = p->kernel == PYMC_KERNEL_PBATCH || auto_ok;
+            if (h->pbatch && p->kernel == PYMC_KERNEL_AUTO) h->persist = h->resident_big = false;
+            h->pb_blocks = blocks;
+            h->pb_threads = (int)threads;
+            h->pb_smem = rows_bytes;
         }
         int threads = (int)(((size_t)p->lenX * h->nw / 2 + 31) / 32 * 32);
         h->resident_threads = threads < 128 ? 128 : (threads > RESIDENT_MAX_THREADS ? RESIDENT_MAX_THREADS : threads);
@@ -1186,6 +1246,90 @@ static int launch_persistent(pymc_handle *h, int64_t nsweeps) {
     return PYMC_OK;
 }
 
+// K12: nsweeps sweeps of every replica in one cooperative launch per <= 4096 sweeps; with xchg_every > 0 (single-GPU
+// replica exchange) an exchange after every xchg_every-th sweep, decided inside the kernel.  Returns
+// PYMC_ERR_UNSUPPORTED (and switches the handle back to the other kernels) if the device refuses the launch.
+static int launch_pbatch(pymc_handle *h, int64_t nsweeps, int xchg_every, int *scheme_io) {
+    REQUIRE(h->tables_set, PYMC_ERR_STATE, "pymc_sweep: call pymc_set_accept_tables first");
+    if (nsweeps <= 0) return PYMC_OK;
+    const int m = h->p.model == PYMC_MODEL_ISING ? 0 : 1;
+    const void *fn;
+    if (h->p.layout == PYMC_LAYOUT_INT8)
+        fn = m ? (const void *)pbatch_kernel<MODEL_LATGAS, PYMC_LAYOUT_INT8, Lat> : (const void *)pbatch_kernel<MODEL_ISING, PYMC_LAYOUT_INT8, Lat>;
+    else
+        fn = m ? (const void *)pbatch_kernel<MODEL_LATGAS, PYMC_LAYOUT_BITS, Lat> : (const void *)pbatch_kernel<MODEL_ISING, PYMC_LAYOUT_BITS, Lat>;
+    if (!h->pb_attr[m]) {
+        if (h->pb_smem > 48 * 1024)
+            CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->pb_smem));
+        h->pb_attr[m] = true;
+    }
+    const int B = h->pb_blocks, R = h->p.ntemps;
+    if (!h->pb_sync) {
+        CUDA_TRY(cudaMalloc(&h->pb_sync, (size_t)(B + 1) * sizeof(unsigned int)));
+        CUDA_TRY(cudaMalloc(&h->pb_xbuf, (size_t)2 * pb_nslots(B, h->p.nreplicas) * h->nw * 8));
+        CUDA_TRY(cudaMalloc(&h->pb_part, (size_t)2 * B * PB_MAXSEG * 2 * sizeof(long long)));
+    }
+    if (xchg_every > 0 && !h->pb_maps) CUDA_TRY(cudaMalloc(&h->pb_maps, (size_t)4 * R * sizeof(int32_t)));
+    Lat L = make_lat(h);
+    int scheme = scheme_io ? *scheme_io : 0;
+    while (nsweeps > 0) {
+        int64_t chunk = nsweeps > 4096 ? 4096 : nsweeps;
+        if (xchg_every > 0 && chunk < nsweeps) chunk -= chunk % xchg_every;  // launches end on exchange boundaries
+        if (chunk <= 0) chunk = nsweeps > 4096 ? xchg_every : nsweeps;
+        PBatchArgs a;
+        memset(&a, 0, sizeof(a));
+        a.nsweeps = chunk;
+        a.sweep0 = h->sweep_counter;
+        a.xchg_every = xchg_every;
+        a.xchg_phase = 0;
+        a.scheme0 = scheme;
+        a.round0 = h->rx_round;
+        a.flags = h->pb_sync;
+        a.bar = h->pb_sync + B;
+        a.err = h->persist_err;
+        a.xbuf = h->pb_xbuf;
+        a.part = h->pb_part;
+        a.out = h->reduced;
+        a.ntemps = R;
+        a.rep_to_T[0] = h->rep_to_T;
+        const int64_t nex = xchg_every > 0 ? chunk / xchg_every : 0;
+        if (xchg_every > 0) {
+            // parity 0 = the handle's own maps (current at entry), parity 1 = the spare pair
+            a.rep_to_T[1] = h->pb_maps;
+            a.T_to_rep[0] = h->T_to_rep;
+            a.T_to_rep[1] = h->pb_maps + R;
+            a.betas = h->betas;
+            a.c_bond = h->c_bond;
+            a.c_second = h->c_second;
+            a.tried = h->rx_tried;
+            a.accepted = h->rx_accepted;
+            a.energies = h->energies;
+        }
+        CUDA_TRY(cudaMemsetAsync(h->pb_sync, 0, (size_t)(B + 1) * sizeof(unsigned int), h->stream));
+        CUDA_TRY(cudaMemsetAsync(h->reduced, 0, (size_t)h->p.nreplicas * 16, h->stream));
+        void *args[] = {(void *)&L, (void *)&a};
+        cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3(B), dim3(h->pb_threads), args, h->pb_smem, h->stream);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            h->pbatch = false;  // nothing has run in this chunk: the caller falls back
+            return fail(PYMC_ERR_UNSUPPORTED, "cooperative launch refused: %s", cudaGetErrorString(e));
+        }
+        // the exact sums at the end of the launch are the new tracked values
+        CUDA_TRY(cudaMemcpyAsync(h->tracked, h->reduced, (size_t)h->p.nreplicas * 16, cudaMemcpyDeviceToDevice, h->stream));
+        if (nex & 1) {  // an odd number of exchanges leaves the current maps in the spare pair
+            CUDA_TRY(cudaMemcpyAsync(h->rep_to_T, h->pb_maps, (size_t)R * 4, cudaMemcpyDeviceToDevice, h->stream));
+            CUDA_TRY(cudaMemcpyAsync(h->T_to_rep, h->pb_maps + R, (size_t)R * 4, cudaMemcpyDeviceToDevice, h->stream));
+        }
+        h->dirty = false;
+        h->sweep_counter += chunk;
+        h->rx_round += (uint64_t)nex;
+        if (nex & 1) scheme ^= 1;
+        nsweeps -= chunk;
+    }
+    if (scheme_io) *scheme_io = scheme;
+    return PYMC_OK;
+}
+
 // K10: nsteps steps (flip sweep and / or pair pass each) of every replica in one launch per <= 4096 steps.
 static int launch_resident(pymc_handle *h, int64_t nsteps, bool flip, uint32_t mask_even, uint32_t mask_odd) {
     REQUIRE(!flip || h->tables_set, PYMC_ERR_STATE, "sweep: call pymc_set_accept_tables first");
@@ -1250,7 +1394,10 @@ int pymc_sweep_kernel_info(pymc_handle *h, int *launches_per_sweep, const char *
     REQUIRE(h, PYMC_ERR_BADARG, "pymc_sweep_kernel_info: null handle");
     const char *name;
     int n = 2;
-    if (h->persist) {
+    if (h->pbatch) {
+        name = "pbatch_kernel";  // one cooperative launch per call of >= 2 sweeps (and per exchange cycle on one GPU)
+        n = 1;
+    } else if (h->persist) {
         name = "persistent_kernel";  // one cooperative launch per call of >= 2 sweeps
         n = 1;
     } else if (h->resident || h->resident_big) {
@@ -1277,6 +1424,10 @@ int pymc_sweep(pymc_handle *h, int64_t nsweeps) {
     REQUIRE(nsweeps >= 0, PYMC_ERR_BADARG, "pymc_sweep: nsweeps %lld", (long long)nsweeps);
     REQUIRE(h->tables_set, PYMC_ERR_STATE, "pymc_sweep: call pymc_set_accept_tables first");
     REQUIRE(!h->slab || h->peer_up[0], PYMC_ERR_STATE, "pymc_sweep: connect the slab to its neighbours first");
+    if (h->pbatch && nsweeps >= 2 && !h->slab) {
+        const int rc = launch_pbatch(h, nsweeps, 0, nullptr);
+        if (rc != PYMC_ERR_UNSUPPORTED) return rc;
+    }
     if (h->resident || (h->resident_big && nsweeps >= 2)) return launch_resident(h, nsweeps, true, 0, 0);
     if (h->persist && nsweeps >= 2) {
         // Several replicas: one launch each, in turn.  If the first launch is refused nothing has run and the
@@ -1553,6 +1704,11 @@ int pymc_rx_cycle(pymc_handle *h, int64_t ncycles, int64_t sweeps_per_exchange, 
     REQUIRE(ncycles >= 0 && sweeps_per_exchange >= 1 && (first_scheme == 0 || first_scheme == 1), PYMC_ERR_BADARG,
             "pymc_rx_cycle: bad arguments");
     int scheme = first_scheme;
+    if (h->pbatch && ncycles > 0 && sweeps_per_exchange <= 4096) {
+        // everything in one kernel: sweeps, exact energies, grid barrier, pair decisions (pmc_pbatch.cuh)
+        const int rc = launch_pbatch(h, ncycles * sweeps_per_exchange, (int)sweeps_per_exchange, &scheme);
+        if (rc != PYMC_ERR_UNSUPPORTED) return rc;
+    }
     for (int64_t c = 0; c < ncycles; ++c) {
         int rc = pymc_sweep(h, sweeps_per_exchange);
         if (rc) return rc;
@@ -1963,7 +2119,7 @@ int pymc_create_slab(const pymc_params *p, int slab_index, int nslabs, pymc_hand
     q.lenX = Xl + 4;  // two halo rows above and below the owned rows
     pymc_handle *h = nullptr;
     int rc = pymc_create(&q, &h);
-    if (rc == PYMC_OK) h->persist = h->resident = h->resident_big = false;  // slabs run the fused kernel only
+    if (rc == PYMC_OK) h->persist = h->pbatch = h->resident = h->resident_big = false;  // slabs run the fused kernel only
     if (rc) return rc;
     h->slab = true;
     h->own_lo = 2;

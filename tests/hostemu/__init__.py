@@ -13,7 +13,7 @@ SRC = os.path.join(HERE, "hostemu.cpp")
 OUTDIR = os.path.join(HERE, "_build")
 LIB = os.path.join(OUTDIR, "libhostemu.so")
 DEPS = [SRC, os.path.join(HERE, "cuda_host_shim.h")] + [os.path.join(CSRC, f) for f in
-                                                         ("pmc_stream.cuh", "pmc_core.cuh", "pmc_pair.cuh", "pmc_persist.cuh")]
+                                                         ("pmc_stream.cuh", "pmc_core.cuh", "pmc_pair.cuh", "pmc_persist.cuh", "pmc_pbatch.cuh")]
 
 
 def build(force=False):
@@ -39,6 +39,8 @@ class HostCore:
                                                 C.c_uint64, LL, LL]
         self.lib.hostemu_persist_sweeps.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_uint32,
                                                     C.c_uint64, C.c_int, C.c_int, C.c_int, LL, LL]
+        self.lib.hostemu_pbatch_sweeps.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_uint64,
+                                                   C.c_uint32, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_void_p]
         self.lib.hostemu_pair_sweep.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_uint32,
                                                 C.c_uint64, C.c_uint32, LL]
 
@@ -51,6 +53,19 @@ class HostCore:
                                              replica, sweep0, nsweeps, nblocks, nthreads, C.byref(dB), C.byref(dS))
         assert rc == 0, rc
         return dB.value, dS.value
+
+    def pbatch_sweeps(self, model, imgs, thr, seed, rep_offset, sweep0, nsweeps, nblocks, nthreads):
+        """nsweeps sweeps of all replicas imgs[nrep, lenX, lenY] (in place) through the batch-resident kernel's logic with
+        nblocks emulated blocks; thr[nrep, nclass] gives every replica its own thresholds.  Returns sums[nrep, 2]
+        (bond sum, second observable) as the kernel's reduction computes them."""
+        assert imgs.dtype == np.int8 and imgs.flags.c_contiguous and imgs.ndim == 3
+        t = np.ascontiguousarray(thr, dtype=np.uint32)
+        assert t.shape == (imgs.shape[0], 5 if model == self.MODEL_ISING else 10)
+        sums = np.zeros((imgs.shape[0], 2), dtype=np.int64)
+        rc = self.lib.hostemu_pbatch_sweeps(model, imgs.ctypes.data, imgs.shape[0], imgs.shape[1], imgs.shape[2], t.ctypes.data,
+                                            seed, rep_offset, sweep0, nsweeps, nblocks, nthreads, sums.ctypes.data)
+        assert rc == 0, rc
+        return sums
 
     def flip_sweep(self, model, img, thr, seed, replica, sweep):
         """One checkerboard sweep of the int8 image, in place; returns (dB, dS)."""

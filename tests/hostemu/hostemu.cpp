@@ -7,8 +7,10 @@
 // comparison, the per-lane tail and the tracked-observable deltas.
 #include "cuda_host_shim.h"
 
+#define PMC_WARP 1  // a "warp" of one thread (see cuda_host_shim.h)
 #include "../../py_mc_b200/csrc/pmc_pair.cuh"
 #include "../../py_mc_b200/csrc/pmc_persist.cuh"
+#include "../../py_mc_b200/csrc/pmc_pbatch.cuh"
 
 #include <vector>
 
@@ -213,4 +215,117 @@ extern "C" int hostemu_persist_sweeps(int model, int8_t *img, int lenX, int lenY
     else
         return -1;
     return 0;
+}
+
+namespace {
+
+// The batch-resident kernel's per-thread pieces (pmc_pbatch.cuh) on the host: B emulated blocks in lock step, thread
+// after thread.  Checks the geometry (which rows a block takes from / gives to which other block), the export-first
+// item order, the flag bookkeeping (a wait that the lock-step order cannot satisfy is reported as an error), the
+// per-replica plans and the exact sums of pb_reduce.  imgs: [nrep][lenX][lenY]; thr: [nrep][nclass] (each replica at
+// its own temperature); sums: [nrep][2] out.
+template <int MODEL>
+int pbatch_sweeps(int8_t *imgs, int nrep, int lenX, int lenY, const uint32_t *thr, int nclass, uint64_t seed, uint32_t rep_offset,
+                  uint64_t sweep0, int nsweeps, int B, int T, long long *sums) {
+    const int nw = lenY / 128;
+    const size_t plane = (size_t)lenX * lenY;
+    std::vector<PBGeom> geo(B);
+    std::vector<std::vector<uint64_t>> rows(B);
+    std::vector<std::vector<int>> segoff(B), segstart(B);
+    std::vector<std::vector<uint32_t>> splan(B);
+    const int nslots = pb_nslots(B, nrep);
+    std::vector<uint64_t> xbuf((size_t)2 * nslots * nw, 0xDEADBEEFDEADBEEFull);
+    std::vector<unsigned int> flags(B, 0), cnt(B, 0);
+    int err = 0;
+    std::vector<PBCtx> ctx(B);
+    for (int b = 0; b < B; ++b) {
+        PBGeom &g = geo[b];
+        pb_geometry(b, B, nrep, lenX, g);
+        if (g.nseg > PB_MAXSEG || g.nxrow * nw > T) return -2;
+        rows[b].assign((size_t)2 * g.nrows * nw, 0);
+        segoff[b].resize(g.nseg);
+        segstart[b].resize(g.nseg);
+        splan[b].resize((size_t)g.nseg * PLAN_WORDS);
+        for (int k = 0; k < g.nseg; ++k) {
+            segstart[b][k] = k == 0 ? 0 : (g.rep_first + k) * lenX - g.R0;
+            segoff[b][k] = k == 0 ? g.i0 : -((g.rep_first + k) * lenX - g.R0);
+            Plan<MODEL>::build_row(thr + (size_t)(g.rep_first + k) * nclass, splan[b].data() + (size_t)k * PLAN_WORDS);
+        }
+        for (int colour = 0; colour < 2; ++colour)
+            for (int lr = 0; lr < g.nrows; ++lr) {
+                const int gr = g.R0 + lr, rep = gr / lenX, i = gr - rep * lenX;
+                Image im = {imgs + (size_t)rep * plane, lenX, lenY};
+                for (int w = 0; w < nw; ++w) rows[b][((size_t)colour * g.nrows + lr) * nw + w] = gather(im, colour, i, w, 0, 0);
+            }
+        PBCtx &c = ctx[b];
+        c.s = rows[b].data();
+        c.segoff = segoff[b].data();
+        c.segstart = segstart[b].data();
+        c.splan = splan[b].data();
+        c.xbuf = xbuf.data();
+        c.flags = flags.data();
+        c.cnt = &cnt[b];
+        c.err = &err;
+        c.lenX = lenX;
+        c.nw = nw;
+        c.nw_shift = -1;
+        for (int k = 0; k < 20; ++k)
+            if ((1 << k) == nw) c.nw_shift = k;
+        c.nslots = nslots;
+        c.b = b;
+        c.rep_offset = rep_offset;
+        c.key = make_key(seed);
+    }
+    for (int b = 0; b < B; ++b) {
+        for (int t = 0; t < T; ++t) pb_publish_loaded(geo[b], ctx[b], t, T);
+        flags[b] = 1;
+    }
+    unsigned int events = 1;
+    for (int sw = 0; sw < nsweeps; ++sw)
+        for (int colour = 0; colour < 2; ++colour) {
+            for (int b = 0; b < B; ++b)
+                for (int t = 0; t < T; ++t) pb_pass<MODEL>(geo[b], ctx[b], colour, 2 * (sweep0 + sw) + colour, events, t, T);
+            ++events;
+            for (int b = 0; b < B; ++b)  // every block with export rows must have raised its flag by now
+                if (geo[b].nexp > 0 && flags[b] != events) return -3;
+        }
+    for (int r = 0; r < 2 * nrep; ++r) sums[r] = 0;
+    for (int b = 0; b < B; ++b) {
+        long long acc[2 * PB_MAXSEG] = {0};
+        for (int t = 0; t < T; ++t) pb_reduce<MODEL>(geo[b], ctx[b], events, acc, t, T);
+        for (int k = 0; k < geo[b].nseg; ++k) {
+            sums[2 * (geo[b].rep_first + k)] += acc[2 * k];
+            sums[2 * (geo[b].rep_first + k) + 1] += acc[2 * k + 1];
+        }
+    }
+    if (err) return -4;
+    for (int b = 0; b < B; ++b) {  // store
+        const PBGeom &g = geo[b];
+        for (int colour = 0; colour < 2; ++colour)
+            for (int lr = 0; lr < g.nrows; ++lr) {
+                const int gr = g.R0 + lr, rep = gr / lenX, i = gr - rep * lenX, q = (i + colour) & 1;
+                Image im = {imgs + (size_t)rep * plane, lenX, lenY};
+                for (int w = 0; w < nw; ++w) {
+                    const uint64_t v = rows[b][((size_t)colour * g.nrows + lr) * nw + w];
+                    for (int l = 0; l < 64; ++l) {
+                        const int bit = (int)((v >> l) & 1ull);
+                        *im.site(i, 2 * (64 * w + l) + q) = MODEL == MODEL_ISING ? (int8_t)(2 * bit - 1) : (int8_t)bit;
+                    }
+                }
+            }
+    }
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int hostemu_pbatch_sweeps(int model, int8_t *imgs, int nrep, int lenX, int lenY, const uint32_t *thr, uint64_t seed,
+                                     uint32_t rep_offset, uint64_t sweep0, int nsweeps, int nblocks, int nthreads,
+                                     long long *sums) {
+    if (lenY % 128 || (lenX & 1) || nblocks < 1 || (long long)nblocks > (long long)nrep * lenX || nthreads < 1) return -1;
+    if (model == MODEL_ISING)
+        return pbatch_sweeps<MODEL_ISING>(imgs, nrep, lenX, lenY, thr, 5, seed, rep_offset, sweep0, nsweeps, nblocks, nthreads, sums);
+    if (model == MODEL_LATGAS)
+        return pbatch_sweeps<MODEL_LATGAS>(imgs, nrep, lenX, lenY, thr, 10, seed, rep_offset, sweep0, nsweeps, nblocks, nthreads, sums);
+    return -1;
 }

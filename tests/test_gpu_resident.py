@@ -163,15 +163,19 @@ def test_resident_is_refused_where_it_cannot_run():
         _cabi.Lattices(_cabi.MODEL_ISING, 2048, 2048, kernel=_cabi.KERNEL_RESIDENT)   # 512 KiB of bits
 
 
-def test_auto_uses_it_for_multi_sweep_calls_on_large_int8_batches():
+@pytest.mark.parametrize("which", ["pbatch_kernel", "resident_kernel"])
+def test_auto_on_large_int8_batches(which, monkeypatch):
     """256 replicas of 1024 x 1024 int8 (BASELINE config 3 on one GPU): calls of one sweep take the fused kernel,
-    longer calls the resident one; the trajectory is that of the two-pass kernel either way."""
+    longer calls a shared-memory-resident one -- the batch-resident kernel K12, or, with PYMC_NO_PERSISTENT=1 (no
+    cooperative launches wanted), one block per replica; the trajectory is that of the two-pass kernel either way."""
     from py_mc_b200 import _cabi
     from py_mc_b200.ising2D import ising2D
     seed, L, R, probe = 3, 1024, 256, 200
     thr = ising2D(-1.0)._pmc_thresholds(2.269)
+    if which == "resident_kernel":
+        monkeypatch.setenv("PYMC_NO_PERSISTENT", "1")
     big = _cabi.Lattices(_cabi.MODEL_ISING, L, L, nreplicas=R, seed=seed)
-    assert big.sweep_kernel_info()[1] == "resident_kernel"
+    assert big.sweep_kernel_info()[1] == which
     one = _cabi.Lattices(_cabi.MODEL_ISING, L, L, nreplicas=1, seed=seed, replica_offset=probe, nreplicas_global=R,
                          kernel=_cabi.KERNEL_TWO_PASS)
     for lat in (big, one):

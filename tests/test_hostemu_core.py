@@ -104,3 +104,40 @@ def test_persistent_kernel_slab_logic_matches_specification(core, shape, nblocks
     for sw in range(3):
         o_latgas.sweep(ref, thr, seed, replica, sw)
     assert np.array_equal(cfg, ref)
+
+
+@pytest.mark.parametrize("nrep,shape,nblocks,nthreads", [
+    (1, (8, 128), 1, 32),        # one block holds everything: no remote rows at all
+    (1, (8, 128), 8, 32),        # one row per block: the row above and the row below are both remote
+    (1, (22, 384), 7, 32),       # uneven pieces, nw = 3 (not a power of two)
+    (3, (10, 256), 4, 64),       # replica boundaries inside blocks: rows 0 / lenX-1 of a replica in another block
+    (5, (6, 128), 7, 32),        # a block with pieces of three replicas
+    (4, (8, 128), 4, 32),        # blocks == replicas: every lattice wraps inside its own block
+    (2, (16, 128), 5, 96),       # more threads than items in a pass
+    (6, (4, 256), 24, 32),       # exactly one row per block
+])
+def test_batch_resident_kernel_logic_matches_specification(core, nrep, shape, nblocks, nthreads):
+    """pmc_pbatch.cuh block after block on the host: the rows of ALL replicas cut into nblocks pieces regardless of
+    the replica boundaries, export rows first, rows of other blocks through the exchange buffer, one plan per
+    replica (every replica at its own temperature), exact sums from the kernel's own reduction.  Ising against the
+    numpy specification, the lattice gas too."""
+    seed, offset, J = 77, 3, -1.0
+    kTs = np.linspace(1.5, 3.5, nrep)
+    ref = np.stack([o_ising.init_config(seed, offset + r, *shape) for r in range(nrep)])
+    cfg = ref.copy()
+    thr = np.stack([ising_table(J, kT) for kT in kTs])
+    sums = core.pbatch_sweeps(core.MODEL_ISING, cfg, thr, seed, offset, 2, 3, nblocks, nthreads)
+    for r in range(nrep):
+        for sw in range(2, 5):
+            o_ising.sweep(ref[r], J, kTs[r], seed, offset + r, sw)
+        assert np.array_equal(cfg[r], ref[r]), r
+        assert int(sums[r, 0]) == o_ising.bond_sum(ref[r]) and int(sums[r, 1]) == int(ref[r].astype(np.int64).sum())
+    ref = np.stack([o_latgas.init_config(seed, offset + r, *shape) for r in range(nrep)])
+    cfg = ref.copy()
+    thr = np.stack([o_latgas.threshold_table(-0.7, -0.2, 0.1, kT) for kT in kTs])
+    sums = core.pbatch_sweeps(core.MODEL_LATGAS, cfg, thr, seed, offset, 0, 2, nblocks, nthreads)
+    for r in range(nrep):
+        for sw in range(2):
+            o_latgas.sweep(ref[r], thr[r], seed, offset + r, sw)
+        assert np.array_equal(cfg[r], ref[r]), r
+        assert int(sums[r, 0]) == o_latgas.bond_sum(ref[r]) and int(sums[r, 1]) == int(ref[r].sum())

@@ -42,14 +42,15 @@ def test_ising_matches_two_pass_kernel(shape, layout):
     check_pair(run_pair(_cabi.MODEL_ISING, shape, layout, ising2D(-1.0)._pmc_thresholds(2.269185314213022)))
 
 
-def test_headline_lattice_matches_the_fused_kernel_and_is_the_automatic_choice():
-    """16384 x 16384 int8: PYMC_KERNEL_AUTO takes the persistent kernel for calls of two sweeps or more; the
-    trajectory and the tracked sums equal those of the fused kernel (forced here through one-sweep calls)."""
+def test_headline_lattice_matches_the_fused_kernel():
+    """16384 x 16384 int8: the persistent kernel for calls of two sweeps or more, the fused kernel for one-sweep
+    calls on the same buffers; trajectory and tracked sums equal those of the two-pass kernel.  (PYMC_KERNEL_AUTO
+    takes the batch-resident kernel K12 here: tests/test_zx_gpu_pbatch.py.)"""
     from py_mc_b200 import _cabi
     from py_mc_b200.ising2D import ising2D
     thr = ising2D(-1.0)._pmc_thresholds(2.269185314213022)
     L = 16384
-    a = _cabi.Lattices(_cabi.MODEL_ISING, L, L, seed=20260611)
+    a = _cabi.Lattices(_cabi.MODEL_ISING, L, L, seed=20260611, kernel=_cabi.KERNEL_PERSISTENT)
     b = _cabi.Lattices(_cabi.MODEL_ISING, L, L, seed=20260611, kernel=_cabi.KERNEL_TWO_PASS)
     assert a.sweep_kernel_info()[1] == "persistent_kernel" and b.sweep_kernel_info()[1] == "sweep_tiled_i8_kernel"
     for lat in (a, b):
@@ -90,7 +91,7 @@ def test_4096_against_the_fused_kernel():
     from py_mc_b200.ising2D import ising2D
     thr = ising2D(-1.0)._pmc_thresholds(2.269185314213022)
     got = []
-    for kernel in (_cabi.KERNEL_PERSISTENT, _cabi.KERNEL_AUTO):
+    for kernel in (_cabi.KERNEL_PERSISTENT, _cabi.KERNEL_TWO_PASS):
         lat = _cabi.Lattices(_cabi.MODEL_ISING, 4096, 4096, seed=21, kernel=kernel)
         lat.init_random()
         lat.set_accept_tables(thr[None, :])
@@ -128,15 +129,17 @@ def test_headline_lattice_bit_packed_matches_the_row_kernel():
 
 
 @pytest.mark.parametrize("layout", [0, 1])
-def test_lattice_gas_at_the_automatic_threshold(layout):
-    """MODEL_LATGAS on a single lattice of 2^27 sites: PYMC_KERNEL_AUTO takes the persistent kernel for calls of two
-    sweeps or more; same trajectory and tracked sums as the per-colour kernels."""
+@pytest.mark.parametrize("which", ["persistent_kernel", "pbatch_kernel"])
+def test_lattice_gas_on_a_large_lattice(layout, which):
+    """MODEL_LATGAS on a single lattice of 2^27 sites on both shared-memory-resident kernels (PYMC_KERNEL_AUTO takes
+    the batch-resident one for calls of two sweeps or more); same trajectory and tracked sums as the per-colour
+    kernels."""
     from py_mc_b200 import _cabi
     from py_mc_b200.latgas import latticegas
     thr = latticegas(Eads=-0.3, J=-1.0, mu=0.2)._pmc_thresholds(0.9)
     shape = (8192, 16384)
     got = []
-    for kernel in (_cabi.KERNEL_AUTO, _cabi.KERNEL_TWO_PASS):
+    for kernel in (_cabi.KERNEL_PERSISTENT if which == "persistent_kernel" else _cabi.KERNEL_AUTO, _cabi.KERNEL_TWO_PASS):
         lat = _cabi.Lattices(_cabi.MODEL_LATGAS, shape[0], shape[1], seed=31, layout=layout, kernel=kernel)
         lat.init_random()
         lat.set_accept_tables(thr[None, :])
@@ -145,7 +148,7 @@ def test_lattice_gas_at_the_automatic_threshold(layout):
         lat.synchronize()
         got.append((lat.download(0), lat.tracked(), lat.reduce_observables(), lat.sweep_kernel_info()[1]))
         lat.close()
-    assert got[0][3] == "persistent_kernel" and got[1][3] != "persistent_kernel"
+    assert got[0][3] == which and got[1][3] not in ("persistent_kernel", "pbatch_kernel")
     assert np.array_equal(got[0][0], got[1][0])
     for k in (0, 1):
         assert int(got[0][1][k][0]) == int(got[1][1][k][0]) == int(got[0][2][k][0])
