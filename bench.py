@@ -1,18 +1,25 @@
 #!/usr/bin/env python
-"""bench.py -- spin-flip attempts/s of the Metropolis sweep hot path.
+"""bench.py -- spin-flip attempts/s of the Metropolis sweep / replica-exchange hot path.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--layout int8|bits]
 
-One "step" = one full checkerboard sweep of the workload (two kernel launches, one per colour).
-N = 1: BASELINE.json configs[1], a single 16384 x 16384 Ising lattice (2^28 sites) at kT = T_c.
-N > 1: the replica-exchange workload -- 256 replicas of 1024^2 per GPU (again 2^28 sites per GPU, weak
-scaling), one temperature ladder over all GPUs, energies all-gathered with NCCL per exchange.
-``--workload`` selects others: ``slab`` (one 16384^2 lattice split by rows, strong scaling), ``ising16k``,
-``latgas``, ``discs``.
-Prints ONE JSON line on rank 0 (contract in the task statement / DESIGN.md section "Measurement").
+One "step" = one full checkerboard sweep of every lattice of the workload (plus the exchange when one is due).
+
+N = 1   BASELINE.json configs[1]: one 16384 x 16384 Ising lattice (2^28 sites) at kT = T_c, int8.  The line also
+        carries the same workload bit-packed, one-sweep-per-launch, and an "rx" block: BASELINE configs[2] (256
+        replicas of 1024^2 with replica exchange) on this one GPU.
+N > 1   BASELINE.json configs[2] as written: 256 replicas of 1024^2 IN TOTAL, block-partitioned over the N GPUs
+        (strong scaling), one temperature ladder, energies all-gathered per exchange, decisions on every GPU.  Extra
+        keys: "weak" (256 replicas PER GPU), "scaling_check" (rank 0 times the whole 256-replica workload alone, in
+        the same job, so that speed-up and efficiency can be read against the same workload), "exchange_us",
+        "parity".
+``--workload`` selects others: ``slab`` (one 16384^2 lattice split by rows), ``rx``, ``latgas`` (config 4),
+``discs`` / ``--rx-model hardcore`` (config 5).  ``--impl reference`` times the UNMODIFIED reference (oracle/_ref) on
+the host cores.  Prints ONE JSON line on rank 0 (contract: task statement / DESIGN.md section "Measurement").
 """
 import argparse
 import json
+import math
 import os
 import subprocess
 import sys
@@ -26,6 +33,9 @@ METRIC = "spin-flip attempts/s"
 UNIT = "attempts/s"
 TC = 2.269185314213022
 SEED = 20260611
+MIN_TIMED_MS = 200.0  # a timed region shorter than this is repeated inside the events ("repeats")
+
+KERNELS = {"auto": 0, "generic": 1, "two_pass": 2, "resident": 3, "persistent": 4, "pbatch": 5}  # PYMC_KERNEL_*
 
 
 def measured_peak_hbm():
@@ -37,27 +47,43 @@ def measured_peak_hbm():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def profiled_traffic(kernel_name, nsites_expected):
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
-    ncu --set full summary of this workload (profiles/); None if there is no capture for this kernel/size."""
+# committed ncu --set full summaries (profiles/): kernel -> (file, launch shape the capture is of)
+PROFILED = {
+    "sweep_fused_i8_kernel": ("r1_fused_final_summary.csv", "16384x16384 int8, one sweep per launch"),
+    "sweep_bits_rows_kernel": ("r1_bits_final_summary.csv", "16384x16384 bits, one colour pass per launch"),
+    "resident_kernel": ("r1_resident_rx_summary.csv", "256 x 1024^2 int8, 10 sweeps per launch"),
+    "persistent_kernel": ("r2_persist_summary.csv", "16384x16384 int8, 20 sweeps per launch"),
+    "pbatch_kernel": ("r2_pbatch_summary.csv", "16384x16384 int8, 20 sweeps per launch"),
+}
+
+
+def profiled(kernel_name):
+    """Per-launch DRAM bytes and pipe utilisation of the dominant kernel from the committed ncu summary."""
     import csv
-    table = {"sweep_fused_i8_kernel": ("r1_fused_final_summary.csv", 268435456),
-             "sweep_bits_rows_kernel": ("r1_bits_final_summary.csv", 268435456),
-             # 256 replicas of 1024^2 int8, 10 sweeps per launch (the default replica-exchange workload)
-             "resident_kernel": ("r1_resident_rx_summary.csv", 268435456)}
-    if kernel_name not in table or table[kernel_name][1] != nsites_expected:
-        return None, None
-    path = os.path.join(ROOT, "profiles", table[kernel_name][0])
+    if kernel_name not in PROFILED:
+        return None
+    fname, shape = PROFILED[kernel_name]
+    path = os.path.join(ROOT, "profiles", fname)
+    want = {"dram__bytes_read.sum": "dram_read", "dram__bytes_write.sum": "dram_write",
+            "smsp__issue_active.avg.pct_of_peak_sustained_active": "issue_active_pct",
+            "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active": "alu_pipe_pct",
+            "sm__pipe_fmaheavy_cycles_active.avg.pct_of_peak_sustained_elapsed": "fmaheavy_pipe_pct",
+            "gpu__time_duration.sum": "duration"}
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "%": 1.0, "us": 1e-3, "ms": 1.0, "ns": 1e-6, "": 1.0}
+    out = {}
     try:
-        vals = {}
         for row in csv.reader(open(path)):
-            if row and row[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
-                scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[row[1]]
-                nums = [float(v.replace(",", "")) * scale for v in row[2:] if v]
-                vals[row[0]] = sum(nums) / len(nums)
-        return vals["dram__bytes_read.sum"] + vals["dram__bytes_write.sum"], "profiles/" + table[kernel_name][0]
+            if row and row[0] in want:
+                nums = [float(v.replace(",", "")) * scale.get(row[1], 1.0) for v in row[2:] if v]
+                out[want[row[0]]] = nums[-1]  # the last captured launch (the first may be a short warm-up call)
     except Exception:
-        return None, None
+        return None
+    if "dram_read" not in out or "dram_write" not in out:
+        return None
+    out["traffic"] = out.pop("dram_read") + out.pop("dram_write")
+    out["source"] = "profiles/" + fname
+    out["capture_shape"] = shape
+    return out
 
 
 class ClockSampler:
@@ -81,6 +107,7 @@ class ClockSampler:
             self.thread.start()
         except Exception:
             self.proc = None
+        return self
 
     def _read(self):
         for line in self.proc.stdout:
@@ -118,50 +145,64 @@ def dist_env():
     return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
 
 
+class Group:
+    """The process group of the run (NCCL under torchrun, nothing on one GPU) with the few collectives bench needs."""
+
+    def __init__(self, local_rank, world):
+        self.world, self.dist, self.torch = world, None, None
+        if world > 1:
+            import torch
+            import torch.distributed as dist
+            torch.cuda.set_device(local_rank)
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+            self.dist, self.torch = dist, torch
+
+    def barrier(self):
+        if self.dist:
+            self.dist.barrier()
+
+    def max(self, x):
+        if not self.dist:
+            return float(x)
+        t = self.torch.tensor([float(x)], device="cuda", dtype=self.torch.float64)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def min(self, x):
+        return -self.max(-float(x))
+
+    def close(self):
+        if self.dist:
+            self.dist.destroy_process_group()
+
+
 # ------------------------------------------------------------------------------------------------
-# CPU baseline: the reference's MCstep loop (oracle/cpu_port.py), one replica per host core
+# CPU baseline: the UNMODIFIED reference (oracle/_ref, see oracle/make_ref.py) on the host cores; the restated loop
+# (oracle/cpu_port.py) only if the reference files are not on this machine
 # ------------------------------------------------------------------------------------------------
-def cpu_baseline(seconds_target=12.0):
-    from oracle import cpu_port
+def cpu_baseline(seconds_target=12.0, legs=False):
+    from oracle import refarm
     cores = os.cpu_count() or 1
-    # size the sample from a short calibration so that it is about seconds_target of CPU work per core
+    if refarm.available():
+        calib, _ = refarm.time_mcstep("ising", 1024, TC, 30000, 1)
+        ntrials = int(max(calib, 5e4) * seconds_target)
+        value, wall = refarm.time_mcstep("ising", 1024, TC, ntrials, cores)
+        out = {"value": value, "unit": UNIT, "cores": cores, "kind": "reference", "wall_s": wall,
+               "sample": "%d calls of the reference's CanonicalMonteCarlo.MCstep (py_mc/mc.py:170-185 on "
+                         "examples/ising2D.py) per core on a 1024x1024 float64 lattice at kT=Tc, one replica per core "
+                         "(%d cores, %.1f s; imported unmodified from oracle/_ref); the per-trial cost does not depend "
+                         "on lattice size" % (ntrials, cores, wall)}
+        if legs:
+            out["legs"] = refarm.all_legs(seconds=2.0, cores=cores)
+        return out
+    from oracle import cpu_port
     calib, _ = cpu_port.time_all_cores(1024, -1.0, TC, 100000, 1)
     ntrials = int(max(calib, 5e4) * seconds_target)
     value, wall = cpu_port.time_all_cores(1024, -1.0, TC, ntrials, cores)
     return {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "wall_s": wall,
-            "sample": "%d single-site MCstep trials per core on a 1024x1024 float64 lattice at kT=Tc, one replica "
-                      "per core (%d cores, %.1f s); per-trial cost of the reference loop does not depend on "
-                      "lattice size" % (ntrials, cores, wall)}
-
-
-def run_reference(args):
-    rank, _, world = dist_env()
-    if rank != 0:
-        return
-    # each "step" of this arm is a bounded sample of the same workload: cap the count so the run ends in minutes
-    args.steps = min(args.steps, 4)
-    args.warmup = min(args.warmup, 1)
-    t_per_step = max(2.0, 20.0 / max(1, args.steps + args.warmup))
-    cb = None
-    vals, walls = [], []
-    for i in range(args.warmup + args.steps):
-        c = cpu_baseline(seconds_target=t_per_step)
-        if i >= args.warmup:
-            vals.append(c["value"])
-            walls.append(c["wall_s"])
-            cb = c
-    value = sum(vals) / len(vals)
-    cb["value"] = value
-    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sum(walls) / len(walls),
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(args)}, "cpu_baseline": cb,
-            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
-
-
-KERNELS = {"auto": 0, "generic": 1, "two_pass": 2, "resident": 3}  # PYMC_KERNEL_* of include/pymc_b200.h
+            "sample": "%d single-site MCstep trials per core (restated loop, oracle/cpu_port.py: the reference files "
+                      "are not on this machine) on a 1024x1024 float64 lattice at kT=Tc, %d cores, %.1f s"
+                      % (ntrials, cores, wall)}
 
 
 def pick_workload(args, world):
@@ -170,455 +211,613 @@ def pick_workload(args, world):
     return "ising16k" if world == 1 else "rx"
 
 
-def workload_name(args, world=None):
-    world = args.gpus if world is None else world
-    if pick_workload(args, world) == "rx":
-        name = ("ising2d" if args.rx_model == "ising" else "hardcore_lattice_gas_mu=%g" % args.rx_mu)
-        return ("%s_replica_exchange_%d_replicas_of_%dx%d_per_gpu_kT=%.2f..%.2f_exchange_every_%d_sweeps"
-                % (name, args.rx_replicas, args.rx_L, args.rx_L, args.rx_kT_lo, args.rx_kT_hi, args.rx_every))
-    return "ising2d_%dx%d_single_replica_checkerboard_kT=%s_J=-1" % (args.L, args.L, "Tc" if args.kT == TC else "%g" % args.kT)
+def headline_config(args, world):
+    """The ``config`` object of the line: the same for our arm and for the reference arm."""
+    wl = pick_workload(args, world)
+    if wl == "rx":
+        R = args.rx_replicas_total if args.rx_replicas_total else args.rx_replicas * world
+        name = "ising2d" if args.rx_model == "ising" else "hardcore_lattice_gas_mu=%g" % args.rx_mu
+        return {"workload": "%s_replica_exchange_%d_replicas_of_%dx%d_in_total_kT=%.2f..%.2f_exchange_every_%d_sweeps"
+                            % (name, R, args.rx_L, args.rx_L, args.rx_kT_lo, args.rx_kT_hi, args.rx_every),
+                "layout": args.layout, "replicas_total": R, "lattice": [args.rx_L, args.rx_L], "seed": SEED}
+    if wl == "slab":
+        return {"workload": "ising2d_%dx%d_one_lattice_in_row_slabs_kT=Tc_J=-1" % (args.L, args.L), "layout": "int8", "seed": SEED}
+    if wl == "latgas":
+        return {"workload": "latgas_%d_replicas_of_%dx%d_J=-1_kT=1" % (args.lg_replicas, args.lg_L, args.lg_L),
+                "layout": args.layout, "seed": SEED}
+    if wl == "discs":
+        return {"workload": "hard_discs_%d_replicas_20_discs" % args.disc_replicas, "seed": SEED}
+    return {"workload": "ising2d_%dx%d_single_replica_checkerboard_kT=%s_J=-1"
+                        % (args.L, args.L, "Tc" if args.kT == TC else "%g" % args.kT),
+            "layout": args.layout, "sites_per_gpu": args.L * args.L, "seed": SEED}
+
+
+def run_reference(args):
+    rank, _, world = dist_env()
+    if rank != 0:
+        return
+    nsamples = args.warmup + args.steps
+    t_per_step = min(6.0, max(1.0, 60.0 / max(1, nsamples)))  # bounded samples: the whole arm ends within minutes
+    vals, walls, cb = [], [], None
+    for i in range(nsamples):
+        c = cpu_baseline(seconds_target=t_per_step)
+        if i >= args.warmup:
+            vals.append(c["value"])
+            walls.append(c["wall_s"])
+            cb = c
+    value = sum(vals) / len(vals)
+    cb["value"] = value
+    try:  # BASELINE.md section 4, legs 3-4, once
+        from oracle import refarm
+        if refarm.available():
+            cb["legs"] = refarm.all_legs(seconds=2.0, cores=cb["cores"])
+    except Exception as exc:
+        cb["legs"] = {"error": repr(exc)}
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sum(walls) / len(walls),
+            "higher_is_better": True, "scaling": "weak" if pick_workload(args, args.gpus) != "rx" else "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": headline_config(args, args.gpus), "cpu_baseline": cb,
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+            "note": "each step is a bounded sample of the workload's Metropolis trials run by the reference's own "
+                    "CPU code on all host cores (one replica per core, as the reference uses cores)"}
+    print(json.dumps(line), flush=True)
+
+
+def roofline_block(kname, alg_bytes_per_launch, launch_ms, on_chip):
+    """The contract's roofline object: algorithmic bytes per launch over the measured launch time against the measured
+    HBM copy peak (SURVEY 8d accounting).  For the kernels that keep the lattice in shared memory that figure is an
+    accounting figure, not DRAM traffic: ``bound`` says what really limits them and ``dram_gbs`` what DRAM moves."""
+    peak, peak_src = measured_peak_hbm()
+    achieved = alg_bytes_per_launch / (launch_ms * 1e-3) / 1e9
+    prof = profiled(kname) or {}
+    r = {"bound": "alu" if on_chip else "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+         "traffic": prof.get("traffic"), "traffic_source": prof.get("source"), "traffic_capture": prof.get("capture_shape"),
+         "kernel": kname, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes_per_launch,
+         "accounting": "achieved = algorithmic bytes (2 x bytes/site per attempt, SURVEY 8d) / CUDA-event time of the launch"}
+    for k in ("issue_active_pct", "alu_pipe_pct", "fmaheavy_pipe_pct"):
+        if k in prof:
+            r[k] = prof[k]
+    if prof.get("traffic") and prof.get("duration"):
+        r["dram_gbs_in_capture"] = prof["traffic"] / (prof["duration"] * 1e-3) / 1e9
+    if on_chip:
+        r["note"] = ("not HBM-bound: the lattices stay in the shared memory of the SMs for all sweeps of a launch, DRAM moves "
+                     "them once per launch (`traffic`); the limiter is instruction issue on the integer ALU / FMA-heavy "
+                     "pipes (Philox4x32-10 + bit-serial Metropolis test), see profiles/README.md")
+    else:
+        r["note"] = "crosses HBM every sweep; measured DRAM traffic equals the algorithmic bytes; issue-limited (profiles/README.md)"
+    return r
+
+
+def timed_repeats(grp, one_block, sync, start, stop, min_ms=MIN_TIMED_MS):
+    """Time ``one_block()`` (the K timed steps) with CUDA events; if it is shorter than min_ms, repeat it inside the
+    events and report the mean.  All ranks use the same repeat count (taken from the all-reduced calibration)."""
+    sync()
+    grp.barrier()
+    start()
+    one_block()
+    ms1 = grp.max(stop())
+    repeats = max(1, int(math.ceil(min_ms / max(ms1, 1e-3))))
+    sync()
+    grp.barrier()
+    start()
+    for _ in range(repeats):
+        one_block()
+    ms = grp.max(stop())
+    return ms / repeats, repeats
 
 
 # ------------------------------------------------------------------------------------------------
-def run_rx(args):
-    """Replica exchange, weak scaling: every GPU holds rx_replicas lattices of rx_L^2; the ladder spans all
-    replicas of all GPUs; energies are all-gathered with NCCL (in place, on the kernels' stream) and the
-    exchange is decided on every GPU by the same kernel.  No host synchronisation in the timed region."""
+# replica exchange on `world` GPUs
+# ------------------------------------------------------------------------------------------------
+def make_rx(args, grp, rank, local_rank, nloc, R, group_size, offset, kernel="auto"):
     import numpy as np
-    import torch
-    rank, local_rank, world = dist_env()
     from py_mc_b200 import _cabi
     from py_mc_b200.ising2D import ising2D
-    from py_mc_b200.mc_mpi import _DeviceArray
-    torch.cuda.set_device(local_rank)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    L, nloc = args.rx_L, args.rx_replicas
-    R = nloc * world
+    L = args.rx_L
     layout = _cabi.LAYOUT_BITS if args.layout == "bits" else _cabi.LAYOUT_INT8
     kTs = np.linspace(args.rx_kT_lo, args.rx_kT_hi, R)
     if args.rx_model == "hardcore":
-        # BASELINE config 5 read as a lattice model: nearest-neighbour exclusion, ladder over kT at fixed mu
-        # (e.g. --rx-model hardcore --rx-replicas 8 on 8 GPUs = 64 temperatures)
         from py_mc_b200.latgas import hardcore_latticegas
         model = hardcore_latticegas(mu=args.rx_mu)
     else:
         model = ising2D(-1.0)
     lat = _cabi.Lattices(model._pmc_model, L, L, nreplicas=nloc, ntemps=R, seed=SEED, layout=layout,
-                         device=local_rank, replica_offset=rank * nloc, nreplicas_global=R, kernel=KERNELS[args.kernel])
-    stream = torch.cuda.current_stream()
-    lat.set_stream(stream.cuda_stream)
+                         device=local_rank, replica_offset=offset, nreplicas_global=R, kernel=KERNELS[kernel])
+    if group_size > 1:
+        lat.set_stream(grp.torch.cuda.current_stream().cuda_stream)
     lat.init_random()
     lat.set_accept_tables(np.array([model._pmc_thresholds(kT) for kT in kTs]))
     lat.rx_setup(1.0 / kTs, *model._pmc_energy_coeffs())
-    eptr, _ = lat.rx_buffers()
-    e_all = torch.as_tensor(_DeviceArray(eptr, R, "<f8"), device="cuda")
-    e_mine = e_all[rank * nloc:(rank + 1) * nloc]
-    state = {"scheme": 0, "done": 0, "exchanges": 0, "calls": 0}
+    return lat
 
-    def steps(n):
-        while n > 0:  # the sweeps up to the next exchange are one call (one launch on the resident kernel)
-            chunk = min(n, args.rx_every - state["done"] % args.rx_every)
-            lat.sweep(chunk)
-            state["calls"] += 1
-            state["done"] += chunk
-            n -= chunk
-            if state["done"] % args.rx_every == 0:
-                lat.rx_energies()
-                if dist is not None:
+
+def rx_measure(args, grp, rank, local_rank, nloc, R, distributed, kernel="auto"):
+    """Time K steps of replica exchange on a batch of nloc local replicas out of R.  distributed: the R replicas are
+    spread over all ranks (energies all-gathered per exchange); otherwise this rank holds all R by itself."""
+    import numpy as np
+    from py_mc_b200.mc_mpi import _DeviceArray
+    world = grp.world if distributed else 1
+    lat = make_rx(args, grp, rank, local_rank, nloc, R, world, rank * nloc if distributed else 0, kernel)
+    every = args.rx_every
+    st = {"scheme": 0, "done": 0, "exchanges": 0, "launches": 0}
+    lps, kname = lat.sweep_kernel_info()
+    if distributed and world > 1:
+        torch, dist = grp.torch, grp.dist
+        eptr, _ = lat.rx_buffers()
+        e_all = torch.as_tensor(_DeviceArray(eptr, R, "<f8"), device="cuda")
+        e_mine = e_all[rank * nloc:(rank + 1) * nloc]
+
+        def steps(n, exchange=True):
+            while n > 0:  # the sweeps up to the next exchange are one call
+                chunk = min(n, every - st["done"] % every)
+                lat.sweep(chunk)
+                st["launches"] += 1 if kname in ("pbatch_kernel", "resident_kernel", "persistent_kernel") and chunk >= 2 else lps * chunk
+                st["done"] += chunk
+                n -= chunk
+                if st["done"] % every == 0 and exchange:
+                    lat.rx_energies()
                     dist.all_gather_into_tensor(e_all, e_mine)
-                lat.rx_exchange(state["scheme"])
-                state["scheme"] ^= 1
-                state["exchanges"] += 1
+                    lat.rx_exchange(st["scheme"])
+                    st["scheme"] ^= 1
+                    st["exchanges"] += 1
+                    st["launches"] += 2
+    else:
+        def steps(n, exchange=True):
+            # one GPU holds all replicas: sweeps, energies and decisions are one launch per call (pymc_rx_cycle)
+            head = min(n, (every - st["done"] % every) % every)
+            if head:
+                lat.sweep(head)
+                st["launches"] += 1
+                st["done"] += head
+                n -= head
+                if st["done"] % every == 0 and exchange:
+                    lat.rx_energies()
+                    lat.rx_exchange(st["scheme"])
+                    st["scheme"] ^= 1
+                    st["exchanges"] += 1
+            ncyc = n // every
+            if ncyc and exchange:
+                lat.rx_cycle(ncyc, every, st["scheme"])
+                st["scheme"] ^= ncyc & 1
+                st["exchanges"] += ncyc
+                st["launches"] += (1 if kname == "pbatch_kernel" else ncyc * (2 + (1 if every >= 2 and lps == 1 else lps * every)))
+            elif ncyc:
+                lat.sweep(ncyc * every)  # the same sweeps in the same single launch, without the exchange steps
+                st["launches"] += 1
+            st["done"] += ncyc * every
+            tail = n - ncyc * every
+            if tail:
+                lat.sweep(tail)
+                st["launches"] += 1
+                st["done"] += tail
 
     steps(args.warmup)
-    torch.cuda.synchronize()
-    if dist is not None:
-        dist.barrier()
-    torch.cuda.synchronize()
-    sampler = ClockSampler(local_rank)
-    sampler.start()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ex0, calls0 = state["exchanges"], state["calls"]
-    ev0.record(stream)
-    steps(args.steps)
-    ex1, ncalls = state["exchanges"], state["calls"] - calls0
-    ev1.record(stream)
-    torch.cuda.synchronize()
-    ms = ev0.elapsed_time(ev1)
-    if dist is not None:
-        dist.barrier()
-        t = torch.tensor([ms], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
-    if ms < 400.0:
-        # keep the same loop running (untimed) until the sampler has seen ~0.4 s under load; the count comes
-        # from the all-reduced time so that every rank issues the same number of collectives
-        steps(int(args.steps * (400.0 - ms) / max(ms, 1e-3)) + 1)
-        torch.cuda.synchronize()
+    if distributed and world > 1:  # one untimed exchange after the barrier: NCCL's first-call and skew costs stay outside
+        lat.synchronize()
+        grp.barrier()
+        steps(every - st["done"] % every)
+    K = args.steps
+    ex0, l0 = st["exchanges"], st["launches"]
+    ms, repeats = timed_repeats(grp, lambda: steps(K), lat.synchronize, lat.timer_start, lat.timer_stop)
+    nex = (st["exchanges"] - ex0) / (repeats + 1.0)
+    nlaunch = (st["launches"] - l0) / (repeats + 1.0)
+    # the same launches without the exchange step: what an exchange costs on top of pure sweeping
+    ms_plain, _ = timed_repeats(grp, lambda: steps(K, exchange=False), lat.synchronize, lat.timer_start, lat.timer_stop)
+    if st["done"] % every:  # realign so that later calls start on an exchange boundary
+        steps(every - st["done"] % every, exchange=False)
+    nsites = nloc * args.rx_L * args.rx_L
+    tried, acc = lat.rx_stats()
+    out = {"lat": lat, "steps": steps, "ms": ms, "repeats": repeats, "kernel": kname, "nsites_local": nsites,
+           "value": world * nsites * K / (ms * 1e-3), "ms_per_step": ms / K, "exchanges_per_block": nex,
+           "launches_per_block": nlaunch, "exchange_us": (1e3 * (ms - ms_plain) / nex) if nex else None,
+           "acceptance": float(acc.sum()) / max(1.0, float(tried.sum())),
+           "rx_sweeps_per_s": world * nloc * K / (ms * 1e-3)}
+    # parity: tracked == recomputed sums on this rank; identical replica -> temperature map on every rank
+    b, m = lat.tracked()
+    b = b.copy()
+    m = m.copy()
+    rb, rm = lat.reduce_observables()
+    ok = bool(np.array_equal(b, rb) and np.array_equal(m, rm))
+    mp = lat.get_replica_to_T()
+    ok = ok and sorted(mp.tolist()) == list(range(R))
+    if distributed and world > 1:
+        t = grp.torch.tensor(mp, device="cuda", dtype=grp.torch.int32)
+        lo, hi = t.clone(), t.clone()
+        grp.dist.all_reduce(lo, op=grp.dist.ReduceOp.MIN)
+        grp.dist.all_reduce(hi, op=grp.dist.ReduceOp.MAX)
+        ok = ok and bool((lo == hi).all().item())
+        ok = grp.min(1.0 if ok else 0.0) > 0.5
+    out["parity"] = "ok" if ok else "FAILED"
+    return out
+
+
+def run_rx(args):
+    rank, local_rank, world = dist_env()
+    grp = Group(local_rank, world)
+    import numpy as np  # noqa: F401
+    R = args.rx_replicas_total if args.rx_replicas_total else args.rx_replicas * world
+    if R % world:
+        raise SystemExit("%d replicas cannot be split evenly over %d GPUs" % (R, world))
+    nloc = R // world
+    sampler = ClockSampler(local_rank).start()  # before the barriers: its start-up cost is not inside a timed region
+    head = rx_measure(args, grp, rank, local_rank, nloc, R, True, args.kernel)
     clocks = sampler.stop()
-    clocks["window"] = "timed region" if ms >= 400.0 else "timed region + untimed repeat of the same loop (0.4 s in all)"
-    nsites = nloc * L * L
-    value = world * nsites * args.steps / (ms * 1e-3)
-    nex = ex1 - ex0
+    lat = head["lat"]
+    layout_bytes = 1.0 if args.layout == "int8" else 0.125
+    nsites = head["nsites_local"]
+    K = args.steps
 
     # end to end: host configurations in, sweeps + exchanges, observables and the map out, every step
+    import numpy as np
+    from py_mc_b200 import _cabi
     host = [lat.download(r) for r in range(min(nloc, 4))]
-    img = np.stack([lat.download(r) for r in range(nloc)]) if args.e2e_full else None
-    reps = 3
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    for _ in range(reps):
-        for r in range(nloc):
-            lat.upload(r, img[r] if img is not None else host[r % len(host)])
-        steps(args.e2e_sweeps)
-        b, m = lat.tracked()
-        mp = lat.get_replica_to_T()
-    t_e2e = time.perf_counter() - t0
-    if dist is not None:
-        t = torch.tensor([t_e2e], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        t_e2e = float(t.item())
-    e2e_value = world * nsites * args.e2e_sweeps * reps / t_e2e
-    tried, acc = lat.rx_stats()
-
-    bytes_per_site = 1.0 if layout == _cabi.LAYOUT_INT8 else 0.125
-    lps, kname = lat.sweep_kernel_info()
-    nlaunch = ncalls if kname == "resident_kernel" else lps * args.steps  # resident: one launch per call
-    # algorithmic bytes (SURVEY 8d): 2 x bytes_per_site per attempt, whatever the kernel really moves
-    alg = 2.0 * bytes_per_site * nsites * args.steps / nlaunch
-    launch_ms = ms / nlaunch  # exchange kernels are ~microseconds; stated in config
-    peak, peak_src = measured_peak_hbm()
-    achieved = alg / (launch_ms * 1e-3) / 1e9
-    traffic = traffic_src = None
-    if (kname == "resident_kernel" and layout == _cabi.LAYOUT_INT8 and args.rx_model == "ising" and (L, nloc) == (1024, 256)
-            and args.rx_every == 10):  # the capture is of exactly this launch shape
-        traffic, traffic_src = profiled_traffic(kname, nsites)
-    if rank == 0:
-        line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "u8" if layout == _cabi.LAYOUT_INT8 else "u64 (1 bit/site)",
-            "data": "synthetic",
-            "config": {"workload": workload_name(args, world), "layout": args.layout, "sites_per_gpu": nsites,
-                       "replicas_per_gpu": nloc, "replicas_total": R, "lattice": [L, L],
-                       "step": "one sweep of every replica (2 colour passes) + exchange when due",
-                       "exchanges_in_timed_region": nex, "seed": SEED,
-                       "rx_sweeps_per_s": world * nloc * args.steps / (ms * 1e-3),
-                       "exchange_acceptance": float(acc.sum()) / max(1.0, float(tried.sum())),
-                       "l2": "working set %d MiB per GPU %s L2" % (int(nsites * bytes_per_site) >> 20,
-                                                                  "exceeds" if nsites * bytes_per_site > 126e6 else "fits in"),
-                       "parallelism": "replicas block-partitioned over %d GPU(s); NCCL all-gather of %d energies per "
-                                      "exchange" % (world, R)},
-            "clocks": clocks,
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": nsites,
-                    "d2h_bytes_per_step": 16 * nloc + 4 * R, "sweeps_per_step": args.e2e_sweeps,
-                    "note": "C-ABI: upload every replica from host int8, sweeps+exchanges, read back tracked "
-                            "observables and the replica->T map"},
-            "gpu_launches": nlaunch + 2 * nex,
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "traffic_source": traffic_src, "kernel": kname, "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": alg},
-        }
-        if kname == "resident_kernel":
-            line["roofline"]["note"] = ("not HBM-bound: the lattice stays in shared memory for the %d sweeps of a launch; "
-                                        "HBM moves 2 x bytes_per_site per launch, not per sweep" % args.rx_every)
-        print(json.dumps(line), flush=True)
-    if dist is not None:
-        dist.destroy_process_group()
-
-
-def run_latgas(args):
-    """BASELINE config 4: pair-interaction lattice gas, 512 batched replicas of 256 x 256 (size not given by
-    BASELINE; stated here), J = -1, Eads - mu = 0, kT = 1.  One step = one flip sweep + one full
-    particle-hole exchange sweep of every replica.  Single GPU."""
-    import numpy as np
-    from py_mc_b200 import _cabi
-    from py_mc_b200.latgas_move import latticegas
-    L, R = args.lg_L, args.lg_replicas
-    layout = _cabi.LAYOUT_BITS if args.layout == "bits" else _cabi.LAYOUT_INT8
-    model = latticegas(Eads=0.0, J=-1.0, mu=0.0)
-    lat = _cabi.Lattices(_cabi.MODEL_LATGAS, L, L, nreplicas=R, ntemps=1, seed=SEED, layout=layout,
-                         kernel=KERNELS[args.kernel])
-    lat.init_random()
-    lat.set_accept_tables(model._pmc_thresholds(1.0)[None, :])
-    lat.set_pair_tables(model._pmc_pair_thresholds(1.0)[None, :])
-    nsites = R * L * L
-    out = {}
-    for name, fn, attempts in (("flip", lambda n: lat.sweep(n), nsites), ("pair_exchange", lambda n: lat.pair_sweep(n), 2 * nsites)):
-        fn(args.warmup)
+    e2e = {}
+    for spp in sorted(set([1, args.e2e_sweeps])):
+        reps = 2
         lat.synchronize()
-        lat.timer_start()
-        fn(args.steps)
-        ms = lat.timer_stop()
-        out[name] = {"value": attempts * args.steps / (ms * 1e-3), "unit": "attempts/s", "ms_per_step": ms / args.steps}
-    b, n = lat.tracked()
-    b2, n2 = lat.reduce_observables()
-    assert np.array_equal(b, b2) and np.array_equal(n, n2)
-    lps, kname = lat.sweep_kernel_info()
-    line = {"metric": "lattice-gas attempts/s", "value": out["flip"]["value"], "unit": "attempts/s", "n_gpus": 1,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": out["flip"]["ms_per_step"],
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": "latgas_%d_replicas_of_%dx%d_J=-1_kT=1" % (R, L, L), "layout": args.layout,
-                       "flip_kernel": kname, "seed": SEED},
-            "pair_exchange": out["pair_exchange"],
-            "gpu_launches": 2 * ((args.steps + 4095) // 4096) if kname == "resident_kernel" else (lps + 16) * args.steps}
-    print(json.dumps(line), flush=True)
-
-
-def run_discs(args):
-    """BASELINE config 5 (re-interpreted, SURVEY.md section 8 notes): batched independent hard-disc replicas,
-    64 x 128 = 8192 replicas of the shipped system (20 discs, L = 1, r = 1/14, maxstep = r/2)."""
-    from py_mc_b200.hardcore import DiscBatch
-    R = args.disc_replicas
-    b = DiscBatch(R, 1.0, 20, 1.0 / 14.0, 1.0 / 28.0, isotropic=False, seed=SEED)
-    per = args.disc_trials
-    b._d.timed_run(per)
-    ms = [b._d.timed_run(per) for _ in range(max(3, args.steps // 10))]
-    ms_best = sorted(ms)[len(ms) // 2]
-    assert not b.any_overlap().any()
-    line = {"metric": "hard-disc move attempts/s", "value": R * per / (ms_best * 1e-3), "unit": "attempts/s", "n_gpus": 1,
-            "steps": len(ms), "warmup": 1, "ms_per_step": ms_best, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "hard_discs_%d_replicas_20_discs_%d_trials_per_launch" % (R, per), "seed": SEED,
-                       "acceptance": float(b.acceptance().mean())},
-            "gpu_launches": len(ms)}
-    print(json.dumps(line), flush=True)
-
-
-def run_slab(args):
-    """Strong scaling of ONE 16384 x 16384 lattice split by rows over the GPUs (SURVEY row f4): halo rows are
-    stored into the neighbours' memory by the sweep kernel itself (CUDA IPC peer mappings), one flag barrier
-    kernel per sweep, no NCCL in the timed region."""
-    import torch
-    rank, local_rank, world = dist_env()
-    from py_mc_b200 import _cabi
-    from py_mc_b200.ising2D import ising2D
-    from py_mc_b200.slab import SlabLattice
-    torch.cuda.set_device(local_rank)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    L = args.L
-    sl = SlabLattice(_cabi.MODEL_ISING, L, L, SEED, dist, device=local_rank)
-    sl.init_random()
-    sl.set_accept_tables(ising2D(-1.0)._pmc_thresholds(TC)[None, :])
-    sl.sweep(args.warmup)
-    sl.lat.synchronize()
-    if dist is not None:
-        dist.barrier()
-    sampler = ClockSampler(local_rank)
-    sampler.start()
-    sl.lat.timer_start()
-    sl.sweep(args.steps)
-    ms = sl.lat.timer_stop()
-    if dist is not None:
-        t = torch.tensor([ms], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
-    if ms < 400.0:  # every slab must issue the same number of sweeps: decide from the all-reduced time
-        sl.sweep(int(args.steps * (400.0 - ms) / max(ms, 1e-3)) + 1)
-        sl.lat.synchronize()
-    clocks = sampler.stop()
-    sl.check()
-    b, m = sl.observables()
-    if rank == 0:
-        nsites = L * L
-        peak, peak_src = measured_peak_hbm()
-        achieved = 2.0 * nsites / world / (ms / args.steps * 1e-3) / 1e9
-        print(json.dumps({
-            "metric": METRIC, "value": nsites * args.steps / (ms * 1e-3), "unit": UNIT, "n_gpus": world,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": "ising2d_%dx%d_one_lattice_in_%d_row_slabs_kT=Tc_J=-1" % (L, L, world),
-                       "layout": "int8", "rows_per_gpu": L // world, "seed": SEED,
-                       "parallelism": "row slabs; halo rows stored into peer memory by the sweep kernel, flag barrier "
-                                      "per sweep, no NCCL in the timed region",
-                       "bond_sum": b, "magnetisation": m},
-            "clocks": clocks, "gpu_launches": (1 if world == 1 else 2) * args.steps,
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "kernel": "sweep_fused_i8_kernel", "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": 2.0 * nsites / world},
-        }), flush=True)
-    if dist is not None:
-        dist.destroy_process_group()
-
-
-def run_ours(args):
-    import numpy as np
-    rank, local_rank, world = dist_env()
-    if args.workload == "slab":
-        return run_slab(args)
-    if args.workload == "latgas":
-        return run_latgas(args)
-    if args.workload == "discs":
-        return run_discs(args)
-    if pick_workload(args, world) == "rx":
-        return run_rx(args)
-    from py_mc_b200 import _cabi
-    from py_mc_b200.ising2D import ising2D
-
-    dist = None
-    if world > 1:
-        import torch
-        import torch.distributed as dist
-        torch.cuda.set_device(local_rank)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-
-    L = args.L
-    layout = _cabi.LAYOUT_BITS if args.layout == "bits" else _cabi.LAYOUT_INT8
-    thr = ising2D(-1.0)._pmc_thresholds(args.kT)[None, :]
-    nsites = L * L
-
-    def make(lay):
-        lat = _cabi.Lattices(_cabi.MODEL_ISING, L, L, nreplicas=1, ntemps=1, seed=SEED, layout=lay,
-                             device=local_rank, replica_offset=rank, nreplicas_global=world)
-        lat.init_random()
-        lat.set_accept_tables(thr)
-        return lat
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-
-    def timed(lat, steps, warmup):
-        lat.sweep(warmup)
+        grp.barrier()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            for r in range(nloc):
+                lat.upload(r, host[r % len(host)])
+            head["steps"](spp)
+            lat.tracked()
+            lat.get_replica_to_T()
         lat.synchronize()
-        barrier()
-        lat.timer_start()
-        lat.sweep(steps)
-        ms = lat.timer_stop()
-        barrier()
-        return ms
-
-    lat = make(layout)
-    sampler = ClockSampler(local_rank)
-    sampler.start()
-    ms = timed(lat, args.steps, args.warmup)
-    if ms < 400.0:  # keep the same kernel running (untimed) until the sampler has seen ~0.4 s under load
-        lat.sweep(int(args.steps * (400.0 - ms) / max(ms, 1e-3)) + 1)
-        lat.synchronize()
-    clocks = sampler.stop()
-    clocks["window"] = "timed region" if ms >= 400.0 else "timed region + untimed repeat of the same loop (0.4 s in all)"
-    if dist is not None:
-        import torch
-        t = torch.tensor([ms], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
-    value = world * nsites * args.steps / (ms * 1e-3)
-
-    # end to end through the C ABI with HOST buffers: upload, sweeps, download, every step
-    host = _cabi.pinned_empty((L, L), np.int8)
-    lat.download(0, out=host)
-    e2e_sweeps = args.e2e_sweeps
-    reps = 5
-    lat.upload(0, host)
-    lat.sweep(1)
-    lat.synchronize()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(reps):
-        lat.upload(0, host)
-        lat.sweep(e2e_sweeps)
-        lat.download(0, out=host)
-        b, m = lat.tracked()
-    t_e2e = time.perf_counter() - t0
-    if dist is not None:
-        import torch
-        t = torch.tensor([t_e2e], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        t_e2e = float(t.item())
-    e2e_value = world * nsites * e2e_sweeps * reps / t_e2e
-
-    bytes_per_site = 1.0 if layout == _cabi.LAYOUT_INT8 else 0.125
-    lps, kname = lat.sweep_kernel_info()
-    persistent = kname == "persistent_kernel"
-    # every site a launch updates is read once and written once (the fused kernel updates both colours).  The
-    # persistent kernel runs all sweeps of a call (<= 4096) in ONE cooperative launch: its algorithmic bytes are
-    # 2 x bytes_per_site per attempt all the same (SURVEY 8d), although DRAM moves the lattice once per launch.
-    nlaunch = (args.steps + 4095) // 4096 if persistent else lps * args.steps
-    alg_bytes_per_launch = 2.0 * bytes_per_site * nsites * args.steps / nlaunch
-    launch_ms = ms / nlaunch
-    peak, peak_src = measured_peak_hbm()
-    achieved = alg_bytes_per_launch / (launch_ms * 1e-3) / 1e9
-    traffic, traffic_src = profiled_traffic(kname, nsites)
+        t = grp.max(time.perf_counter() - t0)
+        e2e[spp] = world * nsites * spp * reps / t
+    lat.close()
 
     extra = {}
-    if args.also_bits and layout == _cabi.LAYOUT_INT8:
-        lat.close()
-        try:  # an extra, never allowed to take the headline line down with it
-            lat2 = make(_cabi.LAYOUT_BITS)
-            ms2 = timed(lat2, args.steps, args.warmup)
-            extra["bitpacked"] = {"value": world * nsites * args.steps / (ms2 * 1e-3), "unit": UNIT,
-                                  "ms_per_step": ms2 / args.steps, "kernel": lat2.sweep_kernel_info()[1],
-                                  "note": "same workload on the 1-bit/site layout (32 MiB: not HBM-bound)"}
-            lat2.close()
-        except Exception as exc:
-            extra["bitpacked"] = {"error": repr(exc)}
-    if persistent:  # the per-sweep kernel on the same workload, for comparison (one launch per sweep, 2 B/attempt of DRAM)
+    if world > 1 and not args.no_extras:
+        # weak scaling: the same per-GPU batch as on one GPU (256 replicas each), one ladder over all of them
         try:
-            lat3 = _cabi.Lattices(_cabi.MODEL_ISING, L, L, nreplicas=1, ntemps=1, seed=SEED, layout=layout,
-                                  device=local_rank, replica_offset=rank, nreplicas_global=world)
-            lat3.init_random()
-            lat3.set_accept_tables(thr)
-            lat3.sweep(1)
-            lat3.synchronize()
-            n3 = max(50, args.steps // 10)
-            lat3.timer_start()
-            for _ in range(n3):
-                lat3.sweep(1)  # single-sweep calls take the fused kernel
-            ms3 = lat3.timer_stop()
-            extra["one_sweep_per_launch"] = {"value": world * nsites * n3 / (ms3 * 1e-3), "unit": UNIT,
-                                             "ms_per_step": ms3 / n3, "kernel": "sweep_fused_i8_kernel",
-                                             "roofline_frac": 2.0 * bytes_per_site * nsites / (ms3 / n3 * 1e-3) / 1e9 /
-                                             measured_peak_hbm()[0]}
-            lat3.close()
+            w = rx_measure(args, grp, rank, local_rank, args.rx_replicas, args.rx_replicas * world, True, args.kernel)
+            w["lat"].close()
+            extra["weak"] = {"value": w["value"], "unit": UNIT, "ms_per_step": w["ms_per_step"], "replicas_per_gpu": args.rx_replicas,
+                             "replicas_total": args.rx_replicas * world, "exchange_us": w["exchange_us"], "kernel": w["kernel"],
+                             "parity": w["parity"], "repeats": w["repeats"], "scaling": "weak"}
         except Exception as exc:
-            extra["one_sweep_per_launch"] = {"error": repr(exc)}
+            extra["weak"] = {"error": repr(exc)}
+        # the SAME 256-replica workload on one GPU, timed by rank 0 in this job
+        n1 = None
+        if rank == 0:
+            try:
+                one = rx_measure(args, Group(local_rank, 1), 0, local_rank, R, R, False, args.kernel)
+                one["lat"].close()
+                n1 = one
+            except Exception as exc:
+                extra["scaling_check"] = {"error": repr(exc)}
+        grp.barrier()
+        if rank == 0 and n1:
+            extra["scaling_check"] = {
+                "n1_value": n1["value"], "n1_ms_per_step": n1["ms_per_step"], "n1_kernel": n1["kernel"],
+                "n1_exchange_us": n1["exchange_us"],
+                "speedup": head["value"] / n1["value"], "efficiency": head["value"] / (world * n1["value"]),
+                "weak_efficiency": (extra["weak"]["value"] / (world * n1["value"])) if "value" in extra.get("weak", {}) else None,
+                "note": "n1 = the same %d-replica workload on one GPU, measured by rank 0 in this job" % R}
 
     if rank == 0:
+        on_chip = head["kernel"] in ("pbatch_kernel", "resident_kernel", "persistent_kernel")
+        alg = 2.0 * layout_bytes * nsites * K / max(1.0, head["launches_per_block"] - 2 * head["exchanges_per_block"])
+        launch_ms = head["ms"] / max(1.0, head["launches_per_block"] - 2 * head["exchanges_per_block"])
+        cfg = headline_config(args, world)
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "u8" if layout == _cabi.LAYOUT_INT8 else "u64 (1 bit/site)",
-            "data": "synthetic",
-            "config": {"workload": workload_name(args), "layout": args.layout, "sites_per_gpu": nsites,
-                       "step": "one full sweep (both colours)", "seed": SEED,
-                       "l2": ("lattice (%d MiB in HBM) is loaded once per launch and stays in the shared memory of the SMs "
-                              "as bits for all %d sweeps of the timed launch, then is stored once; no cache is relied upon"
-                              % (int(nsites * bytes_per_site) >> 20, args.steps)) if persistent else
-                             "working set %d MiB %s L2" % (int(nsites * bytes_per_site) >> 20,
-                                                           "exceeds" if nsites * bytes_per_site > 126e6 else "fits in"),
-                       "parallelism": "replicas only" if world > 1 else "single GPU"},
-            "clocks": clocks,
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": nsites, "d2h_bytes_per_step": nsites + 16,
-                    "sweeps_per_step": e2e_sweeps,
-                    "note": "C-ABI upload(pinned host int8) + sweeps + download(host int8) + tracked observables per step"},
-            "gpu_launches": nlaunch,
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "traffic_source": traffic_src, "kernel": kname, "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": alg_bytes_per_launch,
-                         "note": ("not HBM-bound: the lattice stays in the shared memory of the %d SMs for all sweeps of the "
-                                  "launch; DRAM moves 2 x bytes_per_site per launch, not per sweep; the integer ALU pipe "
-                                  "limits the kernel" % 148) if persistent else
-                                 "not HBM-bound: the integer ALU pipe limits this kernel (profiles/README.md)"},
+            "metric": METRIC, "value": head["value"], "unit": UNIT, "n_gpus": world, "steps": K, "warmup": args.warmup,
+            "repeats": head["repeats"], "ms_per_step": head["ms_per_step"], "higher_is_better": True,
+            "scaling": "strong" if args.rx_replicas_total else "weak", "vs_baseline": None,
+            "dtype": "u8" if args.layout == "int8" else "u64 (1 bit/site)", "data": "synthetic", "config": cfg,
+            "workload_detail": {"replicas_per_gpu": nloc, "sites_per_gpu": nsites,
+                                "step": "one sweep of every replica (2 colour passes) + exchange when due",
+                                "exchanges_per_timed_block": head["exchanges_per_block"], "rx_sweeps_per_s": head["rx_sweeps_per_s"],
+                                "exchange_acceptance": head["acceptance"],
+                                "l2": "no cache is relied upon: the lattices sit in shared memory between exchanges" if on_chip else
+                                      "working set %d MiB per GPU" % (int(nsites * layout_bytes) >> 20),
+                                "parallelism": ("replicas block-partitioned over %d GPUs; all-gather of %d energies (NCCL, in place, on "
+                                                "the kernels' stream) per exchange; identical decision kernel on every GPU" % (world, R))
+                                if world > 1 else "one GPU holds all replicas: sweeps, energies and pair decisions in one launch"},
+            "exchange_us": head["exchange_us"], "parity": head["parity"], "clocks": clocks,
+            "e2e": {"value": e2e[args.e2e_sweeps], "unit": UNIT, "h2d_bytes_per_step": nsites, "d2h_bytes_per_step": 16 * nloc + 4 * R,
+                    "sweeps_per_step": args.e2e_sweeps, "at_1_sweep_per_step": e2e[1],
+                    "note": "C-ABI: upload every local replica from host int8, sweeps + exchanges, read back the exact sums and "
+                            "the replica->T map; bytes are per GPU"},
+            "gpu_launches": int(round(head["launches_per_block"])),
+            "roofline": roofline_block(head["kernel"], alg, launch_ms, on_chip),
         }
         line.update(extra)
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline()
         print(json.dumps(line), flush=True)
-    if dist is not None:
-        dist.destroy_process_group()
+    grp.close()
+
+
+# ------------------------------------------------------------------------------------------------
+def run_latgas(args):
+    """BASELINE config 4: pair-interaction lattice gas, 512 batched replicas of 256 x 256 (size not given by
+    BASELINE; stated here), J = -1, Eads - mu = 0, kT = 1.  Flip sweeps and particle-hole exchange sweeps.  Single GPU."""
+    import numpy as np
+    from py_mc_b200 import _cabi
+    from py_mc_b200.latgas_move import latticegas
+    L, R = args.lg_L, args.lg_replicas
+    layout = _cabi.LAYOUT_BITS if args.layout == "bits" else _cabi.LAYOUT_INT8
+    bps = 1.0 if args.layout == "int8" else 0.125
+    model = latticegas(Eads=0.0, J=-1.0, mu=0.0)
+    lat = _cabi.Lattices(_cabi.MODEL_LATGAS, L, L, nreplicas=R, ntemps=1, seed=SEED, layout=layout, kernel=KERNELS[args.kernel])
+    lat.init_random()
+    lat.set_accept_tables(model._pmc_thresholds(1.0)[None, :])
+    lat.set_pair_tables(model._pmc_pair_thresholds(1.0)[None, :])
+    nsites = R * L * L
+    grp = Group(0, 1)
+    sampler = ClockSampler(0).start()
+    out = {}
+    lps, kname = lat.sweep_kernel_info()
+    for name, fn, attempts in (("flip", lambda: lat.sweep(args.steps), nsites), ("pair_exchange", lambda: lat.pair_sweep(args.steps), 2 * nsites)):
+        fn()
+        ms, rep = timed_repeats(grp, fn, lat.synchronize, lat.timer_start, lat.timer_stop)
+        out[name] = {"value": attempts * args.steps / (ms * 1e-3), "unit": "attempts/s", "ms_per_step": ms / args.steps, "repeats": rep}
+    clocks = sampler.stop()
+    b, n = lat.tracked()
+    b2, n2 = lat.reduce_observables()
+    parity = bool(np.array_equal(b, b2) and np.array_equal(n, n2))
+    # end to end: host images in, one flip sweep + one pair sweep per step, exact sums out
+    host = [lat.download(r) for r in range(4)]
+    e2e = {}
+    for spp in (1, args.e2e_sweeps):
+        t0 = time.perf_counter()
+        for r in range(R):
+            lat.upload(r, host[r % 4])
+        lat.sweep(spp)
+        lat.pair_sweep(spp)
+        lat.tracked()
+        e2e[spp] = nsites * spp / (time.perf_counter() - t0)
+    one_launch = kname in ("resident_kernel", "pbatch_kernel")
+    nl = max(1, (args.steps + 4095) // 4096) if one_launch else lps * args.steps
+    flip_ms = out["flip"]["ms_per_step"] * args.steps
+    roof = roofline_block(kname, 2.0 * bps * nsites * args.steps / nl, flip_ms / nl, one_launch)
+    pair_ms = out["pair_exchange"]["ms_per_step"] * args.steps
+    peak, _ = measured_peak_hbm()
+    out["pair_exchange"]["roofline"] = {"bound": "alu" if one_launch else "latency", "unit": "GB/s", "peak": peak,
+                                        "achieved": 1.0 * bps * 2 * nsites * args.steps / (pair_ms * 1e-3) / 1e9,
+                                        "accounting": "1 B (int8) per pair attempt: one read + one write of the lattice per 2N bonds"}
+    out["pair_exchange"]["roofline"]["frac"] = out["pair_exchange"]["roofline"]["achieved"] / peak
+    line = {"metric": "lattice-gas flip attempts/s", "value": out["flip"]["value"], "unit": "attempts/s", "n_gpus": 1,
+            "steps": args.steps, "warmup": args.warmup, "repeats": out["flip"]["repeats"], "ms_per_step": out["flip"]["ms_per_step"],
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8" if args.layout == "int8" else "u64 (1 bit/site)",
+            "data": "synthetic", "config": headline_config(args, 1), "flip_kernel": kname, "pair_exchange": out["pair_exchange"],
+            "parity": "ok" if parity else "FAILED", "clocks": clocks,
+            "e2e": {"value": e2e[args.e2e_sweeps], "unit": "flip attempts/s", "h2d_bytes_per_step": nsites, "d2h_bytes_per_step": 16 * R,
+                    "sweeps_per_step": args.e2e_sweeps, "at_1_sweep_per_step": e2e[1],
+                    "note": "C-ABI: upload every replica, flip sweeps + pair sweeps, exact sums back"},
+            "gpu_launches": nl, "roofline": roof}
+    if not args.no_cpu:
+        from oracle import refarm
+        if refarm.available():
+            f = refarm.time_mcstep("latgas", 256, 1.0, 200000, 1)[0]
+            mv = refarm.time_mcstep("latgas_move", 64, 1.0, 20000, 1)[0]
+            line["cpu_baseline"] = {"value": f, "unit": "attempts/s", "cores": 1, "kind": "reference",
+                                    "sample": "2e5 MCstep calls on examples/latgas.py latticegas (flip), 256x256, one core",
+                                    "flip_or_move": {"value": mv, "sample": "2e4 MCstep calls on examples/latgas_move.py (flip or "
+                                                                            "non-local move, O(N) per trial), 64x64, one core"}}
+    print(json.dumps(line), flush=True)
+
+
+def run_discs(args):
+    """BASELINE config 5 (re-interpreted, SURVEY.md section 8 notes): batched independent hard-disc replicas of the
+    shipped system (20 discs, L = 1, r = 1/14, maxstep = r/2), split evenly over the GPUs of the job."""
+    rank, local_rank, world = dist_env()
+    grp = Group(local_rank, world)
+    import numpy as np
+    from py_mc_b200.hardcore import DiscBatch
+    R = args.disc_replicas // world
+    b = DiscBatch(R, 1.0, 20, 1.0 / 14.0, 1.0 / 28.0, isotropic=False, seed=SEED, device=local_rank, replica_offset=rank * R)
+    per = args.disc_trials
+    sampler = ClockSampler(local_rank).start()
+    b._d.timed_run(per)
+    grp.barrier()
+    ms = [b._d.timed_run(per) for _ in range(max(3, args.steps // 10))]
+    ms_med = grp.max(sorted(ms)[len(ms) // 2])
+    clocks = sampler.stop()
+    ok = not b.any_overlap().any()
+    # end to end: coordinates in, trials, coordinates and g(r) counts out
+    t0 = time.perf_counter()
+    co = [b._d.download(r) for r in range(4)]
+    for r in range(min(R, 256)):
+        b._d.upload(r, co[r % 4])
+    b._d.run(per)
+    b._d.observe(0.01, 49)
+    e2e = grp.max(time.perf_counter() - t0)
+    if rank == 0:
+        line = {"metric": "hard-disc move attempts/s", "value": world * R * per / (ms_med * 1e-3), "unit": "attempts/s", "n_gpus": world,
+                "steps": len(ms), "warmup": 1, "ms_per_step": ms_med, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": headline_config(args, world),
+                "workload_detail": {"replicas_per_gpu": R, "trials_per_launch": per, "acceptance": float(b.acceptance().mean())},
+                "parity": "ok" if ok else "FAILED", "clocks": clocks, "gpu_launches": len(ms),
+                "e2e": {"value": world * R * per / e2e, "unit": "attempts/s", "h2d_bytes_per_step": 320 * min(R, 256),
+                        "d2h_bytes_per_step": 4 * 320 + R * (4 + 49 * 8), "note": "upload coordinates, one launch of trials, overlap flags and g(r) counts back"},
+                "roofline": {"bound": "latency", "achieved": None, "peak": None, "unit": "GB/s", "frac": None, "traffic": None,
+                             "note": "320 B of state per replica live in registers: no HBM roof; one warp per replica, float64 "
+                                     "with explicit rounding; issue-slot utilisation in profiles/README.md"}}
+        if not args.no_cpu:
+            from oracle import refarm
+            if refarm.available():
+                v = refarm.time_mcstep("hc2d", 0, 1.0, 50000, 1)[0]
+                line["cpu_baseline"] = {"value": v, "unit": "attempts/s", "cores": 1, "kind": "reference",
+                                        "sample": "5e4 MCstep calls on examples/2D_hardcore HC_2D (20 discs), one core"}
+        print(json.dumps(line), flush=True)
+    grp.close()
+
+
+def run_slab(args):
+    """Strong scaling of ONE 16384 x 16384 lattice split by rows over the GPUs (SURVEY row f4): halo rows are
+    stored into the neighbours' memory by the sweep kernel itself (CUDA IPC peer mappings), neighbour barrier inside
+    the kernel, no NCCL in the timed region."""
+    rank, local_rank, world = dist_env()
+    grp = Group(local_rank, world)
+    from py_mc_b200 import _cabi
+    from py_mc_b200.ising2D import ising2D
+    from py_mc_b200.slab import SlabLattice
+    L = args.L
+    sl = SlabLattice(_cabi.MODEL_ISING, L, L, SEED, grp.dist, device=local_rank)
+    sl.init_random()
+    sl.set_accept_tables(ising2D(-1.0)._pmc_thresholds(TC)[None, :])
+    sl.sweep(args.warmup)
+    sampler = ClockSampler(local_rank).start()
+    ms, rep = timed_repeats(grp, lambda: sl.sweep(args.steps), sl.lat.synchronize, sl.lat.timer_start, sl.lat.timer_stop)
+    clocks = sampler.stop()
+    sl.check()
+    b, m = sl.observables()
+    if rank == 0:
+        nsites = L * L
+        print(json.dumps({
+            "metric": METRIC, "value": nsites * args.steps / (ms * 1e-3), "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "repeats": rep, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": headline_config(args, world),
+            "workload_detail": {"rows_per_gpu": L // world, "bond_sum": b, "magnetisation": m,
+                                "parallelism": "row slabs; halo rows stored into peer memory by the sweep kernel, neighbour "
+                                               "barrier inside the kernel, no NCCL in the timed region"},
+            "clocks": clocks, "gpu_launches": args.steps,
+            "roofline": roofline_block("sweep_fused_i8_kernel", 2.0 * nsites / world, ms / args.steps, False),
+        }), flush=True)
+    grp.close()
+
+
+def run_single(args):
+    import numpy as np
+    rank, local_rank, world = dist_env()
+    grp = Group(local_rank, world)
+    from py_mc_b200 import _cabi
+    from py_mc_b200.ising2D import ising2D
+    L = args.L
+    layout = _cabi.LAYOUT_BITS if args.layout == "bits" else _cabi.LAYOUT_INT8
+    thr = ising2D(-1.0)._pmc_thresholds(args.kT)[None, :]
+    nsites = L * L
+    K = args.steps
+
+    def make(lay, kernel=None):
+        lat = _cabi.Lattices(_cabi.MODEL_ISING, L, L, nreplicas=1, ntemps=1, seed=SEED, layout=lay, device=local_rank,
+                             replica_offset=rank, nreplicas_global=world, kernel=KERNELS[args.kernel] if kernel is None else kernel)
+        lat.init_random()
+        lat.set_accept_tables(thr)
+        return lat
+
+    def timed(lat, one_block):
+        lat.sweep(args.warmup)
+        return timed_repeats(grp, one_block, lat.synchronize, lat.timer_start, lat.timer_stop)
+
+    lat = make(layout)
+    sampler = ClockSampler(local_rank).start()
+    ms, repeats = timed(lat, lambda: lat.sweep(K))
+    clocks = sampler.stop()
+    value = world * nsites * K / (ms * 1e-3)
+
+    # end to end through the C ABI with HOST buffers: upload, sweeps, download, exact sums -- every step
+    host = _cabi.pinned_empty((L, L), np.int8)
+    lat.download(0, out=host)
+    e2e = {}
+    for spp in sorted(set([1, args.e2e_sweeps])):
+        reps = 3
+        lat.upload(0, host)
+        lat.sweep(spp)
+        lat.synchronize()
+        grp.barrier()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            lat.upload(0, host)
+            lat.sweep(spp)
+            lat.download(0, out=host)
+            lat.tracked()
+        e2e[spp] = world * nsites * spp * reps / grp.max(time.perf_counter() - t0)
+
+    bytes_per_site = 1.0 if layout == _cabi.LAYOUT_INT8 else 0.125
+    lps, kname = lat.sweep_kernel_info()
+    on_chip = kname in ("persistent_kernel", "pbatch_kernel", "resident_kernel")
+    nlaunch = (K + 4095) // 4096 if on_chip else lps * K
+    roof = roofline_block(kname, 2.0 * bytes_per_site * nsites * K / nlaunch, ms / nlaunch, on_chip)
+
+    extra = {}
+    if not args.no_extras:
+        lat.close()
+        if args.also_bits and layout == _cabi.LAYOUT_INT8:
+            try:  # an extra, never allowed to take the headline line down with it
+                lat2 = make(_cabi.LAYOUT_BITS)
+                ms2, _ = timed(lat2, lambda: lat2.sweep(K))
+                extra["bitpacked"] = {"value": world * nsites * K / (ms2 * 1e-3), "unit": UNIT, "ms_per_step": ms2 / K,
+                                      "kernel": lat2.sweep_kernel_info()[1],
+                                      "note": "same workload on the 1-bit/site layout (32 MiB)"}
+                lat2.close()
+            except Exception as exc:
+                extra["bitpacked"] = {"error": repr(exc)}
+        try:  # the per-sweep kernel on the same workload (one launch per sweep, 2 B/attempt of DRAM)
+            lat3 = make(layout)
+            n3 = max(50, K)
+            ms3, _ = timed(lat3, lambda: [lat3.sweep(1) for _ in range(n3)])  # single-sweep calls: the fused kernel
+            extra["one_sweep_per_launch"] = {"value": world * nsites * n3 / (ms3 * 1e-3), "unit": UNIT, "ms_per_step": ms3 / n3,
+                                             "kernel": "sweep_fused_i8_kernel" if layout == _cabi.LAYOUT_INT8 else "sweep_bits_rows_kernel",
+                                             "roofline_frac": 2.0 * bytes_per_site * nsites / (ms3 / n3 * 1e-3) / 1e9 / measured_peak_hbm()[0]}
+            lat3.close()
+        except Exception as exc:
+            extra["one_sweep_per_launch"] = {"error": repr(exc)}
+        if world == 1:
+            try:  # BASELINE configs[2] on this one GPU: 256 x 1024^2, exchange every rx_every sweeps
+                rx = rx_measure(args, grp, 0, local_rank, args.rx_replicas, args.rx_replicas, False, args.kernel)
+                rx["lat"].close()
+                extra["rx"] = {"value": rx["value"], "unit": UNIT, "ms_per_step": rx["ms_per_step"], "repeats": rx["repeats"],
+                               "kernel": rx["kernel"], "exchange_us": rx["exchange_us"], "parity": rx["parity"],
+                               "rx_sweeps_per_s": rx["rx_sweeps_per_s"], "exchange_acceptance": rx["acceptance"],
+                               "workload": "ising2d_replica_exchange_%d_replicas_of_%dx%d_kT=%.2f..%.2f_exchange_every_%d_sweeps"
+                                           % (args.rx_replicas, args.rx_L, args.rx_L, args.rx_kT_lo, args.rx_kT_hi, args.rx_every)}
+            except Exception as exc:
+                extra["rx"] = {"error": repr(exc)}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": args.warmup, "repeats": repeats,
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u8" if layout == _cabi.LAYOUT_INT8 else "u64 (1 bit/site)", "data": "synthetic",
+            "config": headline_config(args, world),
+            "workload_detail": {"step": "one full sweep (both colours)",
+                                "l2": ("no cache is relied upon: the lattice (%d MiB in HBM) is loaded once per launch, stays in the shared "
+                                       "memory of the SMs as bits for the %d sweeps of the launch and is stored once"
+                                       % (int(nsites * bytes_per_site) >> 20, K)) if on_chip else
+                                      "working set %d MiB %s L2" % (int(nsites * bytes_per_site) >> 20,
+                                                                    "exceeds" if nsites * bytes_per_site > 126e6 else "fits in"),
+                                "parallelism": "replicas only" if world > 1 else "single GPU"},
+            "clocks": clocks,
+            "e2e": {"value": e2e[args.e2e_sweeps], "unit": UNIT, "h2d_bytes_per_step": nsites, "d2h_bytes_per_step": nsites + 16,
+                    "sweeps_per_step": args.e2e_sweeps, "at_1_sweep_per_step": e2e[1],
+                    "note": "C-ABI upload(pinned host int8) + sweeps + download(host int8) + exact sums per step"},
+            "gpu_launches": nlaunch * repeats, "roofline": roof,
+        }
+        line.update(extra)
+        if world == 1 and not args.no_cpu:
+            line["cpu_baseline"] = cpu_baseline()
+        print(json.dumps(line), flush=True)
+    grp.close()
+
+
+def run_ours(args):
+    _, _, world = dist_env()
+    wl = pick_workload(args, world)
+    if wl == "slab":
+        return run_slab(args)
+    if wl == "latgas":
+        return run_latgas(args)
+    if wl == "discs":
+        return run_discs(args)
+    if wl == "rx":
+        if args.workload == "auto" and not args.rx_replicas_total:
+            args.rx_replicas_total = 256  # BASELINE configs[2]: 256 replicas in total
+        return run_rx(args)
+    return run_single(args)
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=3000)
-    ap.add_argument("--warmup", type=int, default=200)
+    ap.add_argument("--steps", type=int, default=1000)
+    ap.add_argument("--warmup", type=int, default=100)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--layout", default="int8", choices=["int8", "bits"])
     ap.add_argument("--L", type=int, default=16384)
@@ -627,22 +826,23 @@ def main():
     ap.add_argument("--e2e-sweeps", type=int, default=64)
     ap.add_argument("--also-bits", action="store_true", default=True)
     ap.add_argument("--no-also-bits", dest="also_bits", action="store_false")
+    ap.add_argument("--no-extras", action="store_true", help="headline only (profiling runs)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--workload", default="auto", choices=["auto", "ising16k", "rx", "latgas", "discs", "slab"])
     ap.add_argument("--lg-replicas", type=int, default=512)
     ap.add_argument("--lg-L", type=int, default=256)
     ap.add_argument("--disc-replicas", type=int, default=8192)
     ap.add_argument("--disc-trials", type=int, default=2000)
-    ap.add_argument("--rx-replicas", type=int, default=256, help="replicas per GPU (weak scaling)")
+    ap.add_argument("--rx-replicas", type=int, default=256, help="replicas per GPU (weak scaling / the rx block at N = 1)")
+    ap.add_argument("--rx-replicas-total", type=int, default=0, help="replicas over all GPUs (strong scaling); default at "
+                    "N > 1: 256, BASELINE configs[2]")
     ap.add_argument("--rx-L", type=int, default=1024)
     ap.add_argument("--rx-every", type=int, default=10, help="sweeps between exchanges")
-    ap.add_argument("--kernel", default="auto", choices=["auto", "generic", "two_pass", "resident"],
-                    help="sweep kernel of the handle (PYMC_KERNEL_*); resident = one block keeps one replica in shared memory")
+    ap.add_argument("--kernel", default="auto", choices=sorted(KERNELS), help="sweep kernel of the handle (PYMC_KERNEL_*)")
     ap.add_argument("--rx-model", default="ising", choices=["ising", "hardcore"])
     ap.add_argument("--rx-mu", type=float, default=1.0, help="chemical potential of the hard-core lattice gas")
     ap.add_argument("--rx-kT-lo", type=float, default=2.0)
     ap.add_argument("--rx-kT-hi", type=float, default=2.6)
-    ap.add_argument("--e2e-full", action="store_true", help="rx e2e uploads a distinct host image per replica")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

@@ -65,7 +65,7 @@ __device__ __forceinline__ void count_masks(uint64_t a0, uint64_t a1, uint64_t a
 template <int MAXH>
 __device__ __forceinline__ uint64_t decide_hard(const uint64_t (&hm)[MAXH], const uint32_t (&ht)[MAXH],
                                                 uint64_t always, uint64_t valid, uint32_t word_idx,
-                                                uint32_t replica, uint64_t step, uint32_t domain, PhiloxKey key) {
+                                                uint32_t replica, uint64_t step, uint32_t domain, const PhiloxKey &key) {
     uint64_t needed = 0;
 #pragma unroll
     for (int k = 0; k < MAXH; ++k) needed |= hm[k];
@@ -211,7 +211,7 @@ struct Plan<MODEL_LATGAS> {
 template <int MODEL>
 __device__ __forceinline__ uint64_t update_word(uint64_t S, uint64_t U, uint64_t D, uint64_t C, uint64_t Sd,
                                                 uint64_t valid, const Plan<MODEL> &plan, uint32_t word_idx,
-                                                uint32_t replica, uint64_t step, PhiloxKey key, int &dB, int &dS) {
+                                                uint32_t replica, uint64_t step, const PhiloxKey &key, int &dB, int &dS) {
     if constexpr (MODEL == MODEL_ISING) {
         uint64_t c0, c1, c2;
         const uint64_t nm = plan.notmask;

@@ -60,7 +60,7 @@ __device__ __forceinline__ void add3(uint64_t x, uint64_t y, uint64_t z, uint64_
 // Returns the mask of accepted exchanges; dB = change of the bond count.
 __device__ __forceinline__ uint64_t pair_update(uint64_t S, uint64_t Bw, uint64_t A0, uint64_t A1, uint64_t B0,
                                                 uint64_t B1, uint64_t active, const PairPlan &plan, uint32_t word_idx,
-                                                uint32_t replica, uint64_t step, PhiloxKey key, int &dB) {
+                                                uint32_t replica, uint64_t step, const PhiloxKey &key, int &dB) {
     const uint64_t movable = (S ^ Bw) & active;
     // source = where the particle sits.  P - Q is the quantity whose positive values are the hard moves.
     const uint64_t sel = S ^ plan.notmask;  // neg orientation: P = source count, Q = destination count

@@ -150,11 +150,12 @@ struct PBCtx {
     uint64_t *xbuf;              // [2 colours][nslots][nw] exchange buffer (global)
     unsigned int *flags;         // [B] number of export events of each block (1 after the load)
     unsigned int *cnt;           // shared: export warps that have finished, summed over all passes
+    unsigned int *abort_word;    // global: set when a wait has timed out
     int *err;
     int lenX, nw, nw_shift;      // nw_shift >= 0: nw is that power of two
     int nslots, b;
     uint32_t rep_offset;
-    PhiloxKey key;
+    const PhiloxKey *key;        // round keys (in the kernel parameters: constant memory)
 };
 
 struct SmemRow {
@@ -170,21 +171,44 @@ __device__ __forceinline__ uint64_t pb_ldcg(const uint64_t *p) {
 #endif
 }
 
-// Wait until block `blk` has published `need` export events.  Bounded: a time-out raises *err.
-__device__ __forceinline__ void pb_wait(const unsigned int *flag, unsigned int need, int *err) {
+// Acquire / release at GPU scope without the full (sequentially consistent) __threadfence.
+__device__ __forceinline__ unsigned int pb_ld_acquire(const unsigned int *p) {
 #ifdef __CUDA_ARCH__
-    if (*(volatile const unsigned int *)flag < need && !*(volatile int *)err) {  // after one time-out nobody waits again
-        const long long t0 = clock64();
-        while (*(volatile const unsigned int *)flag < need) {
+    unsigned int v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+#else
+    return *p;
+#endif
+}
+__device__ __forceinline__ void pb_fence() {
+#ifdef __CUDA_ARCH__
+    asm volatile("fence.acq_rel.gpu;" ::: "memory");
+#endif
+}
+
+// Wait until block `blk` has published `need` export events.  The poll backs off (many threads of many blocks may
+// watch the same few cache lines) and is bounded: after about two seconds *err is raised, and so is the abort word
+// in device memory that lets every other waiter of the launch give up at once.
+__device__ __forceinline__ void pb_wait(const unsigned int *flag, unsigned int need, int *err, unsigned int *abort_word) {
+#ifdef __CUDA_ARCH__
+    if (pb_ld_acquire(flag) >= need) return;
+    const long long t0 = clock64();
+    unsigned int spins = 0;
+    while (pb_ld_acquire(flag) < need) {
+        __nanosleep(40);
+        if ((++spins & 1023u) == 0) {
+            if (*(volatile unsigned int *)abort_word) return;
             if (clock64() - t0 > 4000000000LL) {
+                *(volatile unsigned int *)abort_word = 1u;
                 *err = 1;
-                break;
+                return;
             }
         }
     }
-    __threadfence();  // what that block wrote before raising its flag is visible to the loads that follow
 #else
     if (*flag < need) *err = 1;  // the host drives the blocks in lock step: the flag must be there already
+    (void)abort_word;
 #endif
 }
 
@@ -236,71 +260,144 @@ __device__ __forceinline__ void pb_neighbours(const PBGeom &g, int lenX, int lr,
 __device__ __forceinline__ uint64_t pb_row_word(const PBGeom &g, const PBCtx &c, int oc, int row, int w, unsigned int need) {
     if (row >= 0) return c.s[((size_t)oc * g.nrows + row) * c.nw + w];
     const int k = -1 - row;
-    pb_wait(c.flags + g.imp_blk[k], need, c.err);
+    pb_wait(c.flags + g.imp_blk[k], need, c.err, c.abort_word);
     return pb_ldcg(c.xbuf + ((size_t)oc * c.nslots + g.imp_slot[k]) * c.nw + w);
 }
 
 // One colour pass of one thread.  `events` = export events every block has completed before this pass (1 + number
 // of passes since the load).  Every thread of a warp must call this together (update_word votes).
+//
+// Items are taken export rows first, then the other rows in their natural order: ordinal o = base + t, ordinal row
+// o / nw, column o % nw.  The first round (ordinals 0 .. T-1) holds all items of the export rows (the host makes T at
+// least that large): it takes the general path -- rows of other blocks from the exchange buffer, new words to the
+// exchange buffer, flag.  Every later round touches only rows whose neighbours are all in this block, and a thread
+// walks down the rows with a fixed stride: its row, replica segment and plan are carried from one item to the next
+// instead of being recomputed.  (Measured alternatives, slower: recomputing the row from the ordinal per item; the
+// natural order with the export items pulled forward by their owners -- with few words per row those owners' warps do
+// a whole extra item.)
 template <int MODEL>
 __device__ __forceinline__ void pb_pass(const PBGeom &g, const PBCtx &c, int colour, uint64_t step, unsigned int events, int t,
                                         int T) {
-    const int oc = colour ^ 1, items = g.nrows * c.nw, nexport = g.nxrow * c.nw;
+    // block-uniform values out of shared memory once: the stores of the loop could alias them for all the compiler knows
+    const int nrows = g.nrows, nxrow = g.nxrow, nseg = g.nseg, nw = c.nw, lenX = c.lenX;
+    const int oc = colour ^ 1, items = nrows * nw, nexport = nxrow * nw;
+    uint64_t *const sc = c.s + (size_t)colour * items;
+    const uint64_t *const so = c.s + (size_t)oc * items;
+    const uint32_t rep0 = c.rep_offset + (uint32_t)g.rep_first;
     Plan<MODEL> plan;
-    int cur = -1;
-#pragma unroll 1
-    for (int base = 0; base < items; base += T) {
-        const bool on = base + t < items;
-        const int o = on ? base + t : items - 1;
+    int cur;
+
+    // ---- first round: general path -----------------------------------------------------------------------
+    {
+        const bool on = t < items;
+        const int o = on ? t : items - 1;
         int lr, w, seg, i, up, dn;
         pb_locate(g, c, o, true, lr, w, seg, i);
-        pb_neighbours(g, c.lenX, lr, i, up, dn);
-        if (seg != cur) {
-            plan.init(SmemRow{c.splan + seg * PLAN_WORDS});
-            cur = seg;
-        }
-        uint64_t *row_c = c.s + ((size_t)colour * g.nrows + lr) * c.nw;
-        const uint64_t *row_o = c.s + ((size_t)oc * g.nrows + lr) * c.nw;
-        const uint64_t S = row_c[w], C = row_o[w];
+        pb_neighbours(g, lenX, lr, i, up, dn);
+        plan.init(SmemRow{c.splan + seg * PLAN_WORDS});
+        cur = seg;
+        const int idx = lr * nw + w;
+        const uint64_t S = sc[idx], C = so[idx];
         uint64_t Sd;
         if ((i + colour) & 1)
-            Sd = (C >> 1) | (row_o[w == c.nw - 1 ? 0 : w + 1] << 63);
+            Sd = (C >> 1) | (so[w == nw - 1 ? idx - w : idx + 1] << 63);
         else
-            Sd = (C << 1) | (row_o[w == 0 ? c.nw - 1 : w - 1] >> 63);
+            Sd = (C << 1) | (so[w == 0 ? idx + nw - 1 : idx - 1] >> 63);
         const uint64_t U = pb_row_word(g, c, oc, up, w, events), D = pb_row_word(g, c, oc, dn, w, events);
         int dB, dS;  // unused: the sums are recomputed where they are needed (pb_reduce)
-        const uint64_t Snew = update_word<MODEL>(S, U, D, C, Sd, on ? ~0ull : 0ull, plan, (uint32_t)(i * c.nw + w),
-                                                 c.rep_offset + (uint32_t)(g.rep_first + seg), step, c.key, dB, dS);
+        const uint64_t Snew = update_word<MODEL>(S, U, D, C, Sd, on ? ~0ull : 0ull, plan, (uint32_t)(i * nw + w),
+                                                 rep0 + (uint32_t)seg, step, *c.key, dB, dS);
         if (on) {
-            row_c[w] = Snew;
-            if (o < nexport) {
+            sc[idx] = Snew;
+            if (o < nexport)
                 for (int e = 0; e < g.nexp; ++e)
-                    if (g.exp_row[e] == lr) c.xbuf[((size_t)colour * c.nslots + g.exp_slot[e]) * c.nw + w] = Snew;
-#ifdef __CUDA_ARCH__
-                __threadfence();
-#endif
-            }
+                    if (g.exp_row[e] == lr) c.xbuf[((size_t)colour * c.nslots + g.exp_slot[e]) * nw + w] = Snew;
         }
-        if (base == 0 && nexport > 0 && (t - t % PMC_WARP) < nexport) {
-            // this warp held export items: once all such warps are through, the block's flag goes up
+        if (nexport > 0 && (t - t % PMC_WARP) < nexport) {
+            // This warp held export items: once all such warps are through, the block's flag goes up.  Ordering: the
+            // lanes' stores to the exchange buffer -> __syncwarp -> lane 0: fence, count (release pattern on the shared
+            // counter); the last warp: count, fence (acquire pattern), flag.  Readers load the flag with acquire.
 #ifdef __CUDA_ARCH__
             __syncwarp();
 #endif
             if (t % PMC_WARP == 0) {
                 const unsigned int nwarps = (unsigned int)((nexport + PMC_WARP - 1) / PMC_WARP);
+                pb_fence();
 #ifdef __CUDA_ARCH__
                 const unsigned int arrived = atomicAdd(c.cnt, 1u) + 1u;
 #else
                 const unsigned int arrived = ++*c.cnt;
 #endif
                 if (arrived == events * nwarps) {  // cnt counts over all passes; the load was event 1
+                    pb_fence();
 #ifdef __CUDA_ARCH__
-                    __threadfence();
                     *(volatile unsigned int *)(c.flags + c.b) = events + 1u;
 #else
                     c.flags[c.b] = events + 1u;
 #endif
                 }
+            }
+        }
+    }
+    if (T >= items) return;
+
+    // ---- later rounds: all neighbours local, incremental indexing -----------------------------------------------
+    const bool strided = T % nw == 0;  // then a thread keeps its word column and moves down T / nw ordinal rows per round
+    const int dr = strided ? T / nw : 0;
+    const int wrap = (lenX - 1) * nw;  // from row 0 of a replica to its last row
+    int lr, w, left, right, xk = 0, xn;  // xn: the next export row at or below which lr has not yet been moved past
+    {
+        const int ro = (T + t) / nw;
+        w = (T + t) - ro * nw;
+        lr = ro - nxrow;  // rank among the rows that are not export rows -> row: skip over the export rows
+        while (xk < nxrow && lr >= g.xrow[xk]) {
+            ++lr;
+            ++xk;
+        }
+        xn = xk < nxrow ? g.xrow[xk] : 0x7FFFFFFF;
+        left = w == 0 ? nw - 1 : -1;
+        right = w == nw - 1 ? 1 - nw : 1;
+    }
+    int seg = 0, seg_end = nseg > 1 ? c.segstart[1] : 0x7FFFFFFF, ioff = c.segoff[0];
+#pragma unroll 1
+    for (int base = T; base < items; base += T) {  // whole warps stay in the loop: the update votes
+        const bool on = base + t < items;
+        if (!strided && on) {
+            const int ro = (base + t) / nw;
+            w = (base + t) - ro * nw;
+            left = w == 0 ? nw - 1 : -1;
+            right = w == nw - 1 ? 1 - nw : 1;
+            lr = ro - nxrow;
+            for (xk = 0; xk < nxrow && lr >= g.xrow[xk]; ++xk) ++lr;
+        }
+        while (on && lr >= seg_end) {  // next replica (rows only ever increase within a thread)
+            ++seg;
+            ioff = c.segoff[seg];
+            seg_end = seg + 1 < nseg ? c.segstart[seg + 1] : 0x7FFFFFFF;
+        }
+        if (on && seg != cur) {
+            plan.init(SmemRow{c.splan + seg * PLAN_WORDS});
+            cur = seg;
+        }
+        const int i = lr + ioff;
+        const int o = on ? lr * nw + w : 0;  // idle lanes of the last round read word 0 of the block: always there
+        const int ou = !on ? 0 : (i == 0 ? o + wrap : o - nw), od = !on ? 0 : (i == lenX - 1 ? o - wrap : o + nw);
+        const uint64_t S = sc[o], C = so[o];
+        uint64_t Sd;
+        if ((i + colour) & 1)
+            Sd = (C >> 1) | (so[on ? o + right : 0] << 63);
+        else
+            Sd = (C << 1) | (so[on ? o + left : 0] >> 63);
+        int dB, dS;
+        const uint64_t Snew = update_word<MODEL>(S, so[ou], so[od], C, Sd, on ? ~0ull : 0ull, plan, (uint32_t)(i * nw + w),
+                                                 rep0 + (uint32_t)seg, step, *c.key, dB, dS);
+        if (on) sc[o] = Snew;
+        if (strided) {
+            lr += dr;
+            while (lr >= xn) {  // moved past an export row: those were done in the first round
+                ++lr;
+                ++xk;
+                xn = xk < nxrow ? g.xrow[xk] : 0x7FFFFFFF;
             }
         }
     }
@@ -317,15 +414,19 @@ __device__ __forceinline__ void pb_publish_loaded(const PBGeom &g, const PBCtx &
 }
 
 // Exact bond sum and second observable (magnetisation / particle number) of the rows of this block, per replica,
-// added into acc[seg][2] (shared memory, zeroed by the caller).  Same definition as reduce_kernel: every word
-// contributes its bonds to the row above and to the site on its left.  Warps take contiguous runs of items so that
-// a warp changes replica at most nseg - 1 times.  `events` as in pb_pass (the remote rows must be current).
+// added into acc[seg][2] (shared memory, zeroed by the caller).  Every bond joins a site of colour 0 and a site of
+// colour 1, so one walk over the words of colour 0 with their four neighbour words counts every bond once (the same
+// integers as reduce_kernel, which walks both colours with two neighbours each); the same-row neighbour word is also
+// the only visit of that colour-1 word, so the second observable is taken from both.  Warps take contiguous runs of
+// items so that a warp changes replica at most nseg - 1 times.  `events` as in pb_pass: the rows of colour 1 that
+// other blocks hold must be those of the last pass.
 template <int MODEL>
 __device__ __forceinline__ void pb_reduce(const PBGeom &g, const PBCtx &c, unsigned int events, long long *acc, int t, int T) {
-    const int items = g.nrows * c.nw;
+    const int nw = c.nw, items = g.nrows * nw;
     const int nwarps = T / PMC_WARP, wid = t / PMC_WARP, lane = t % PMC_WARP;
     const int per_warp = ((items + nwarps - 1) / nwarps + PMC_WARP - 1) / PMC_WARP * PMC_WARP;
     const int lo = wid * per_warp, hi = lo + per_warp < items ? lo + per_warp : items;
+    const uint64_t *const s0 = c.s, *const s1 = c.s + (size_t)items;
     int aB = 0, aS = 0, cur = 0;
     auto flush = [&]() {
 #ifdef __CUDA_ARCH__
@@ -340,51 +441,51 @@ __device__ __forceinline__ void pb_reduce(const PBGeom &g, const PBCtx &c, unsig
 #endif
         aB = aS = 0;
     };
-    for (int colour = 0; colour < 2; ++colour) {
-        const int oc = colour ^ 1;
 #pragma unroll 1
-        for (int base = lo; base < hi; base += PMC_WARP) {
-            const bool on = base + lane < hi;
-            const int o = on ? base + lane : hi - 1;
-            int lr, w, seg, i, up, dn;
-            pb_locate(g, c, o, false, lr, w, seg, i);
-            pb_neighbours(g, c.lenX, lr, i, up, dn);
-            int dB = 0, dS = 0;
-            if (on) {
-                const uint64_t *row_o = c.s + ((size_t)oc * g.nrows + lr) * c.nw;
-                const uint64_t S = c.s[((size_t)colour * g.nrows + lr) * c.nw + w], C = row_o[w];
-                const uint64_t U = pb_row_word(g, c, oc, up, w, events);
-                // the site at column y-1: same k of the other colour, or k-1
-                const uint64_t Lw = ((i + colour) & 1) ? C : ((C << 1) | (row_o[w == 0 ? c.nw - 1 : w - 1] >> 63));
-                if (MODEL == MODEL_ISING) {
-                    dB = 128 - 2 * (__popcll(S ^ U) + __popcll(S ^ Lw));
-                    dS = 2 * __popcll(S) - 64;
-                } else {
-                    dB = __popcll(S & U) + __popcll(S & Lw);
-                    dS = __popcll(S);
-                }
+    for (int base = lo; base < hi; base += PMC_WARP) {
+        const bool on = base + lane < hi;
+        const int o = on ? base + lane : hi - 1;
+        int lr, w, seg, i, up, dn;
+        pb_locate(g, c, o, false, lr, w, seg, i);
+        pb_neighbours(g, c.lenX, lr, i, up, dn);
+        int dB = 0, dS = 0;
+        if (on) {
+            const int idx = lr * nw + w;
+            const uint64_t S = s0[idx], C = s1[idx];
+            const uint64_t U = pb_row_word(g, c, 1, up, w, events), D = pb_row_word(g, c, 1, dn, w, events);
+            uint64_t Sd;  // the other same-row neighbour: site k+1 (rows where colour 0 starts at column 1) or k-1
+            if (i & 1)
+                Sd = (C >> 1) | (s1[w == nw - 1 ? idx - w : idx + 1] << 63);
+            else
+                Sd = (C << 1) | (s1[w == 0 ? idx + nw - 1 : idx - 1] >> 63);
+            if (MODEL == MODEL_ISING) {
+                dB = 256 - 2 * (__popcll(S ^ U) + __popcll(S ^ D) + __popcll(S ^ C) + __popcll(S ^ Sd));
+                dS = 2 * (__popcll(S) + __popcll(C)) - 128;
+            } else {
+                dB = __popcll(S & U) + __popcll(S & D) + __popcll(S & C) + __popcll(S & Sd);
+                dS = __popcll(S) + __popcll(C);
             }
+        }
 #ifdef __CUDA_ARCH__
-            const int seg0 = __shfl_sync(0xFFFFFFFFu, seg, 0);
-            const bool uniform = __all_sync(0xFFFFFFFFu, seg == seg0);
+        const int seg0 = __shfl_sync(0xFFFFFFFFu, seg, 0);
+        const bool uniform = __all_sync(0xFFFFFFFFu, seg == seg0);
 #else
-            const int seg0 = seg;
-            const bool uniform = true;
+        const int seg0 = seg;
+        const bool uniform = true;
 #endif
-            if (uniform) {
-                if (seg0 != cur) {
-                    flush();
-                    cur = seg0;
-                }
-                aB += dB;
-                aS += dS;
-            } else {  // the 32 items straddle a replica boundary: every lane adds its own
+        if (uniform) {
+            if (seg0 != cur) {
                 flush();
-#ifdef __CUDA_ARCH__
-                if (dB) atomicAdd((unsigned long long *)&acc[2 * seg], (unsigned long long)(long long)dB);
-                if (dS) atomicAdd((unsigned long long *)&acc[2 * seg + 1], (unsigned long long)(long long)dS);
-#endif
+                cur = seg0;
             }
+            aB += dB;
+            aS += dS;
+        } else {  // the 32 items straddle a replica boundary: every lane adds its own
+            flush();
+#ifdef __CUDA_ARCH__
+            if (dB) atomicAdd((unsigned long long *)&acc[2 * seg], (unsigned long long)(long long)dB);
+            if (dS) atomicAdd((unsigned long long *)&acc[2 * seg + 1], (unsigned long long)(long long)dS);
+#endif
         }
     }
     flush();
@@ -429,7 +530,7 @@ struct PBatchArgs {
     int scheme0;                   // XCscheme of the first exchange of this launch (alternates from there)
     unsigned long long round0;     // the handle's exchange round at entry
     unsigned int *flags;           // [B] zeroed by the host before the launch
-    unsigned int *bar;             // grid barrier arrivals, zeroed by the host before the launch
+    unsigned int *bar;             // [2] grid barrier arrivals and the abort word, zeroed by the host before the launch
     int *err;
     uint64_t *xbuf;                // [2][nslots][nw]
     long long *part;               // [2][B][PB_MAXSEG][2]
@@ -443,18 +544,25 @@ struct PBatchArgs {
 };
 
 __device__ __forceinline__ void pb_grid_barrier(unsigned int *counter, unsigned int target, int *err) {
-    __threadfence();
-    __syncthreads();
+    __syncthreads();  // this block's stores before thread 0's fence
     if (threadIdx.x == 0) {
+        pb_fence();
         atomicAdd(counter, 1u);
-        const long long t0 = clock64();
-        while (*(volatile unsigned int *)counter < target) {
-            if (clock64() - t0 > 4000000000LL || (((clock64() - t0) & 0xFFFFF) == 0 && *(volatile int *)err)) {
-                *err = 1;
-                break;
+        if (pb_ld_acquire(counter) < target) {
+            const long long t0 = clock64();
+            unsigned int spins = 0;
+            while (pb_ld_acquire(counter) < target) {
+                __nanosleep(32);
+                if ((++spins & 1023u) == 0) {
+                    if (*(volatile unsigned int *)(counter + 1)) break;  // somebody has given up: so do I
+                    if (clock64() - t0 > 4000000000LL) {
+                        *(volatile unsigned int *)(counter + 1) = 1u;
+                        *err = 1;
+                        break;
+                    }
+                }
             }
         }
-        __threadfence();
     }
     __syncthreads();
 }
@@ -462,7 +570,7 @@ __device__ __forceinline__ void pb_grid_barrier(unsigned int *counter, unsigned 
 // grid = B blocks (<= number of SMs, cooperative launch: all resident), block = multiple of 32 threads with
 // 4 * nw <= threads, dynamic shared memory = 2 * (largest nrows) * nw * 8 bytes.
 template <int MODEL, int LAYOUT, class LatT>
-__global__ void __launch_bounds__(PB_MAX_THREADS, 1) pbatch_kernel(LatT L, PBatchArgs a) {
+__global__ void __launch_bounds__(PB_MAX_THREADS, 1) pbatch_kernel(const __grid_constant__ LatT L, const __grid_constant__ PBatchArgs a) {
     extern __shared__ __align__(16) uint64_t s_rows[];
     __shared__ uint32_t s_plan[PB_MAXSEG * PLAN_WORDS];
     __shared__ int s_segoff[PB_MAXSEG], s_segstart[PB_MAXSEG], s_T[PB_MAXSEG];
@@ -491,6 +599,7 @@ __global__ void __launch_bounds__(PB_MAX_THREADS, 1) pbatch_kernel(LatT L, PBatc
     c.xbuf = a.xbuf;
     c.flags = a.flags;
     c.cnt = &s_cnt;
+    c.abort_word = a.bar + 1;
     c.err = a.err;
     c.lenX = lenX;
     c.nw = nw;
@@ -498,7 +607,7 @@ __global__ void __launch_bounds__(PB_MAX_THREADS, 1) pbatch_kernel(LatT L, PBatc
     c.nslots = pb_nslots(B, nrep);
     c.b = b;
     c.rep_offset = (uint32_t)L.rep_offset;
-    c.key = L.key;
+    c.key = &L.key;
 
     // ---- load my rows (both colours) ---------------------------------------------------------------------
     for (int colour = 0; colour < 2; ++colour) {
@@ -526,9 +635,11 @@ __global__ void __launch_bounds__(PB_MAX_THREADS, 1) pbatch_kernel(LatT L, PBatc
     };
     load_plans();
     pb_publish_loaded(g, c, t, T);
-    __threadfence();
     __syncthreads();
-    if (t == 0) *(volatile unsigned int *)(a.flags + b) = 1u;
+    if (t == 0) {
+        pb_fence();  // the block's stores to the exchange buffer (ordered before me by the barrier) before the flag
+        *(volatile unsigned int *)(a.flags + b) = 1u;
+    }
 
     unsigned int events = 1, arrivals = 0;
     int scheme = a.scheme0, cur = 0;
@@ -555,11 +666,34 @@ __global__ void __launch_bounds__(PB_MAX_THREADS, 1) pbatch_kernel(LatT L, PBatc
             if (t < 2 * g.nseg) part[(size_t)b * PB_MAXSEG * 2 + t] = s_acc[t];
             arrivals += (unsigned int)B;
             pb_grid_barrier(a.bar, arrivals, a.err);  // every block's sums are in `part`
-            // ---- the pair decisions of Xtrial (py_mc/mc_mpi.py:102-140), identical in every block -------------
+            // ---- the pair decisions of Xtrial (py_mc/mc_mpi.py:102-140) ---------------------------------------------
+            // A decision is a pure function of (pair, round, the two energies): every block works out the pairs its own
+            // replicas are in (it needs their new temperatures), block 0 works out all of them and keeps the books.
             const int nxt = cur ^ 1, R = a.ntemps;
-            const int32_t *t2r = a.T_to_rep[cur];
-            if (b == 0)  // temperatures without a partner this round keep their replica
-                for (int tt = t; tt < R; tt += T) {
+            const int32_t *t2r = a.T_to_rep[cur], *r2t = a.rep_to_T[cur];
+            auto decide = [&](int tl, int &r_lo, int &r_hi) -> bool {  // pair (tl, tl + 1) of temperature indices
+                r_lo = t2r[tl];
+                r_hi = t2r[tl + 1];
+                const double e_lo = pb_energy(part, r_lo - (int)L.rep_offset, B, nrep, lenX, a.c_bond, a.c_second);
+                const double e_hi = pb_energy(part, r_hi - (int)L.rep_offset, B, nrep, lenX, a.c_bond, a.c_second);
+                const double delta = __dmul_rn(__dsub_rn(a.betas[tl + 1], a.betas[tl]), __dsub_rn(e_lo, e_hi));
+                if (delta < 0.0) return true;
+                const uint4 o = philox4x32_10((uint32_t)tl, 0u, (uint32_t)round, ctr3(DOMAIN_RX, 0, round), L.key);
+                return (double)o.x * (1.0 / 4294967296.0) <= exp(-delta);
+            };
+            if (b != 0) {
+                if (t < g.nseg) {
+                    const int r = (int)L.rep_offset + g.rep_first + t, Tc = r2t[r];
+                    const int tl = Tc - (Tc >= scheme ? ((Tc - scheme) & 1) : 0);  // lower index of my pair
+                    int Tn = Tc;
+                    if (Tc >= scheme && tl + 1 < R) {
+                        int r_lo, r_hi;
+                        if (decide(tl, r_lo, r_hi)) Tn = r == r_lo ? tl + 1 : tl;
+                    }
+                    s_T[t] = Tn;
+                }
+            } else {
+                for (int tt = t; tt < R; tt += T) {  // temperatures without a partner this round keep their replica
                     const bool paired = tt >= scheme && (((tt - scheme) & 1) ? true : tt + 1 < R);
                     if (!paired) {
                         const int r = t2r[tt];
@@ -567,25 +701,16 @@ __global__ void __launch_bounds__(PB_MAX_THREADS, 1) pbatch_kernel(LatT L, PBatc
                         a.rep_to_T[nxt][r] = tt;
                     }
                 }
-            if (b == 0)
                 for (int r = t; r < nrep; r += T)
                     a.energies[L.rep_offset + r] = pb_energy(part, r, B, nrep, lenX, a.c_bond, a.c_second);
-            const int g_first = (int)L.rep_offset + g.rep_first;
-            for (int p = t; 2 * p + scheme + 1 < R; p += T) {
-                const int tl = 2 * p + scheme;  // lower temperature index of the pair
-                const int r_lo = t2r[tl], r_hi = t2r[tl + 1];
-                const double e_lo = pb_energy(part, r_lo - (int)L.rep_offset, B, nrep, lenX, a.c_bond, a.c_second);
-                const double e_hi = pb_energy(part, r_hi - (int)L.rep_offset, B, nrep, lenX, a.c_bond, a.c_second);
-                const double delta = __dmul_rn(__dsub_rn(a.betas[tl + 1], a.betas[tl]), __dsub_rn(e_lo, e_hi));
-                bool accept = delta < 0.0;
-                if (!accept) {
-                    const uint4 o = philox4x32_10((uint32_t)tl, 0u, (uint32_t)round, ctr3(DOMAIN_RX, 0, round), L.key);
-                    accept = (double)o.x * (1.0 / 4294967296.0) <= exp(-delta);
-                }
-                const int T_lo = accept ? tl + 1 : tl, T_hi = accept ? tl : tl + 1;  // new temperatures of r_lo, r_hi
-                if (r_lo >= g_first && r_lo < g_first + g.nseg) s_T[r_lo - g_first] = T_lo;
-                if (r_hi >= g_first && r_hi < g_first + g.nseg) s_T[r_hi - g_first] = T_hi;
-                if (b == 0) {
+                const int g_first = (int)L.rep_offset + g.rep_first;
+                for (int p = t; 2 * p + scheme + 1 < R; p += T) {
+                    const int tl = 2 * p + scheme;
+                    int r_lo, r_hi;
+                    const bool accept = decide(tl, r_lo, r_hi);
+                    const int T_lo = accept ? tl + 1 : tl, T_hi = accept ? tl : tl + 1;  // new temperatures of r_lo, r_hi
+                    if (r_lo >= g_first && r_lo < g_first + g.nseg) s_T[r_lo - g_first] = T_lo;
+                    if (r_hi >= g_first && r_hi < g_first + g.nseg) s_T[r_hi - g_first] = T_hi;
                     a.rep_to_T[nxt][r_lo] = T_lo;
                     a.rep_to_T[nxt][r_hi] = T_hi;
                     a.T_to_rep[nxt][T_lo] = r_lo;

@@ -46,7 +46,7 @@ __device__ __forceinline__ uint64_t &persist_word(uint64_t *s, int nrows, int nw
 // One colour pass over the slab.  Every thread of a warp must call this together (update_word votes).
 template <int MODEL>
 __device__ __forceinline__ void persist_pass(uint64_t *s, int nrows, int nw, int r0, int colour, const Plan<MODEL> &plan,
-                                             uint32_t greplica, uint64_t step, PhiloxKey key, int t, int T, long long &dB,
+                                             uint32_t greplica, uint64_t step, const PhiloxKey &key, int t, int T, long long &dB,
                                              long long &dS) {
     const int oc = colour ^ 1, items = nrows * nw;
 #pragma unroll 1

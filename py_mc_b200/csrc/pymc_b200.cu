@@ -27,13 +27,17 @@
 
 // largest bit image (bytes) for which PYMC_KERNEL_AUTO takes the resident kernel: several blocks per SM
 static const size_t RESIDENT_AUTO_MAX_IMAGE = 32 * 1024;
-// smallest lattice (sites) for which PYMC_KERNEL_AUTO takes the persistent kernel.  Measured at 16384 x 16384 only
-// (0.104 ms per sweep against 0.174 for the fused kernel); two grid barriers per sweep cost a few microseconds, so the
-// bound is kept where a sweep is at least ten times that.
-static const size_t PERSIST_AUTO_MIN_SITES = (size_t)16384 * 8192;
+// smallest single lattice (sites) for which PYMC_KERNEL_AUTO takes the persistent kernel K11 on calls of >= 2 sweeps.
+// Measured (profiles/r2_persist_probe.json): 6.2 / 7.2 / 11.7 us per sweep at 1024^2 / 2048^2 / 4096^2 against 8.2 /
+// 8.3 / 16.5 for the fused kernel; its two grid barriers cost 2.9 us per colour pass.  From PBATCH_SINGLE_MIN_SITES
+// on the batch-resident kernel K12 (no grid barrier) is faster still and takes over.
+static const size_t PERSIST_AUTO_MIN_SITES = (size_t)1024 * 1024;
 // smallest batch (sites of all replicas together) for which PYMC_KERNEL_AUTO takes the batch-resident kernel K12
 // on calls of >= 2 sweeps: from 1024 x 1024 on the resident kernels beat the per-sweep ones (profiles/README.md)
 static const size_t PBATCH_AUTO_MIN_SITES = (size_t)1024 * 1024;
+// ... but a single lattice below 4096 x 4096 gives a block so few rows that a pass is shorter than the flag
+// hand-shake between neighbouring blocks; there K11 is as good or better (profiles/r2_pbatch_probe.json)
+static const size_t PBATCH_SINGLE_MIN_SITES = (size_t)4096 * 4096;
 #ifndef PMC_PERSIST_AUTO
 #define PMC_PERSIST_AUTO 1  // 0: only PYMC_KERNEL_PERSISTENT selects the persistent kernel
 #endif
@@ -666,7 +670,7 @@ struct pymc_handle {
     bool pbatch;                   // calls of >= 2 sweeps (and single-GPU exchange cycles) run on the batch kernel
     int pb_blocks, pb_threads;
     size_t pb_smem;
-    unsigned int *pb_sync;         // [pb_blocks] export-event flags + [1] grid-barrier counter (zeroed per launch)
+    unsigned int *pb_sync;         // [pb_blocks] export-event flags + grid-barrier counter + abort word (zeroed per launch)
     uint64_t *pb_xbuf;             // [2][2*blocks + 2*nrep][nw] rows exchanged between blocks
     long long *pb_part;            // [2][blocks][PB_MAXSEG][2] partial sums of an exchange
     int32_t *pb_maps;              // [2 maps][2 parities][ntemps] replica <-> temperature maps of the kernel
@@ -947,8 +951,9 @@ int pymc_create(const pymc_params *p, pymc_handle **out) {
             const bool allowed = !(off && off[0] == '1');
             // AUTO: one lattice of >= 2^20 sites, or a batch that the one-block-per-replica kernel does not already
             // serve with several blocks per SM (small images, >= one replica per SM)
+            const size_t sites = (size_t)p->nreplicas * p->lenX * p->lenY;
             const bool auto_ok = p->kernel == PYMC_KERNEL_AUTO && allowed && ok && !h->resident &&
-                                 (size_t)p->nreplicas * p->lenX * p->lenY >= PBATCH_AUTO_MIN_SITES;
+                                 sites >= (p->nreplicas == 1 ? PBATCH_SINGLE_MIN_SITES : PBATCH_AUTO_MIN_SITES);
             h->pbatch = p->kernel == PYMC_KERNEL_PBATCH || auto_ok;
             if (h->pbatch && p->kernel == PYMC_KERNEL_AUTO) h->persist = h->resident_big = false;
             h->pb_blocks = blocks;
@@ -1265,7 +1270,7 @@ static int launch_pbatch(pymc_handle *h, int64_t nsweeps, int xchg_every, int *s
     }
     const int B = h->pb_blocks, R = h->p.ntemps;
     if (!h->pb_sync) {
-        CUDA_TRY(cudaMalloc(&h->pb_sync, (size_t)(B + 1) * sizeof(unsigned int)));
+        CUDA_TRY(cudaMalloc(&h->pb_sync, (size_t)(B + 2) * sizeof(unsigned int)));
         CUDA_TRY(cudaMalloc(&h->pb_xbuf, (size_t)2 * pb_nslots(B, h->p.nreplicas) * h->nw * 8));
         CUDA_TRY(cudaMalloc(&h->pb_part, (size_t)2 * B * PB_MAXSEG * 2 * sizeof(long long)));
     }
@@ -1305,7 +1310,7 @@ static int launch_pbatch(pymc_handle *h, int64_t nsweeps, int xchg_every, int *s
             a.accepted = h->rx_accepted;
             a.energies = h->energies;
         }
-        CUDA_TRY(cudaMemsetAsync(h->pb_sync, 0, (size_t)(B + 1) * sizeof(unsigned int), h->stream));
+        CUDA_TRY(cudaMemsetAsync(h->pb_sync, 0, (size_t)(B + 2) * sizeof(unsigned int), h->stream));
         CUDA_TRY(cudaMemsetAsync(h->reduced, 0, (size_t)h->p.nreplicas * 16, h->stream));
         void *args[] = {(void *)&L, (void *)&a};
         cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3(B), dim3(h->pb_threads), args, h->pb_smem, h->stream);

@@ -237,6 +237,8 @@ int pbatch_sweeps(int8_t *imgs, int nrep, int lenX, int lenY, const uint32_t *th
     std::vector<uint64_t> xbuf((size_t)2 * nslots * nw, 0xDEADBEEFDEADBEEFull);
     std::vector<unsigned int> flags(B, 0), cnt(B, 0);
     int err = 0;
+    unsigned int abort_word = 0;
+    const PhiloxKey keys = make_key(seed);
     std::vector<PBCtx> ctx(B);
     for (int b = 0; b < B; ++b) {
         PBGeom &g = geo[b];
@@ -265,6 +267,7 @@ int pbatch_sweeps(int8_t *imgs, int nrep, int lenX, int lenY, const uint32_t *th
         c.xbuf = xbuf.data();
         c.flags = flags.data();
         c.cnt = &cnt[b];
+        c.abort_word = &abort_word;
         c.err = &err;
         c.lenX = lenX;
         c.nw = nw;
@@ -274,7 +277,7 @@ int pbatch_sweeps(int8_t *imgs, int nrep, int lenX, int lenY, const uint32_t *th
         c.nslots = nslots;
         c.b = b;
         c.rep_offset = rep_offset;
-        c.key = make_key(seed);
+        c.key = &keys;
     }
     for (int b = 0; b < B; ++b) {
         for (int t = 0; t < T; ++t) pb_publish_loaded(geo[b], ctx[b], t, T);

@@ -110,7 +110,7 @@ def test_exchange_inside_the_kernel_matches_the_decision_kernel(R, shape, every,
     pair, round and sweep counters, exact sums."""
     from py_mc_b200 import _cabi
     from py_mc_b200.ising2D import ising2D
-    kTs = np.linspace(2.0, 2.6, R)
+    kTs = np.linspace(2.25, 2.25 + 0.004 * R, R)  # close enough for exchanges to be accepted on every lattice size here
     model = ising2D(-1.0)
     thr = _ising_thr(kTs)
     a = _rx(shape, layout, _cabi.KERNEL_PBATCH, R, ncycles, every, 1, _cabi.MODEL_ISING, thr, model._pmc_energy_coeffs(), kTs)
