@@ -343,7 +343,10 @@ def rx_measure(args, grp, rank, local_rank, nloc, R, distributed, kernel="auto")
     every = args.rx_every
     st = {"scheme": 0, "done": 0, "exchanges": 0, "launches": 0}
     lps, kname = lat.sweep_kernel_info()
-    if distributed and world > 1:
+    peer = distributed and world > 1 and args.rx_comm == "peer" and kname == "pbatch_kernel"
+    if peer:  # the exchange goes through peer memory inside the sweep kernel: one launch per call, like on one GPU
+        lat.rx_connect_group(grp.dist)
+    if distributed and world > 1 and not peer:
         torch, dist = grp.torch, grp.dist
         eptr, _ = lat.rx_buffers()
         e_all = torch.as_tensor(_DeviceArray(eptr, R, "<f8"), device="cuda")
@@ -368,15 +371,15 @@ def rx_measure(args, grp, rank, local_rank, nloc, R, distributed, kernel="auto")
             # one GPU holds all replicas: sweeps, energies and decisions are one launch per call (pymc_rx_cycle)
             head = min(n, (every - st["done"] % every) % every)
             if head:
-                lat.sweep(head)
+                if (st["done"] + head) % every == 0 and exchange:  # up to the next exchange, and that exchange
+                    lat.rx_cycle(1, head, st["scheme"])
+                    st["scheme"] ^= 1
+                    st["exchanges"] += 1
+                else:
+                    lat.sweep(head)
                 st["launches"] += 1
                 st["done"] += head
                 n -= head
-                if st["done"] % every == 0 and exchange:
-                    lat.rx_energies()
-                    lat.rx_exchange(st["scheme"])
-                    st["scheme"] ^= 1
-                    st["exchanges"] += 1
             ncyc = n // every
             if ncyc and exchange:
                 lat.rx_cycle(ncyc, every, st["scheme"])
@@ -394,10 +397,11 @@ def rx_measure(args, grp, rank, local_rank, nloc, R, distributed, kernel="auto")
                 st["done"] += tail
 
     steps(args.warmup)
-    if distributed and world > 1:  # one untimed exchange after the barrier: NCCL's first-call and skew costs stay outside
-        lat.synchronize()
-        grp.barrier()
-        steps(every - st["done"] % every)
+    # one untimed exchange after the barrier: first-call and skew costs stay outside, and the timed blocks start on an
+    # exchange boundary (one launch each where the exchange is inside the kernel)
+    lat.synchronize()
+    grp.barrier()
+    steps(every - st["done"] % every)
     K = args.steps
     ex0, l0 = st["exchanges"], st["launches"]
     ms, repeats = timed_repeats(grp, lambda: steps(K), lat.synchronize, lat.timer_start, lat.timer_stop)
@@ -410,6 +414,7 @@ def rx_measure(args, grp, rank, local_rank, nloc, R, distributed, kernel="auto")
     nsites = nloc * args.rx_L * args.rx_L
     tried, acc = lat.rx_stats()
     out = {"lat": lat, "steps": steps, "ms": ms, "repeats": repeats, "kernel": kname, "nsites_local": nsites,
+           "comm": "peer" if peer else ("nccl" if distributed and world > 1 else "none"),
            "value": world * nsites * K / (ms * 1e-3), "ms_per_step": ms / K, "exchanges_per_block": nex,
            "launches_per_block": nlaunch, "exchange_us": (1e3 * (ms - ms_plain) / nex) if nex else None,
            "acceptance": float(acc.sum()) / max(1.0, float(tried.sum())),
@@ -478,6 +483,7 @@ def run_rx(args):
             w["lat"].close()
             extra["weak"] = {"value": w["value"], "unit": UNIT, "ms_per_step": w["ms_per_step"], "replicas_per_gpu": args.rx_replicas,
                              "replicas_total": args.rx_replicas * world, "exchange_us": w["exchange_us"], "kernel": w["kernel"],
+                             "exchange_comm": w["comm"],
                              "parity": w["parity"], "repeats": w["repeats"], "scaling": "weak"}
         except Exception as exc:
             extra["weak"] = {"error": repr(exc)}
@@ -515,10 +521,14 @@ def run_rx(args):
                                 "exchange_acceptance": head["acceptance"],
                                 "l2": "no cache is relied upon: the lattices sit in shared memory between exchanges" if on_chip else
                                       "working set %d MiB per GPU" % (int(nsites * layout_bytes) >> 20),
-                                "parallelism": ("replicas block-partitioned over %d GPUs; all-gather of %d energies (NCCL, in place, on "
-                                                "the kernels' stream) per exchange; identical decision kernel on every GPU" % (world, R))
+                                "parallelism": (("replicas block-partitioned over %d GPUs; per exchange every GPU stores the exact sums of "
+                                                 "its replicas into the others' memory over NVLink from inside the sweep kernel and "
+                                                 "all decide alike: one launch per GPU, no NCCL, no host in the loop" % world)
+                                                if head["comm"] == "peer" else
+                                                ("replicas block-partitioned over %d GPUs; all-gather of %d energies (NCCL, in place, on "
+                                                 "the kernels' stream) per exchange; identical decision kernel on every GPU" % (world, R)))
                                 if world > 1 else "one GPU holds all replicas: sweeps, energies and pair decisions in one launch"},
-            "exchange_us": head["exchange_us"], "parity": head["parity"], "clocks": clocks,
+            "exchange_us": head["exchange_us"], "exchange_comm": head["comm"], "parity": head["parity"], "clocks": clocks,
             "e2e": {"value": e2e[args.e2e_sweeps], "unit": UNIT, "h2d_bytes_per_step": nsites, "d2h_bytes_per_step": 16 * nloc + 4 * R,
                     "sweeps_per_step": args.e2e_sweeps, "at_1_sweep_per_step": e2e[1],
                     "note": "C-ABI: upload every local replica from host int8, sweeps + exchanges, read back the exact sums and "
@@ -838,6 +848,8 @@ def main():
                     "N > 1: 256, BASELINE configs[2]")
     ap.add_argument("--rx-L", type=int, default=1024)
     ap.add_argument("--rx-every", type=int, default=10, help="sweeps between exchanges")
+    ap.add_argument("--rx-comm", default="peer", choices=["peer", "nccl"], help="several GPUs: energies exchanged through peer "
+                    "memory inside the sweep kernel (one launch per GPU), or by an NCCL all-gather between launches")
     ap.add_argument("--kernel", default="auto", choices=sorted(KERNELS), help="sweep kernel of the handle (PYMC_KERNEL_*)")
     ap.add_argument("--rx-model", default="ising", choices=["ising", "hardcore"])
     ap.add_argument("--rx-mu", type=float, default=1.0, help="chemical potential of the hard-core lattice gas")

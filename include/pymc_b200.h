@@ -251,13 +251,25 @@ int pymc_discs_timer(pymc_discs *d, int64_t ntrials, float *elapsed_ms);
  *                    double per pair and the Allgather of the rank->T map (mc_mpi.py:106-138).
  * pymc_rx_exchange   Xtrial(XCscheme) (mc_mpi.py:102-140) for every pair at once, on the device;
  *                    identical on every GPU because it reads only all-gathered data.
- * pymc_rx_cycle      single-GPU loop [sweeps, energies, exchange] x ncycles with alternating
- *                    scheme (mc_mpi.py:165-169), no host synchronisation inside. */
+ * pymc_rx_cycle      [sweeps, energies, exchange] x ncycles with alternating scheme (mc_mpi.py:165-169), no host
+ *                    synchronisation inside; one kernel launch where the batch-resident kernel applies.  On a
+ *                    handle that holds only part of the replicas it needs pymc_rx_connect (below). */
 int pymc_rx_setup(pymc_handle *h, const double *betas, int ntemps, double c_bond, double c_second);
 int pymc_rx_energies(pymc_handle *h);
 int pymc_rx_buffers(pymc_handle *h, void **energies_all, void **replica_to_T);
 int pymc_rx_exchange(pymc_handle *h, int xcscheme);
 int pymc_rx_cycle(pymc_handle *h, int64_t ncycles, int64_t sweeps_per_exchange, int first_scheme);
+/* The ladder spread over several GPUs with the exchange inside the sweep kernel (replaces the Send/Recv of one double
+ * per pair and the Allgather of mc_mpi.py:106-138 by stores into peer memory over NVLink; no host, no NCCL in the loop).
+ * pymc_rx_ipc_export  two CUDA IPC handles of this GPU (2 x 64 bytes): its per-replica sums and its delivery flags.
+ * pymc_rx_connect     all_handles = the exports of all GPUs in rank order (nranks x 128 bytes).  Needs the block
+ *                     partition rank g <-> replicas [g*R/G, (g+1)*R/G) and the batch-resident kernel.
+ * Afterwards pymc_rx_cycle works on the partitioned handle: ONE launch per GPU for all sweeps and exchanges of the call;
+ * every GPU must make the same calls.  A GPU that waits ten seconds for another one raises the handle's error
+ * (see pymc_synchronize).  pymc_rx_set_round to an earlier round restarts the delivery flags: call it on every GPU
+ * and synchronise the processes before the next cycle. */
+int pymc_rx_ipc_export(pymc_handle *h, void *handles, size_t nbytes);
+int pymc_rx_connect(pymc_handle *h, const void *all_handles, size_t nbytes, int nranks, int rank);
 int pymc_rx_get_energies(pymc_handle *h, double *energies, int n);
 /* attempts / acceptances per temperature pair, indexed by the lower temperature index */
 int pymc_rx_get_stats(pymc_handle *h, uint64_t *tried, uint64_t *accepted, int n);

@@ -32,7 +32,7 @@ SYMBOLS = [
     "pymc_create_slab", "pymc_slab_ipc_export", "pymc_slab_connect", "pymc_slab_connect_local",
     "pymc_slab_push_halos", "pymc_slab_status",
     "pymc_discs_timer", "pymc_stats_reset", "pymc_stats_accumulate", "pymc_stats_get",
-    "pymc_debug_raise_async_error",
+    "pymc_debug_raise_async_error", "pymc_rx_ipc_export", "pymc_rx_connect",
 ]
 
 
@@ -121,6 +121,8 @@ def _load():
         "pymc_rx_energies": [P],
         "pymc_rx_buffers": [P, C.POINTER(P), C.POINTER(P)],
         "pymc_rx_exchange": [P, I],
+        "pymc_rx_ipc_export": [P, P, C.c_size_t],
+        "pymc_rx_connect": [P, P, C.c_size_t, I, I],
         "pymc_rx_cycle": [P, I64, I64, I],
         "pymc_rx_get_energies": [P, P, I],
         "pymc_rx_get_stats": [P, P, P, I],
@@ -402,6 +404,27 @@ class Lattices:
 
     def rx_exchange(self, xcscheme):
         check(lib.pymc_rx_exchange(self._h, int(xcscheme)))
+
+    def rx_ipc_export(self):
+        """128 bytes: CUDA IPC handles of this GPU's per-replica sums and delivery flags (in-kernel exchange)."""
+        buf = (C.c_char * 128)()
+        check(lib.pymc_rx_ipc_export(self._h, buf, 128))
+        return bytes(buf)
+
+    def rx_connect(self, all_handles, nranks, rank):
+        """all_handles: the exports of all GPUs concatenated in rank order."""
+        check(lib.pymc_rx_connect(self._h, C.c_char_p(all_handles), len(all_handles), int(nranks), int(rank)))
+
+    def rx_connect_group(self, dist):
+        """Exchange the IPC handles over a torch.distributed group (once) and connect: afterwards rx_cycle on this
+        partitioned handle is one launch per GPU with the exchange done through peer memory inside the kernel."""
+        import torch
+        mine = torch.frombuffer(bytearray(self.rx_ipc_export()), dtype=torch.uint8).cuda()
+        world = dist.get_world_size()
+        out = torch.empty(128 * world, dtype=torch.uint8, device="cuda")
+        dist.all_gather_into_tensor(out, mine)
+        self.rx_connect(bytes(out.cpu().numpy().tobytes()), world, dist.get_rank())
+        dist.barrier()
 
     def rx_cycle(self, ncycles, sweeps_per_exchange, first_scheme=0):
         self._tracked_cache = None

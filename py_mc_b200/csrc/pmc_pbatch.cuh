@@ -54,6 +54,7 @@ namespace pmc {
 constexpr int PB_MAXSEG = 8;  // replicas a block may hold rows of
 constexpr int PB_MAXX = 4;    // rows a block takes from / gives to other blocks, per colour
 constexpr int PB_MAX_THREADS = 1024;
+constexpr int PB_MAXRANKS = 16;  // GPUs one ladder of replicas may be spread over
 
 // ---- geometry of block b (pure function of b, B, nrep, lenX) -------------------------------------------------
 struct PBGeom {
@@ -492,28 +493,16 @@ __device__ __forceinline__ void pb_reduce(const PBGeom &g, const PBCtx &c, unsig
 }
 
 // ---- replica exchange ----------------------------------------------------------------------------------------
-// Partial sums of the blocks: part[parity][block][seg][2].  Energy of global replica r from them, evaluated like
-// rx_energy_kernel (no FMA contraction) so that it equals the host expression J*B + (Eads-mu)*N bit for bit.
-__device__ __forceinline__ double pb_energy(const long long *part, int r_local, int B, int nrep, int lenX, double c_bond,
-                                            double c_second) {
-    const long long NR = (long long)nrep * lenX;
-    const int b0 = pb_block_of_row((long long)r_local * lenX, NR, B), b1 = pb_block_of_row((long long)r_local * lenX + lenX - 1, NR, B);
-    long long Bs = 0, Ss = 0;
-    for (int bb = b0; bb <= b1; ++bb) {
-        const int seg = r_local - pb_row0(bb, NR, B) / lenX;
-        const long long *p = part + ((size_t)bb * PB_MAXSEG + seg) * 2;
+// esum[global replica][2] = exact bond sum and second observable of every replica at this exchange.  The energy is
+// evaluated like rx_energy_kernel (no FMA contraction) so that it equals the host expression J*B + (Eads-mu)*N bit
+// for bit.
+__device__ __forceinline__ double pb_energy(const long long *esum, int r, double c_bond, double c_second) {
 #ifdef __CUDA_ARCH__
-        Bs += __ldcg(p);
-        Ss += __ldcg(p + 1);
-#else
-        Bs += p[0];
-        Ss += p[1];
-#endif
-    }
-#ifdef __CUDA_ARCH__
+    const long long Bs = __ldcg(esum + 2 * r), Ss = __ldcg(esum + 2 * r + 1);
     double e = __dmul_rn(c_bond, (double)Bs);
     if (c_second != 0.0) e = __dadd_rn(e, __dmul_rn((double)Ss, c_second));
 #else
+    const long long Bs = esum[2 * r], Ss = esum[2 * r + 1];
     double e = c_bond * (double)Bs;
     if (c_second != 0.0) e = e + (double)Ss * c_second;
 #endif
@@ -533,7 +522,13 @@ struct PBatchArgs {
     unsigned int *bar;             // [2] grid barrier arrivals and the abort word, zeroed by the host before the launch
     int *err;
     uint64_t *xbuf;                // [2][nslots][nw]
-    long long *part;               // [2][B][PB_MAXSEG][2]
+    long long *esum;               // [2 parities][R][2] per-replica exact sums of an exchange, indexed by GLOBAL replica;
+                                   // the local slice is zeroed by the host before the launch (blocks add deltas)
+    // replicas spread over several GPUs (pymc_rx_connect): the all-gather of the energies is done by this kernel
+    int nranks, rank;              // 1, 0 on a single GPU
+    long long *peer_esum[PB_MAXRANKS];    // the other GPUs' esum arrays (CUDA IPC mappings); [rank] unused
+    unsigned int *xflags;                 // [nranks] mine: xflags[g] = exchanges whose sums GPU g has delivered here
+    unsigned int *peer_xflags[PB_MAXRANKS];
     unsigned long long *out;       // [nrep][2] zeroed by the host: the exact sums at the end of the launch
     const double *betas;
     double c_bond, c_second;
@@ -574,7 +569,7 @@ __global__ void __launch_bounds__(PB_MAX_THREADS, 1) pbatch_kernel(const __grid_
     extern __shared__ __align__(16) uint64_t s_rows[];
     __shared__ uint32_t s_plan[PB_MAXSEG * PLAN_WORDS];
     __shared__ int s_segoff[PB_MAXSEG], s_segstart[PB_MAXSEG], s_T[PB_MAXSEG];
-    __shared__ long long s_acc[PB_MAXSEG * 2];
+    __shared__ long long s_acc[PB_MAXSEG * 2], s_prev[2][PB_MAXSEG * 2];
     __shared__ unsigned int s_cnt;
     __shared__ PBGeom s_geom;
     const int b = blockIdx.x, B = gridDim.x, t = threadIdx.x, T = blockDim.x;
@@ -591,6 +586,7 @@ __global__ void __launch_bounds__(PB_MAX_THREADS, 1) pbatch_kernel(const __grid_
         s_segoff[t] = t == 0 ? g.i0 : -((g.rep_first + t) * lenX - g.R0);
         s_T[t] = L.single_plan ? 0 : a.rep_to_T[0][L.rep_offset + g.rep_first + t];
     }
+    if (t < 2 * PB_MAXSEG) s_prev[0][t] = s_prev[1][t] = 0;
     PBCtx c;
     c.s = s_rows;
     c.segoff = s_segoff;
@@ -661,21 +657,63 @@ __global__ void __launch_bounds__(PB_MAX_THREADS, 1) pbatch_kernel(const __grid_
         pb_reduce<MODEL>(g, c, events, s_acc, t, T);
         __syncthreads();
         if (xch) {
-            const int par = (int)(round & 1ull);
-            long long *part = a.part + (size_t)par * B * PB_MAXSEG * 2;
-            if (t < 2 * g.nseg) part[(size_t)b * PB_MAXSEG * 2 + t] = s_acc[t];
+            const int par = (int)(round & 1ull), R = a.ntemps;
+            long long *es = a.esum + (size_t)par * R * 2;
+            if (t < 2 * g.nseg) {  // what my rows add to the replica's sums since I last wrote to this parity
+                const long long d = s_acc[t] - s_prev[par][t];
+                s_prev[par][t] = s_acc[t];
+                if (d) atomicAdd((unsigned long long *)(es + 2 * (size_t)(L.rep_offset + g.rep_first + t / 2) + (t & 1)), (unsigned long long)d);
+            }
             arrivals += (unsigned int)B;
-            pb_grid_barrier(a.bar, arrivals, a.err);  // every block's sums are in `part`
+            pb_grid_barrier(a.bar, arrivals, a.err);  // the sums of all replicas of this GPU are complete
+            if (a.nranks > 1) {
+                // All-gather over NVLink, written by hand: block 0 stores the sums of my replicas straight into every other
+                // GPU's array (peer memory), then raises my flag over there; every block waits until all other GPUs have
+                // delivered theirs here.  Flags carry the exchange round (the same number on every GPU, never reset).
+                const unsigned int xr = (unsigned int)round + 1u;
+                if (b == 0) {
+                    for (int k = t; k < 2 * nrep * a.nranks; k += T) {
+                        const int peer = k / (2 * nrep), j = k - peer * 2 * nrep;
+                        if (peer != a.rank) {
+                            const size_t at = (size_t)par * R * 2 + 2 * (size_t)L.rep_offset + j;
+                            a.peer_esum[peer][at] = __ldcg(a.esum + at);
+                        }
+                    }
+                    __threadfence_system();
+                    __syncthreads();
+                    if (t < a.nranks && t != a.rank) {
+                        __threadfence_system();
+                        *(volatile unsigned int *)(a.peer_xflags[t] + a.rank) = xr;
+                    }
+                }
+                if (t < a.nranks && t != a.rank) {
+                    const long long t0 = clock64();
+                    unsigned int spins = 0;
+                    while (*(volatile unsigned int *)(a.xflags + t) < xr) {
+                        __nanosleep(64);
+                        if ((++spins & 1023u) == 0) {
+                            if (*(volatile unsigned int *)(a.bar + 1)) break;
+                            if (clock64() - t0 > 20000000000LL) {  // ten seconds: the other GPU is not running this exchange
+                                *(volatile unsigned int *)(a.bar + 1) = 1u;
+                                *a.err = 1;
+                                break;
+                            }
+                        }
+                    }
+                    __threadfence_system();
+                }
+                __syncthreads();
+            }
             // ---- the pair decisions of Xtrial (py_mc/mc_mpi.py:102-140) ---------------------------------------------
             // A decision is a pure function of (pair, round, the two energies): every block works out the pairs its own
             // replicas are in (it needs their new temperatures), block 0 works out all of them and keeps the books.
-            const int nxt = cur ^ 1, R = a.ntemps;
+            const int nxt = cur ^ 1;
             const int32_t *t2r = a.T_to_rep[cur], *r2t = a.rep_to_T[cur];
             auto decide = [&](int tl, int &r_lo, int &r_hi) -> bool {  // pair (tl, tl + 1) of temperature indices
                 r_lo = t2r[tl];
                 r_hi = t2r[tl + 1];
-                const double e_lo = pb_energy(part, r_lo - (int)L.rep_offset, B, nrep, lenX, a.c_bond, a.c_second);
-                const double e_hi = pb_energy(part, r_hi - (int)L.rep_offset, B, nrep, lenX, a.c_bond, a.c_second);
+                const double e_lo = pb_energy(es, r_lo, a.c_bond, a.c_second);
+                const double e_hi = pb_energy(es, r_hi, a.c_bond, a.c_second);
                 const double delta = __dmul_rn(__dsub_rn(a.betas[tl + 1], a.betas[tl]), __dsub_rn(e_lo, e_hi));
                 if (delta < 0.0) return true;
                 const uint4 o = philox4x32_10((uint32_t)tl, 0u, (uint32_t)round, ctr3(DOMAIN_RX, 0, round), L.key);
@@ -701,8 +739,7 @@ __global__ void __launch_bounds__(PB_MAX_THREADS, 1) pbatch_kernel(const __grid_
                         a.rep_to_T[nxt][r] = tt;
                     }
                 }
-                for (int r = t; r < nrep; r += T)
-                    a.energies[L.rep_offset + r] = pb_energy(part, r, B, nrep, lenX, a.c_bond, a.c_second);
+                for (int r = t; r < R; r += T) a.energies[r] = pb_energy(es, r, a.c_bond, a.c_second);
                 const int g_first = (int)L.rep_offset + g.rep_first;
                 for (int p = t; 2 * p + scheme + 1 < R; p += T) {
                     const int tl = 2 * p + scheme;

@@ -672,7 +672,11 @@ struct pymc_handle {
     size_t pb_smem;
     unsigned int *pb_sync;         // [pb_blocks] export-event flags + grid-barrier counter + abort word (zeroed per launch)
     uint64_t *pb_xbuf;             // [2][2*blocks + 2*nrep][nw] rows exchanged between blocks
-    long long *pb_part;            // [2][blocks][PB_MAXSEG][2] partial sums of an exchange
+    long long *pb_esum;            // [2 parities][ntemps][2] exact sums per GLOBAL replica at an exchange
+    unsigned int *pb_xflags;       // [PB_MAXRANKS] exchange rounds whose sums each other GPU has delivered here
+    int rx_nranks, rx_rank;        // > 1 after pymc_rx_connect: the ladder is spread over that many GPUs
+    long long *peer_esum[PB_MAXRANKS];       // CUDA IPC mappings of the other GPUs' pb_esum / pb_xflags
+    unsigned int *peer_xflags[PB_MAXRANKS];
     int32_t *pb_maps;              // [2 maps][2 parities][ntemps] replica <-> temperature maps of the kernel
     bool pb_attr[2];
     // Time-outs of the in-kernel barriers are raised by the kernels in two ints of mapped pinned host memory, so
@@ -792,7 +796,13 @@ int pymc_destroy(pymc_handle *h) {
         cudaFree(h->persist_halo);
         cudaFree(h->pb_sync);
         cudaFree(h->pb_xbuf);
-        cudaFree(h->pb_part);
+        for (int g = 0; g < h->rx_nranks; ++g)
+            if (g != h->rx_rank) {
+                if (h->peer_esum[g]) cudaIpcCloseMemHandle(h->peer_esum[g]);
+                if (h->peer_xflags[g]) cudaIpcCloseMemHandle(h->peer_xflags[g]);
+            }
+        cudaFree(h->pb_esum);
+        cudaFree(h->pb_xflags);
         cudaFree(h->pb_maps);
         if (h->err_host) cudaFreeHost((void *)h->err_host);
         cudaFree(h->staging);
@@ -1251,6 +1261,19 @@ static int launch_persistent(pymc_handle *h, int64_t nsweeps) {
     return PYMC_OK;
 }
 
+// Buffers of the in-kernel exchange; also what pymc_rx_ipc_export hands to the other GPUs.
+static int ensure_rx_exchange_buffers(pymc_handle *h) {
+    if (!h->pb_esum) {
+        CUDA_TRY(cudaMalloc(&h->pb_esum, (size_t)2 * h->p.ntemps * 2 * sizeof(long long)));
+        CUDA_TRY(cudaMemset(h->pb_esum, 0, (size_t)2 * h->p.ntemps * 2 * sizeof(long long)));
+    }
+    if (!h->pb_xflags) {
+        CUDA_TRY(cudaMalloc(&h->pb_xflags, PB_MAXRANKS * sizeof(unsigned int)));
+        CUDA_TRY(cudaMemset(h->pb_xflags, 0, PB_MAXRANKS * sizeof(unsigned int)));
+    }
+    return PYMC_OK;
+}
+
 // K12: nsweeps sweeps of every replica in one cooperative launch per <= 4096 sweeps; with xchg_every > 0 (single-GPU
 // replica exchange) an exchange after every xchg_every-th sweep, decided inside the kernel.  Returns
 // PYMC_ERR_UNSUPPORTED (and switches the handle back to the other kernels) if the device refuses the launch.
@@ -1272,9 +1295,12 @@ static int launch_pbatch(pymc_handle *h, int64_t nsweeps, int xchg_every, int *s
     if (!h->pb_sync) {
         CUDA_TRY(cudaMalloc(&h->pb_sync, (size_t)(B + 2) * sizeof(unsigned int)));
         CUDA_TRY(cudaMalloc(&h->pb_xbuf, (size_t)2 * pb_nslots(B, h->p.nreplicas) * h->nw * 8));
-        CUDA_TRY(cudaMalloc(&h->pb_part, (size_t)2 * B * PB_MAXSEG * 2 * sizeof(long long)));
     }
     if (xchg_every > 0 && !h->pb_maps) CUDA_TRY(cudaMalloc(&h->pb_maps, (size_t)4 * R * sizeof(int32_t)));
+    if (xchg_every > 0) {
+        int rc = ensure_rx_exchange_buffers(h);
+        if (rc) return rc;
+    }
     Lat L = make_lat(h);
     int scheme = scheme_io ? *scheme_io : 0;
     while (nsweeps > 0) {
@@ -1293,7 +1319,14 @@ static int launch_pbatch(pymc_handle *h, int64_t nsweeps, int xchg_every, int *s
         a.bar = h->pb_sync + B;
         a.err = h->persist_err;
         a.xbuf = h->pb_xbuf;
-        a.part = h->pb_part;
+        a.esum = h->pb_esum;
+        a.nranks = h->rx_nranks > 1 ? h->rx_nranks : 1;
+        a.rank = h->rx_nranks > 1 ? h->rx_rank : 0;
+        a.xflags = h->pb_xflags;
+        for (int g = 0; g < a.nranks; ++g) {
+            a.peer_esum[g] = h->peer_esum[g];
+            a.peer_xflags[g] = h->peer_xflags[g];
+        }
         a.out = h->reduced;
         a.ntemps = R;
         a.rep_to_T[0] = h->rep_to_T;
@@ -1312,6 +1345,10 @@ static int launch_pbatch(pymc_handle *h, int64_t nsweeps, int xchg_every, int *s
         }
         CUDA_TRY(cudaMemsetAsync(h->pb_sync, 0, (size_t)(B + 2) * sizeof(unsigned int), h->stream));
         CUDA_TRY(cudaMemsetAsync(h->reduced, 0, (size_t)h->p.nreplicas * 16, h->stream));
+        if (xchg_every > 0)  // the blocks add deltas to the sums of MY replicas (other GPUs store theirs whole)
+            for (int par = 0; par < 2; ++par)
+                CUDA_TRY(cudaMemsetAsync(h->pb_esum + ((size_t)par * R + h->p.replica_offset) * 2, 0,
+                                         (size_t)h->p.nreplicas * 16, h->stream));
         void *args[] = {(void *)&L, (void *)&a};
         cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3(B), dim3(h->pb_threads), args, h->pb_smem, h->stream);
         if (e != cudaSuccess) {
@@ -1703,16 +1740,18 @@ int pymc_rx_exchange(pymc_handle *h, int xcscheme) {
 int pymc_rx_cycle(pymc_handle *h, int64_t ncycles, int64_t sweeps_per_exchange, int first_scheme) {
     ENTER(h);
     REQUIRE(h->rx_ready, PYMC_ERR_STATE, "pymc_rx_cycle: call pymc_rx_setup first");
-    REQUIRE(h->p.nreplicas == h->p.nreplicas_global, PYMC_ERR_STATE,
-            "pymc_rx_cycle: this handle holds %d of %d replicas; with several GPUs the caller all-gathers the "
-            "energies between pymc_rx_energies and pymc_rx_exchange", h->p.nreplicas, h->p.nreplicas_global);
+    const bool partitioned = h->p.nreplicas != h->p.nreplicas_global;
+    REQUIRE(!partitioned || (h->rx_nranks > 1 && h->pbatch && sweeps_per_exchange <= 4096), PYMC_ERR_STATE,
+            "pymc_rx_cycle: this handle holds %d of %d replicas; connect the GPUs with pymc_rx_ipc_export / pymc_rx_connect "
+            "(batch-resident kernel), or all-gather the energies yourself between pymc_rx_energies and pymc_rx_exchange",
+            h->p.nreplicas, h->p.nreplicas_global);
     REQUIRE(ncycles >= 0 && sweeps_per_exchange >= 1 && (first_scheme == 0 || first_scheme == 1), PYMC_ERR_BADARG,
             "pymc_rx_cycle: bad arguments");
     int scheme = first_scheme;
     if (h->pbatch && ncycles > 0 && sweeps_per_exchange <= 4096) {
         // everything in one kernel: sweeps, exact energies, grid barrier, pair decisions (pmc_pbatch.cuh)
         const int rc = launch_pbatch(h, ncycles * sweeps_per_exchange, (int)sweeps_per_exchange, &scheme);
-        if (rc != PYMC_ERR_UNSUPPORTED) return rc;
+        if (rc != PYMC_ERR_UNSUPPORTED || partitioned) return rc;  // (the other GPUs cannot follow a fall-back)
     }
     for (int64_t c = 0; c < ncycles; ++c) {
         int rc = pymc_sweep(h, sweeps_per_exchange);
@@ -1723,6 +1762,50 @@ int pymc_rx_cycle(pymc_handle *h, int64_t ncycles, int64_t sweeps_per_exchange, 
         scheme ^= 1;
     }
     CUDA_TRY(cudaGetLastError());
+    return PYMC_OK;
+}
+
+// ---- the ladder over several GPUs: exchange of the energies through peer memory, inside the sweep kernel ------
+// Each process exports two CUDA IPC handles (its per-replica sums and its flag words); pymc_rx_connect maps those of
+// all other GPUs.  After that pymc_rx_cycle on a partitioned handle is one launch per GPU: at an exchange, block 0
+// stores the sums of its replicas into every other GPU's array over NVLink and raises a flag there; the decisions
+// are then made on every GPU from identical data.  All GPUs must issue the same pymc_rx_cycle calls.
+int pymc_rx_ipc_export(pymc_handle *h, void *handles, size_t nbytes) {
+    ENTER(h);
+    REQUIRE(h->rx_ready, PYMC_ERR_STATE, "pymc_rx_ipc_export: call pymc_rx_setup first");
+    REQUIRE(handles && nbytes == 2 * sizeof(cudaIpcMemHandle_t), PYMC_ERR_BADARG, "pymc_rx_ipc_export: need %zu bytes",
+            2 * sizeof(cudaIpcMemHandle_t));
+    REQUIRE(h->pbatch, PYMC_ERR_UNSUPPORTED,
+            "pymc_rx_ipc_export: the in-kernel exchange needs the batch-resident kernel (PYMC_KERNEL_PBATCH or AUTO where it applies)");
+    int rc = ensure_rx_exchange_buffers(h);
+    if (rc) return rc;
+    cudaIpcMemHandle_t *out = (cudaIpcMemHandle_t *)handles;
+    CUDA_TRY(cudaIpcGetMemHandle(out + 0, h->pb_esum));
+    CUDA_TRY(cudaIpcGetMemHandle(out + 1, h->pb_xflags));
+    return PYMC_OK;
+}
+
+int pymc_rx_connect(pymc_handle *h, const void *all_handles, size_t nbytes, int nranks, int rank) {
+    ENTER(h);
+    REQUIRE(h->rx_ready && h->pb_esum, PYMC_ERR_STATE, "pymc_rx_connect: call pymc_rx_setup and pymc_rx_ipc_export first");
+    REQUIRE(nranks >= 2 && nranks <= PB_MAXRANKS && rank >= 0 && rank < nranks, PYMC_ERR_BADARG,
+            "pymc_rx_connect: rank %d of %d (at most %d GPUs)", rank, nranks, PB_MAXRANKS);
+    REQUIRE(all_handles && nbytes == (size_t)nranks * 2 * sizeof(cudaIpcMemHandle_t), PYMC_ERR_BADARG,
+            "pymc_rx_connect: need %zu bytes of handles", (size_t)nranks * 2 * sizeof(cudaIpcMemHandle_t));
+    REQUIRE(h->p.nreplicas * nranks == h->p.nreplicas_global && h->p.replica_offset == rank * h->p.nreplicas, PYMC_ERR_BADARG,
+            "pymc_rx_connect: the replicas must be block-partitioned evenly, rank g holding [g*R/G, (g+1)*R/G)");
+    REQUIRE(h->rx_nranks <= 1, PYMC_ERR_STATE, "pymc_rx_connect: already connected");
+    const cudaIpcMemHandle_t *hd = (const cudaIpcMemHandle_t *)all_handles;
+    for (int g = 0; g < nranks; ++g) {
+        if (g == rank) continue;
+        void *p0 = nullptr, *p1 = nullptr;
+        CUDA_TRY(cudaIpcOpenMemHandle(&p0, hd[2 * g + 0], cudaIpcMemLazyEnablePeerAccess));
+        CUDA_TRY(cudaIpcOpenMemHandle(&p1, hd[2 * g + 1], cudaIpcMemLazyEnablePeerAccess));
+        h->peer_esum[g] = (long long *)p0;
+        h->peer_xflags[g] = (unsigned int *)p1;
+    }
+    h->rx_nranks = nranks;
+    h->rx_rank = rank;
     return PYMC_OK;
 }
 
@@ -1756,6 +1839,11 @@ int pymc_rx_get_round(pymc_handle *h, uint64_t *round) {
 
 int pymc_rx_set_round(pymc_handle *h, uint64_t round) {
     REQUIRE(h, PYMC_ERR_BADARG, "pymc_rx_set_round: null handle");
+    if (h->pb_xflags && round < h->rx_round) {  // the delivery flags count rounds: start them again (do this on every GPU,
+        DeviceGuard guard(h->p.device);        // then synchronise the processes, before the next pymc_rx_cycle)
+        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        CUDA_TRY(cudaMemset(h->pb_xflags, 0, PB_MAXRANKS * sizeof(unsigned int)));
+    }
     h->rx_round = round;
     return PYMC_OK;
 }

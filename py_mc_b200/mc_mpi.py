@@ -258,6 +258,13 @@ class TemperatureRX_MPI(ParallelMC):
         self._lat.rx_setup(self.betas, c_bond, c_second)
         self._energies_t = None
         self.accept_count = 0
+        # the exchange inside the sweep kernel: always on one GPU; on several after connecting them through peer memory
+        self._fused = self._lat.sweep_kernel_info()[1] == "pbatch_kernel" and self.nreplicas <= 4096 * 16
+        if self._fused and self.procs > 1:
+            if self.comm.backend == "nccl" and os.environ.get("PYMC_RX_COMM", "peer") == "peer":
+                self._lat.rx_connect_group(self.comm.dist)
+            else:
+                self._fused = False
 
     # -- restart (mc_mpi.py:86-92) ---------------------------------------------------------------
     def reload(self):
@@ -304,6 +311,36 @@ class TemperatureRX_MPI(ParallelMC):
             self._allgather_energies()
         lat.rx_exchange(scheme)
 
+    def _advance(self, n, done, every, scheme):
+        """n sweeps from sweep number ``done`` with an exchange after every ``every``-th sweep (mc_mpi.py:165-169);
+        returns the scheme of the next exchange.  Where the batch-resident kernel applies (one GPU, or several
+        connected through peer memory) whole runs of exchange cycles are one launch: sweeps, exact energies and
+        the pair decisions all happen inside it."""
+        lat = self._lat
+        while n > 0:
+            to_x = every - done % every  # sweeps up to and including the next exchange point
+            if n < to_x:
+                lat.sweep(n)
+                return scheme
+            if self._fused:
+                if to_x == every:
+                    ncyc = n // every
+                    lat.rx_cycle(ncyc, every, scheme)
+                    scheme = (scheme + ncyc) % 2
+                    k = ncyc * every
+                else:
+                    lat.rx_cycle(1, to_x, scheme)
+                    scheme = (scheme + 1) % 2
+                    k = to_x
+            else:
+                lat.sweep(to_x)
+                self._exchange(scheme)
+                scheme = (scheme + 1) % 2
+                k = to_x
+            n -= k
+            done += k
+        return scheme
+
     def _allgather_energies(self):
         if self.comm.backend == "nccl":
             import torch
@@ -322,13 +359,9 @@ class TemperatureRX_MPI(ParallelMC):
         lat.stats_reset(*self.model._pmc_energy_coeffs())
         XCscheme, done, nsample = 0, 0, 0
         while done < nsteps:
-            chunk = min(nsteps - done, RXtrial_frequency - done % RXtrial_frequency,
-                        sample_frequency - done % sample_frequency)
-            lat.sweep(chunk)
+            chunk = min(nsteps - done, sample_frequency - done % sample_frequency)
+            XCscheme = self._advance(chunk, done, RXtrial_frequency, XCscheme)
             done += chunk
-            if done % RXtrial_frequency == 0:
-                self._exchange(XCscheme)
-                XCscheme = (XCscheme + 1) % 2
             if done % sample_frequency == 0:
                 lat.stats_accumulate()
                 nsample += 1
@@ -372,14 +405,11 @@ class TemperatureRX_MPI(ParallelMC):
         done = 0
         try:
             while done < nsteps:
-                chunk = min(nsteps - done, RXtrial_frequency - done % RXtrial_frequency)
+                chunk = nsteps - done
                 if observe:
                     chunk = min(chunk, sample_frequency - done % sample_frequency)
-                self._lat.sweep(chunk)
+                XCscheme = self._advance(chunk, done, RXtrial_frequency, XCscheme)
                 done += chunk
-                if done % RXtrial_frequency == 0:
-                    self._exchange(XCscheme)
-                    XCscheme = (XCscheme + 1) % 2
                 if observe and done % sample_frequency == 0:
                     self.rank_to_T = self._lat.get_replica_to_T().astype(int)
                     self._configs_changed()

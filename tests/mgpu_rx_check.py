@@ -98,6 +98,56 @@ def main():
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
         ok &= bool(flag.item())
         os.chdir(work[0])
+    # exchange inside the sweep kernel through peer memory (pymc_rx_ipc_export / pymc_rx_connect): one launch per GPU
+    # for all sweeps and exchanges; everything a caller can observe must equal the one-GPU run of the same ladder
+    from py_mc_b200 import _cabi
+    for (R, shape, every, ncyc) in ((16, (128, 256), 2, (5, 4)), (8 * world, (64, 128), 1, (7,)), (2 * world, (1024, 1024), 3, (3,))):
+        if R % world:
+            continue
+        kTs = np.linspace(2.25, 2.25 + 0.004 * R, R)
+        model = ising2D(-1.0)
+        thr = np.array([model._pmc_thresholds(kT) for kT in kTs])
+
+        def ladder(nloc, offset, group):
+            lat = _cabi.Lattices(_cabi.MODEL_ISING, shape[0], shape[1], nreplicas=nloc, ntemps=R, seed=99, device=local,
+                                 replica_offset=offset, nreplicas_global=R, kernel=_cabi.KERNEL_PBATCH)
+            lat.init_random()
+            lat.set_accept_tables(thr)
+            lat.rx_setup(1.0 / kTs, *model._pmc_energy_coeffs())
+            if group is not None:
+                lat.rx_connect_group(group)
+            scheme = 1
+            for n in ncyc:
+                lat.rx_cycle(n, every, scheme)
+                scheme ^= n & 1
+            lat.synchronize()
+            res = dict(map=lat.get_replica_to_T(), energies=lat.rx_get_energies(), stats=lat.rx_stats(), tracked=lat.tracked(),
+                       reduced=lat.reduce_observables(), configs=[lat.download(r) for r in range(nloc)], round=lat.rx_round)
+            lat.close()
+            return res
+
+        nloc = R // world
+        multi = ladder(nloc, rank * nloc, dist)
+        good = all(np.array_equal(multi["tracked"][k], multi["reduced"][k]) for k in (0, 1))
+        # every rank must hold the same map, energies and counters
+        t = torch.tensor(multi["map"], device="cuda", dtype=torch.int32)
+        lo, hi = t.clone(), t.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        good &= bool((lo == hi).all().item())
+        if rank == 0:
+            single = ladder(R, 0, None)
+            good &= np.array_equal(multi["map"], single["map"]) and np.array_equal(multi["energies"], single["energies"])
+            good &= all(np.array_equal(multi["stats"][k], single["stats"][k]) for k in (0, 1)) and multi["round"] == single["round"]
+            good &= int(single["stats"][1].sum()) > 0
+            for r in range(nloc):
+                good &= np.array_equal(multi["configs"][r], single["configs"][r])
+                good &= all(int(multi["tracked"][k][r]) == int(single["tracked"][k][r]) for k in (0, 1))
+            print("exchange through peer memory, %d replicas of %dx%d on %d GPUs vs 1 GPU: %s"
+                  % (R, shape[0], shape[1], world, "ok" if good else "MISMATCH"), flush=True)
+        flag = torch.tensor([1 if good else 0], device="cuda")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        ok &= bool(flag.item())
     if rank == 0:
         print("MGPU_RX_CHECK", "PASS" if ok else "FAIL", flush=True)
     dist.destroy_process_group()
