@@ -289,6 +289,19 @@ int pymc_stats_reset(pymc_handle *h, double c_bond, double c_second);
 int pymc_stats_accumulate(pymc_handle *h);
 int pymc_stats_get(pymc_handle *h, double *sums, uint64_t *counts, int ntemps, int nstat);
 
+/* Time series by temperature and their blocking analysis on the device: binning (py_mc/mc.py:47-61) and the
+ * per-temperature regrouping of examples/analyze_ising2D_mpi.py:28-45 without obs_save.npy / Trank_hist.npy round
+ * trips.  pymc_series_record appends one sample: series[sample][T] = (E, |M|) of the replica at temperature index T
+ * (entries of replicas on other GPUs stay 0: add the GPUs' series up, pymc_series_get / pymc_series_put).
+ * pymc_series_binning: for every (T, observable): mean over samples [discard, count) and the nlevels + 1 standard
+ * errors of binning() over all samples (leading count % 2^nlevels dropped); mean[ntemps][2], err[ntemps][2][nlevels+1]. */
+int pymc_series_reset(pymc_handle *h, int capacity, double c_bond, double c_second);
+int pymc_series_record(pymc_handle *h);
+int pymc_series_count(pymc_handle *h, int *count);
+int pymc_series_get(pymc_handle *h, double *out, size_t n);
+int pymc_series_put(pymc_handle *h, const double *in, int count);
+int pymc_series_binning(pymc_handle *h, int discard, int nlevels, double *mean, double *err);
+
 /* ---- pinned host memory ----------------------------------------------------------------
  * Page-locked buffers for upload/download at full PCIe speed (the reference keeps its arrays in
  * ordinary numpy memory, examples/ising2D.py:62; pageable buffers work too, only slower). */

@@ -21,6 +21,9 @@ the oracle is pinned against the reference *itself*, imported from
 ``/root/reference`` in the build container and driven with injected random
 draws; the outputs are committed under ``tests/golden/`` together with the
 script that made them (``tests/golden/make_golden.py``).  ``tests/test_oracle_*``
-check the oracle against those fixtures on every run, and against the live
-reference when ``/root/reference`` is present.
+check the oracle against those fixtures on every run; ``tests/test_live_reference.py``
+regenerates every fixture from the live reference (``/root/reference`` or the
+git-ignored copy ``oracle/_ref`` made by ``oracle/make_ref.py``) wherever it is present
+and compares array for array.  ``oracle/refarm.py`` times that same unmodified reference
+for ``bench.py``'s CPU baseline.
 """

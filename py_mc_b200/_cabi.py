@@ -33,6 +33,7 @@ SYMBOLS = [
     "pymc_slab_push_halos", "pymc_slab_status",
     "pymc_discs_timer", "pymc_stats_reset", "pymc_stats_accumulate", "pymc_stats_get",
     "pymc_debug_raise_async_error", "pymc_rx_ipc_export", "pymc_rx_connect",
+    "pymc_series_reset", "pymc_series_record", "pymc_series_count", "pymc_series_get", "pymc_series_put", "pymc_series_binning",
 ]
 
 
@@ -117,6 +118,12 @@ def _load():
         "pymc_stats_reset": [P, C.c_double, C.c_double],
         "pymc_stats_accumulate": [P],
         "pymc_stats_get": [P, P, P, I, I],
+        "pymc_series_reset": [P, I, C.c_double, C.c_double],
+        "pymc_series_record": [P],
+        "pymc_series_count": [P, C.POINTER(I)],
+        "pymc_series_get": [P, P, C.c_size_t],
+        "pymc_series_put": [P, P, I],
+        "pymc_series_binning": [P, I, I, P, P],
         "pymc_rx_setup": [P, P, I, C.c_double, C.c_double],
         "pymc_rx_energies": [P],
         "pymc_rx_buffers": [P, C.POINTER(P), C.POINTER(P)],
@@ -387,6 +394,35 @@ class Lattices:
         counts = np.empty(self.ntemps, dtype=np.uint64)
         check(lib.pymc_stats_get(self._h, _ptr(sums), _ptr(counts), self.ntemps, self.NSTAT))
         return sums, counts
+
+    # -- time series by temperature + blocking analysis on the device
+    def series_reset(self, capacity, c_bond, c_second=0.0):
+        check(lib.pymc_series_reset(self._h, int(capacity), float(c_bond), float(c_second)))
+
+    def series_record(self):
+        check(lib.pymc_series_record(self._h))
+
+    def series_count(self):
+        n = C.c_int(0)
+        check(lib.pymc_series_count(self._h, C.byref(n)))
+        return n.value
+
+    def series_get(self):
+        """[sample, T, (E, |M|)] as recorded on this GPU."""
+        out = np.empty((self.series_count(), self.ntemps, 2), dtype=np.float64)
+        check(lib.pymc_series_get(self._h, _ptr(out), out.size))
+        return out
+
+    def series_put(self, series):
+        a = np.ascontiguousarray(series, dtype=np.float64).reshape(-1, self.ntemps, 2)
+        check(lib.pymc_series_put(self._h, _ptr(a), a.shape[0]))
+
+    def series_binning(self, discard, nlevels):
+        """(mean [T, 2] over samples [discard:], errors [T, 2, nlevels + 1] of binning() over all samples)."""
+        mean = np.empty((self.ntemps, 2), dtype=np.float64)
+        err = np.empty((self.ntemps, 2, nlevels + 1), dtype=np.float64)
+        check(lib.pymc_series_binning(self._h, int(discard), int(nlevels), _ptr(mean), _ptr(err)))
+        return mean, err
 
     # -- replica exchange
     def rx_setup(self, betas, c_bond, c_second=0.0):

@@ -84,6 +84,15 @@ class LatticeConfig:
         """Return the one-replica device lattice for this config, creating/uploading as needed."""
         layout = _layout_code(self.layout, self.lenY)
         key = (model_code, layout)
+        if self._lat is not None and self._lat_shared:
+            # bound to a batch of a replica-exchange engine: a host edit goes back into that batch, whatever layout
+            # the batch was created with (it is taken from the first configuration)
+            if self._lat_key[0] != model_code:
+                raise TypeError("this configuration is bound to a batch of another model")
+            if not self._dev_valid:
+                self._lat.upload(self._rep, self._to_int8(self._host))
+                self._dev_valid = True
+            return self._lat
         if self._lat is None or self._lat_key != key:
             if self._lat is not None:
                 self._pull()

@@ -74,6 +74,78 @@ __global__ void stats_accumulate_kernel(const unsigned long long *__restrict__ t
     atomicAdd(counts + t, 1ull);
 }
 
+// ---- time series by temperature and their blocking analysis on the device --------------------------
+// series[sample][T][2] = (E, |M|) of whichever replica sits at temperature index T at that sample: the regrouping
+// examples/analyze_ising2D_mpi.py:28-34 does afterwards from obs_save.npy / Trank_hist.npy (np.where + Reduce).
+// One thread per local replica; entries of replicas on other GPUs stay 0 (the caller adds the GPUs up).
+__global__ void series_record_kernel(const unsigned long long *__restrict__ tracked, int nrep, int offset,
+                                     const int32_t *__restrict__ rep_to_T, double c_bond, double c_second, int ntemps,
+                                     double *__restrict__ row) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= nrep) return;
+    const double b = (double)(long long)tracked[2 * r], m = (double)(long long)tracked[2 * r + 1];
+    double e = __dmul_rn(c_bond, b);
+    if (c_second != 0.0) e = __dadd_rn(e, __dmul_rn(m, c_second));
+    const int t = rep_to_T[offset + r];
+    row[2 * t] = e;
+    row[2 * t + 1] = fabs(m);
+}
+
+// Sum of the n values v(i) over a block of 256 threads (every thread gets the result).
+template <class F>
+__device__ __forceinline__ double block_sum_256(int n, F v) {
+    __shared__ double s_part[8];
+    __shared__ double s_total;
+    double a = 0.0;
+    for (int i = threadIdx.x; i < n; i += 256) a += v(i);
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) a += __shfl_down_sync(0xFFFFFFFFu, a, d);
+    __syncthreads();  // s_part / s_total of a previous call have been read
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = a;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int k = 0; k < 8; ++k) t += s_part[k];
+        s_total = t;
+    }
+    __syncthreads();
+    return s_total;
+}
+
+// binning() of py_mc/mc.py:47-61 for every (temperature, observable) series at once: block (T, j) drops the leading
+// count % 2^nlevels samples, then per level takes sqrt(var(x, ddof=1) / len(x)) and averages neighbouring pairs
+// ((a + b) / 2.0, the reference's expression).  Also the mean over samples [discard, count) that
+// analyze_ising2D_mpi.py:36 prints.  work: [ntemps * 2][2][capacity] ping-pong buffers.  block = 256 threads.
+__global__ void __launch_bounds__(256) series_binning_kernel(const double *__restrict__ series, int count, int ntemps,
+                                                             int discard, int nlevels, double *work, int capacity,
+                                                             double *__restrict__ mean_out, double *__restrict__ err_out) {
+    const int sidx = blockIdx.x;  // T * 2 + j
+    double *buf0 = work + (size_t)sidx * 2 * capacity, *buf1 = buf0 + capacity;
+    const int drop = count % (1 << nlevels);
+    int n = count - drop;
+    for (int i = threadIdx.x; i < count; i += 256) {
+        const double v = series[(size_t)i * ntemps * 2 + sidx];
+        if (i >= drop) buf0[i - drop] = v;
+    }
+    __syncthreads();
+    const int nm = count - discard;
+    const double msum = block_sum_256(nm, [&](int i) { return series[(size_t)(i + discard) * ntemps * 2 + sidx]; });
+    if (threadIdx.x == 0) mean_out[sidx] = nm > 0 ? msum / nm : 0.0;
+    double *x = buf0, *y = buf1;
+    for (int lvl = 0; lvl <= nlevels; ++lvl) {
+        const double mu = block_sum_256(n, [&](int i) { return x[i]; }) / n;
+        const double ss = block_sum_256(n, [&](int i) { const double d = x[i] - mu; return d * d; });
+        if (threadIdx.x == 0) err_out[(size_t)sidx * (nlevels + 1) + lvl] = sqrt(ss / (n - 1) / n);
+        if (lvl == nlevels) break;
+        for (int i = threadIdx.x; i < n / 2; i += 256) y[i] = (x[2 * i] + x[2 * i + 1]) / 2.0;
+        __syncthreads();
+        n /= 2;
+        double *tmp = x;
+        x = y;
+        y = tmp;
+    }
+}
+
 __global__ void rx_invert_map_kernel(const int32_t *__restrict__ rep_to_T, int32_t *T_to_rep, int n) {
     const int r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r < n) T_to_rep[rep_to_T[r]] = r;

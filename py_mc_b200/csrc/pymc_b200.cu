@@ -640,6 +640,10 @@ struct pymc_handle {
     double c_bond, c_second;
     double *stats;                 // [ntemps][NSTAT] device-side observable sums (pymc_stats_*)
     unsigned long long *stats_count;  // [ntemps]
+    double *series;                // [series_cap][ntemps][2] (E, |M|) by temperature index per sample (pymc_series_*)
+    double *series_work;           // [ntemps*2][2][series_cap] ping-pong buffers of the blocking analysis
+    double *series_out;            // [ntemps*2] means + [ntemps*2][32] errors
+    int series_cap, series_count;
     bool rx_ready;
     uint64_t rx_round;
     // row-slab mode (pymc_create_slab): see Lat
@@ -814,6 +818,9 @@ int pymc_destroy(pymc_handle *h) {
         cudaFree(h->rx_accepted);
         cudaFree(h->stats);
         cudaFree(h->stats_count);
+        cudaFree(h->series);
+        cudaFree(h->series_work);
+        cudaFree(h->series_out);
         cudaFree(h->flags);
         cudaFree(h->slab_done);
         if (h->slab && h->nslabs > 1 && h->peer_up[0] && !h->local_peers) {
@@ -2159,6 +2166,93 @@ int pymc_stats_get(pymc_handle *h, double *sums, uint64_t *counts, int ntemps, i
     return PYMC_OK;
 }
 
+
+// ------------------------------------------------------------------------------------------
+// time series by temperature + blocking analysis on the device
+// ------------------------------------------------------------------------------------------
+#define PYMC_SERIES_MAXLEVELS 31
+
+int pymc_series_reset(pymc_handle *h, int capacity, double c_bond, double c_second) {
+    ENTER(h);
+    REQUIRE(capacity >= 1, PYMC_ERR_BADARG, "pymc_series_reset: capacity %d", capacity);
+    if (capacity > h->series_cap) {
+        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        cudaFree(h->series);
+        cudaFree(h->series_work);
+        h->series = h->series_work = nullptr;
+        h->series_cap = 0;
+        CUDA_TRY(cudaMalloc(&h->series, (size_t)capacity * h->p.ntemps * 2 * sizeof(double)));
+        CUDA_TRY(cudaMalloc(&h->series_work, (size_t)capacity * h->p.ntemps * 4 * sizeof(double)));
+        h->series_cap = capacity;
+    }
+    if (!h->series_out) CUDA_TRY(cudaMalloc(&h->series_out, (size_t)h->p.ntemps * 2 * (PYMC_SERIES_MAXLEVELS + 2) * sizeof(double)));
+    CUDA_TRY(cudaMemsetAsync(h->series, 0, (size_t)h->series_cap * h->p.ntemps * 2 * sizeof(double), h->stream));
+    h->series_count = 0;
+    h->c_bond = c_bond;
+    h->c_second = c_second;
+    return PYMC_OK;
+}
+
+int pymc_series_record(pymc_handle *h) {
+    ENTER(h);
+    REQUIRE(h->series, PYMC_ERR_STATE, "pymc_series_record: call pymc_series_reset first");
+    REQUIRE(h->series_count < h->series_cap, PYMC_ERR_STATE, "pymc_series_record: the series is full (%d samples)", h->series_cap);
+    if (h->dirty) {
+        int rc = rebase_tracked(h);
+        if (rc) return rc;
+    }
+    series_record_kernel<<<(h->p.nreplicas + 127) / 128, 128, 0, h->stream>>>(
+        h->tracked, h->p.nreplicas, h->p.replica_offset, h->rep_to_T, h->c_bond, h->c_second, h->p.ntemps,
+        h->series + (size_t)h->series_count * h->p.ntemps * 2);
+    CUDA_TRY(cudaGetLastError());
+    h->series_count++;
+    return PYMC_OK;
+}
+
+int pymc_series_count(pymc_handle *h, int *count) {
+    REQUIRE(h && count, PYMC_ERR_BADARG, "pymc_series_count: null pointer");
+    *count = h->series_count;
+    return PYMC_OK;
+}
+
+int pymc_series_get(pymc_handle *h, double *out, size_t n) {
+    ENTER(h);
+    REQUIRE(h->series && out && n == (size_t)h->series_count * h->p.ntemps * 2, PYMC_ERR_BADARG,
+            "pymc_series_get: need %zu values", h->series ? (size_t)h->series_count * h->p.ntemps * 2 : (size_t)0);
+    if (n) CUDA_TRY(cudaMemcpyAsync(out, h->series, n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    CHECK_ASYNC(h);
+    return PYMC_OK;
+}
+
+int pymc_series_put(pymc_handle *h, const double *in, int count) {
+    ENTER(h);
+    REQUIRE(h->series && in && count >= 0 && count <= h->series_cap, PYMC_ERR_BADARG, "pymc_series_put: %d samples, capacity %d",
+            count, h->series_cap);
+    if (count) CUDA_TRY(cudaMemcpyAsync(h->series, in, (size_t)count * h->p.ntemps * 2 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    h->series_count = count;
+    return PYMC_OK;
+}
+
+int pymc_series_binning(pymc_handle *h, int discard, int nlevels, double *mean, double *err) {
+    ENTER(h);
+    REQUIRE(h->series && mean && err, PYMC_ERR_BADARG, "pymc_series_binning: call pymc_series_reset first; null pointer");
+    REQUIRE(nlevels >= 0 && nlevels <= PYMC_SERIES_MAXLEVELS && discard >= 0 && discard < h->series_count &&
+                (h->series_count >> nlevels) >= 2,
+            PYMC_ERR_BADARG, "pymc_series_binning: %d samples, discard %d, %d levels (the top level needs two blocks)",
+            h->series_count, discard, nlevels);
+    const int ns = h->p.ntemps * 2;
+    double *d_mean = h->series_out, *d_err = h->series_out + ns;
+    series_binning_kernel<<<ns, 256, 0, h->stream>>>(h->series, h->series_count, h->p.ntemps, discard, nlevels, h->series_work,
+                                                    h->series_cap, d_mean, d_err);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpyAsync(mean, d_mean, (size_t)ns * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaMemcpyAsync(err, d_err, (size_t)ns * (nlevels + 1) * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    CHECK_ASYNC(h);
+    return PYMC_OK;
+}
 
 // ------------------------------------------------------------------------------------------
 // row-slab mode: one lattice split over GPUs

@@ -357,6 +357,9 @@ class TemperatureRX_MPI(ParallelMC):
         """The run loop with sampling on the device: nothing in it synchronises with the host."""
         lat = self._lat
         lat.stats_reset(*self.model._pmc_energy_coeffs())
+        keep = getattr(observer, "keep_series", False)
+        if keep:
+            lat.series_reset(max(1, nsteps // sample_frequency), *self.model._pmc_energy_coeffs())
         XCscheme, done, nsample = 0, 0, 0
         while done < nsteps:
             chunk = min(nsteps - done, sample_frequency - done % sample_frequency)
@@ -364,8 +367,15 @@ class TemperatureRX_MPI(ParallelMC):
             done += chunk
             if done % sample_frequency == 0:
                 lat.stats_accumulate()
+                if keep:
+                    lat.series_record()
                 nsample += 1
         sums, counts = lat.stats_get()
+        if keep:
+            if self.procs > 1:  # every GPU recorded the entries of its own replicas: add them up, everywhere
+                full = self.comm.allreduce_sum_host(lat.series_get().ravel())
+                lat.series_put(full)
+            observer._lat = lat
         if self.procs > 1:
             sums = self.comm.allreduce_sum_host(sums)
             counts = np.rint(self.comm.allreduce_sum_host(counts.astype(np.float64))).astype(np.uint64)

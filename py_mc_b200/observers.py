@@ -14,6 +14,12 @@ trip per sample.  After ``run`` the observer holds
 
 all as totals for the lattice (divide by the number of sites for per-site values).  Time series
 files (``obs_save.npy`` ...) are not written on this path.
+
+``device_observer(series=True)`` also keeps the time series of (E, |M|) *by temperature index* on the
+device (``series_record_kernel``) -- the regrouping ``examples/analyze_ising2D_mpi.py:28-34`` does
+afterwards from the per-replica files -- and ``analyze()`` runs the reference's post-processing on it
+there: mean after discarding the first 10 % and the blocking errors of ``binning`` (py_mc/mc.py:47-61)
+for every temperature and observable in one kernel (``series_binning_kernel``).
 """
 import numpy as np
 
@@ -35,9 +41,27 @@ def thermo(sums, counts, kTs):
 class device_observer(observer_base):
     _pmc_device = True
 
-    def __init__(self):
+    def __init__(self, series=False):
         super(device_observer, self).__init__()
         self.counts = None
+        self.keep_series = bool(series)
+        self._lat = None
+
+    def analyze(self, discard_fraction=0.1, bin_level=None):
+        """(means [T, 2], errors [T, 2], all blocking errors [T, 2, level]) of the recorded series, as
+        examples/analyze_ising2D_mpi.py computes them: mean over the samples after the first 10 %, error = the
+        largest blocking error over levels 0 .. int(log2(nsamples // 30))."""
+        if self._lat is None or not self.keep_series:
+            raise RuntimeError("no series was recorded: use device_observer(series=True) and run first")
+        n = self._lat.series_count()
+        if bin_level is None:
+            bin_level = int(np.log2(n // 30))
+        mean, err = self._lat.series_binning(int(n * discard_fraction), bin_level)
+        return mean, err.max(axis=2), err
+
+    def series(self):
+        """[sample, T, (E, |M|)]"""
+        return self._lat.series_get()
 
     # host fallback with the same two logged quantities (used for the probe call and obs_info)
     def logfunc(self, calc_state):

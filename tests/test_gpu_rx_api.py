@@ -101,3 +101,48 @@ def test_parallel_mc_returns_per_replica_means(workdir):
     assert out.shape == (3, 2)
     assert out[0, 0] < out[2, 0] < 0  # colder replica has lower energy
     assert os.path.exists("0/config.pickle") and os.path.exists("2/obs.dat")
+
+
+def test_fused_cycles_and_host_edits_on_a_word_aligned_ladder(workdir):
+    """64 x 128 lattices: the batch-resident kernel applies, so the engine runs whole stretches of exchange cycles
+    as one launch (TemperatureRX_MPI._advance).  The outcome must not depend on the kernel; and a host edit of a replica whose config object was created with another ``layout=`` than the
+    first one must reach the batch of the engine (it used to be diverted to a private lattice)."""
+    import py_mc_b200
+    from py_mc_b200.ising2D import ising2D, ising2D_config, observer
+    from py_mc_b200.mc import CanonicalMonteCarlo
+    from py_mc_b200.mc_mpi import TemperatureRX_MPI
+    from oracle import ising as o_ising
+    R, shape, seed = 6, (64, 128), 31
+    kTs = np.linspace(2.2, 2.35, R)
+
+    def engine(layouts, no_persistent=False):
+        py_mc_b200.set_seed(seed)
+        if no_persistent:
+            os.environ["PYMC_NO_PERSISTENT"] = "1"
+        cfgs = []
+        for r in range(R):
+            c = ising2D_config(shape[0], shape[1], layout=layouts[r % len(layouts)])
+            c.config[:, :] = o_ising.init_config(seed, r, *shape)
+            cfgs.append(c)
+        rx = TemperatureRX_MPI(None, CanonicalMonteCarlo, ising2D(-1.0), cfgs, kTs)
+        os.environ.pop("PYMC_NO_PERSISTENT", None)
+        return rx, cfgs
+
+    results = []
+    for k, (layouts, cuts, nop) in enumerate(((["int8"], (24,), False), (["int8", "bits"], (24,), False), (["int8"], (24,), True))):
+        sub = workdir / ("run%d" % k)
+        sub.mkdir()
+        os.chdir(sub)
+        rx, cfgs = engine(layouts, nop)
+        assert rx._fused == (not nop)
+        outs = [rx.run(n, 3, 2, 10 ** 12, observer(), True, True) for n in cuts]
+        # a host edit between runs: flip one replica completely, then four more sweeps with exchanges
+        cfgs[1].config[:, :] = -cfgs[1].config
+        rx.run(4, 2)
+        results.append((np.array(rx.rank_to_T), [np.array(c.config) for c in cfgs], [s.energy for s in rx.states], outs[0][0]))
+    for other in results[1:]:
+        assert np.array_equal(results[0][0], other[0])
+        for a, b in zip(results[0][1], other[1]):
+            assert np.array_equal(a, b)
+        assert results[0][2] == other[2]
+        assert np.array_equal(np.array(results[0][3]), np.array(other[3]))  # per-temperature means of the first run

@@ -213,3 +213,51 @@ def test_binder_cumulants_cross_at_the_onsager_temperature(tmp_path):
         assert 0.58 < u_cross < 0.63, u_cross
     finally:
         os.chdir(old)
+
+
+def test_device_series_and_binning_match_the_reference_post_processing(tmp_path):
+    """The same replica-exchange run twice: with the host observer (per-replica obs_save.npy / Trank_hist.npy, then
+    py_mc_b200.analyze.analyze, whose output is byte-identical to examples/analyze_ising2D_mpi.py -- tests/
+    test_analyze_cpu.py) and with device_observer(series=True), where the series by temperature and the blocking
+    analysis (py_mc/mc.py:47-61) stay on the device.  The series must agree exactly (they are the same exact integers
+    times J), the means to rounding, the blocking errors to 1e-9 relative (summation order)."""
+    import py_mc_b200
+    from py_mc_b200 import analyze
+    from py_mc_b200.ising2D import ising2D, ising2D_config, observer
+    from py_mc_b200.mc import CanonicalMonteCarlo, binning
+    from py_mc_b200.mc_mpi import TemperatureRX_MPI
+    from py_mc_b200.observers import device_observer
+    R, shape, seed, nsteps, every, sample = 6, (16, 16), 77, 1500, 2, 3
+    kTs = np.linspace(2.0, 2.8, R)
+
+    def engine():
+        py_mc_b200.set_seed(seed)
+        cfgs = []
+        for r in range(R):
+            c = ising2D_config(*shape)
+            c.config[:, :] = o_ising.init_config(seed, r, *shape)
+            cfgs.append(c)
+        return TemperatureRX_MPI(None, CanonicalMonteCarlo, ising2D(-1.0), cfgs, kTs)
+
+    old = os.getcwd()
+    try:
+        os.chdir(tmp_path)
+        engine().run(nsteps, every, sample, 10 ** 12, observer(), True, True)
+        means, errors = analyze.analyze(R, ".", write=False)
+        obs = np.array([np.load(os.path.join(str(r), "obs_save.npy")) for r in range(R)])
+        th = np.array([np.load(os.path.join(str(r), "Trank_hist.npy")) for r in range(R)])
+        host_series = analyze.regroup(obs, th)          # [T, sample, 2]
+        dev = device_observer(series=True)
+        engine().run(nsteps, every, sample, observer=dev)
+    finally:
+        os.chdir(old)
+    series = dev.series()                                # [sample, T, 2]
+    assert series.shape == (nsteps // sample, R, 2)
+    assert np.array_equal(series.transpose(1, 0, 2), host_series)
+    dmean, derr, levels = dev.analyze()
+    assert np.allclose(dmean, means, rtol=1e-13, atol=0)
+    assert np.allclose(derr, errors, rtol=1e-9, atol=0)
+    nlev = int(np.log2(series.shape[0] // 30))
+    for t in (0, R - 1):
+        for j in (0, 1):
+            assert np.allclose(levels[t, j], binning(series[:, t, j], nlev), rtol=1e-9, atol=0)
