@@ -47,22 +47,27 @@ def measured_peak_hbm():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-# committed ncu --set full summaries (profiles/): kernel -> (file, launch shape the capture is of)
+# committed ncu --set full summaries (profiles/): (kernel, workload tag) -> (file, launch shape the capture is of).
+# A line only quotes a capture of its own kernel on its own workload.
 PROFILED = {
-    "sweep_fused_i8_kernel": ("r1_fused_final_summary.csv", "16384x16384 int8, one sweep per launch"),
-    "sweep_bits_rows_kernel": ("r1_bits_final_summary.csv", "16384x16384 bits, one colour pass per launch"),
-    "resident_kernel": ("r1_resident_rx_summary.csv", "256 x 1024^2 int8, 10 sweeps per launch"),
-    "persistent_kernel": ("r2_persist_summary.csv", "16384x16384 int8, 20 sweeps per launch"),
-    "pbatch_kernel": ("r2_pbatch_summary.csv", "16384x16384 int8, 20 sweeps per launch"),
+    ("sweep_fused_i8_kernel", "single16k"): ("r1_fused_final_summary.csv", "16384x16384 int8, one sweep per launch"),
+    ("sweep_bits_rows_kernel", "single16k"): ("r1_bits_final_summary.csv", "16384x16384 bits, one colour pass per launch"),
+    ("resident_kernel", "rx256"): ("r1_resident_rx_summary.csv", "256 x 1024^2 int8, 10 sweeps per launch"),
+    ("persistent_kernel", "single16k"): ("r2_persist_summary.csv", "16384x16384 int8, 20 sweeps per launch"),
+    ("pbatch_kernel", "single16k"): ("r2_pbatch_summary.csv", "16384x16384 int8, 20 sweeps per launch"),
+    ("pbatch_kernel", "rx256"): ("r2_pbatch_rx_summary.csv", "256 x 1024^2 int8, 20 sweeps + 2 exchanges per launch"),
+    ("resident_kernel", "latgas512_pair"): ("r2_latgas_resident_summary.csv", "512 x 256^2 int8 lattice gas, 20 pair-exchange sweeps per launch"),
+    ("pair_class_kernel", "latgas512_pair"): ("r2_latgas_pair_summary.csv", "512 x 256^2 int8 lattice gas, one bond class per launch"),
+    ("discs_run_kernel", "discs8192"): ("r2_discs_summary.csv", "8192 replicas x 20 discs, 2000 trials per launch"),
 }
 
 
-def profiled(kernel_name):
+def profiled(kernel_name, tag):
     """Per-launch DRAM bytes and pipe utilisation of the dominant kernel from the committed ncu summary."""
     import csv
-    if kernel_name not in PROFILED:
+    if (kernel_name, tag) not in PROFILED:
         return None
-    fname, shape = PROFILED[kernel_name]
+    fname, shape = PROFILED[(kernel_name, tag)]
     path = os.path.join(ROOT, "profiles", fname)
     want = {"dram__bytes_read.sum": "dram_read", "dram__bytes_write.sum": "dram_write",
             "smsp__issue_active.avg.pct_of_peak_sustained_active": "issue_active_pct",
@@ -265,13 +270,13 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
-def roofline_block(kname, alg_bytes_per_launch, launch_ms, on_chip):
+def roofline_block(kname, alg_bytes_per_launch, launch_ms, on_chip, tag=None):
     """The contract's roofline object: algorithmic bytes per launch over the measured launch time against the measured
     HBM copy peak (SURVEY 8d accounting).  For the kernels that keep the lattice in shared memory that figure is an
     accounting figure, not DRAM traffic: ``bound`` says what really limits them and ``dram_gbs`` what DRAM moves."""
     peak, peak_src = measured_peak_hbm()
     achieved = alg_bytes_per_launch / (launch_ms * 1e-3) / 1e9
-    prof = profiled(kname) or {}
+    prof = profiled(kname, tag) or {}
     r = {"bound": "alu" if on_chip else "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
          "traffic": prof.get("traffic"), "traffic_source": prof.get("source"), "traffic_capture": prof.get("capture_shape"),
          "kernel": kname, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes_per_launch,
@@ -534,7 +539,8 @@ def run_rx(args):
                     "note": "C-ABI: upload every local replica from host int8, sweeps + exchanges, read back the exact sums and "
                             "the replica->T map; bytes are per GPU"},
             "gpu_launches": int(round(head["launches_per_block"])),
-            "roofline": roofline_block(head["kernel"], alg, launch_ms, on_chip),
+            "roofline": roofline_block(head["kernel"], alg, launch_ms, on_chip,
+                                       "rx256" if (nloc, args.rx_L, args.layout, args.rx_model) == (256, 1024, "int8", "ising") else None),
         }
         line.update(extra)
         if world == 1 and not args.no_cpu:
@@ -592,6 +598,12 @@ def run_latgas(args):
                                         "achieved": 1.0 * bps * 2 * nsites * args.steps / (pair_ms * 1e-3) / 1e9,
                                         "accounting": "1 B (int8) per pair attempt: one read + one write of the lattice per 2N bonds"}
     out["pair_exchange"]["roofline"]["frac"] = out["pair_exchange"]["roofline"]["achieved"] / peak
+    pk = "resident_kernel" if one_launch and kname == "resident_kernel" else "pair_class_kernel"
+    pp = profiled(pk, "latgas512_pair") if (R, L, args.layout) == (512, 256, "int8") else None
+    out["pair_exchange"]["roofline"].update({"kernel": pk, "traffic": pp["traffic"] if pp else None,
+                                             "traffic_source": pp["source"] if pp else None,
+                                             "issue_active_pct": pp.get("issue_active_pct") if pp else None,
+                                             "alu_pipe_pct": pp.get("alu_pipe_pct") if pp else None})
     line = {"metric": "lattice-gas flip attempts/s", "value": out["flip"]["value"], "unit": "attempts/s", "n_gpus": 1,
             "steps": args.steps, "warmup": args.warmup, "repeats": out["flip"]["repeats"], "ms_per_step": out["flip"]["ms_per_step"],
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8" if args.layout == "int8" else "u64 (1 bit/site)",
@@ -646,9 +658,13 @@ def run_discs(args):
                 "parity": "ok" if ok else "FAILED", "clocks": clocks, "gpu_launches": len(ms),
                 "e2e": {"value": world * R * per / e2e, "unit": "attempts/s", "h2d_bytes_per_step": 320 * min(R, 256),
                         "d2h_bytes_per_step": 4 * 320 + R * (4 + 49 * 8), "note": "upload coordinates, one launch of trials, overlap flags and g(r) counts back"},
-                "roofline": {"bound": "latency", "achieved": None, "peak": None, "unit": "GB/s", "frac": None, "traffic": None,
-                             "note": "320 B of state per replica live in registers: no HBM roof; one warp per replica, float64 "
-                                     "with explicit rounding; issue-slot utilisation in profiles/README.md"}}
+                "roofline": {"bound": "issue", "achieved": None, "peak": None, "unit": "GB/s", "frac": None,
+                             "traffic": (profiled("discs_run_kernel", "discs8192") or {}).get("traffic") if args.disc_replicas == 8192 else None,
+                             "issue_active_pct": (profiled("discs_run_kernel", "discs8192") or {}).get("issue_active_pct"),
+                             "alu_pipe_pct": (profiled("discs_run_kernel", "discs8192") or {}).get("alu_pipe_pct"),
+                             "traffic_source": "profiles/r2_discs_summary.csv",
+                             "note": "320 B of state per replica live in registers: no HBM roof (SURVEY 8d); one warp per replica, "
+                                     "float64 with explicit rounding; the figure of merit is issue-slot utilisation"}}
         if not args.no_cpu:
             from oracle import refarm
             if refarm.available():
@@ -744,7 +760,8 @@ def run_single(args):
     lps, kname = lat.sweep_kernel_info()
     on_chip = kname in ("persistent_kernel", "pbatch_kernel", "resident_kernel")
     nlaunch = (K + 4095) // 4096 if on_chip else lps * K
-    roof = roofline_block(kname, 2.0 * bytes_per_site * nsites * K / nlaunch, ms / nlaunch, on_chip)
+    roof = roofline_block(kname, 2.0 * bytes_per_site * nsites * K / nlaunch, ms / nlaunch, on_chip,
+                          "single16k" if (L, args.layout) == (16384, "int8") or (L == 16384 and kname == "sweep_bits_rows_kernel") else None)
 
     extra = {}
     if not args.no_extras:

@@ -104,7 +104,7 @@ def test_parallel_mc_returns_per_replica_means(workdir):
 
 
 def test_fused_cycles_and_host_edits_on_a_word_aligned_ladder(workdir):
-    """64 x 128 lattices: the batch-resident kernel applies, so the engine runs whole stretches of exchange cycles
+    """Eight 256 x 512 lattices (2^20 sites: where PYMC_KERNEL_AUTO takes it): the batch-resident kernel applies, so the engine runs whole stretches of exchange cycles
     as one launch (TemperatureRX_MPI._advance).  The outcome must not depend on the kernel; and a host edit of a replica whose config object was created with another ``layout=`` than the
     first one must reach the batch of the engine (it used to be diverted to a private lattice)."""
     import py_mc_b200
@@ -112,7 +112,7 @@ def test_fused_cycles_and_host_edits_on_a_word_aligned_ladder(workdir):
     from py_mc_b200.mc import CanonicalMonteCarlo
     from py_mc_b200.mc_mpi import TemperatureRX_MPI
     from oracle import ising as o_ising
-    R, shape, seed = 6, (64, 128), 31
+    R, shape, seed = 8, (256, 512), 31
     kTs = np.linspace(2.2, 2.35, R)
 
     def engine(layouts, no_persistent=False):
