@@ -738,10 +738,21 @@ def run_single(args):
     clocks = sampler.stop()
     value = world * nsites * K / (ms * 1e-3)
 
-    # end to end through the C ABI with HOST buffers: upload, sweeps, download, exact sums -- every step
+    # end to end through the C ABI with HOST buffers: upload, sweeps, download, exact sums -- every step.
+    # "serial": one handle, every call waits for the one before.  Headline: the same jobs through
+    # py_mc_b200.pipeline.SweepPipeline (the public way to stream host lattices through the GPU): `depth` handles, each
+    # on its own stream, so that the PCIe copies of one lattice overlap the sweeps of another.  Every job still uploads
+    # its own 256 MiB from pinned host memory and downloads its configuration and exact sums inside the timed region.
+    from py_mc_b200.pipeline import SweepPipeline
     host = _cabi.pinned_empty((L, L), np.int8)
     lat.download(0, out=host)
-    e2e = {}
+    e2e, e2e_serial = {}, {}
+    depth = args.e2e_depth
+    bufs = [_cabi.pinned_empty((L, L), np.int8) for _ in range(depth)]
+    for k, b in enumerate(bufs):  # distinct inputs: the lattice a few sweeps apart
+        if k:
+            lat.sweep(2)
+        lat.download(0, out=b)
     for spp in sorted(set([1, args.e2e_sweeps])):
         reps = 3
         lat.upload(0, host)
@@ -754,7 +765,22 @@ def run_single(args):
             lat.sweep(spp)
             lat.download(0, out=host)
             lat.tracked()
-        e2e[spp] = world * nsites * spp * reps / grp.max(time.perf_counter() - t0)
+        e2e_serial[spp] = world * nsites * spp * reps / grp.max(time.perf_counter() - t0)
+        with SweepPipeline(_cabi.MODEL_ISING, L, L, thr[0], spp, depth=depth, seed=SEED, layout=layout, device=local_rank,
+                           kernel=KERNELS[args.kernel]) as pipe:
+            for k in range(depth):  # warm-up: first-call allocations of every handle
+                pipe.submit(bufs[k], bufs[k], first_sweep=0)
+            pipe.drain()
+            njobs, sums = 8 * depth, []  # fill and drain of the pipeline are inside the timed region
+            grp.barrier()
+            t0 = time.perf_counter()
+            for j in range(njobs):  # job j continues the lattice of job j - depth: host -> GPU -> host every time
+                r = pipe.submit(bufs[j % depth], bufs[j % depth], first_sweep=(1 + j // depth) * spp)
+                if r is not None:
+                    sums.append(r[2:])
+            sums += [r[2:] for r in pipe.drain()]
+            e2e[spp] = world * nsites * spp * njobs / grp.max(time.perf_counter() - t0)
+            assert len(sums) == njobs
 
     bytes_per_site = 1.0 if layout == _cabi.LAYOUT_INT8 else 0.125
     lps, kname = lat.sweep_kernel_info()
@@ -813,8 +839,12 @@ def run_single(args):
                                 "parallelism": "replicas only" if world > 1 else "single GPU"},
             "clocks": clocks,
             "e2e": {"value": e2e[args.e2e_sweeps], "unit": UNIT, "h2d_bytes_per_step": nsites, "d2h_bytes_per_step": nsites + 16,
-                    "sweeps_per_step": args.e2e_sweeps, "at_1_sweep_per_step": e2e[1],
-                    "note": "C-ABI upload(pinned host int8) + sweeps + download(host int8) + exact sums per step"},
+                    "sweeps_per_step": args.e2e_sweeps, "at_1_sweep_per_step": e2e[1], "pipeline_depth": depth,
+                    "serial": {"value": e2e_serial[args.e2e_sweeps], "at_1_sweep_per_step": e2e_serial[1],
+                               "note": "one handle, upload -> sweeps -> download -> sums strictly one after the other"},
+                    "note": "py_mc_b200.pipeline.SweepPipeline over the C ABI: every step uploads its lattice from pinned host "
+                            "int8, sweeps it, downloads the configuration and the exact sums; %d handles on their own "
+                            "streams, so the copies of one step overlap the sweeps of another" % depth},
             "gpu_launches": nlaunch * repeats, "roofline": roof,
         }
         line.update(extra)
@@ -851,6 +881,7 @@ def main():
     ap.add_argument("--kT", type=float, default=TC, help="temperature of the single-lattice workload (default T_c; "
                     "SURVEY 8d also asks for 2.0 and 5.0)")
     ap.add_argument("--e2e-sweeps", type=int, default=64)
+    ap.add_argument("--e2e-depth", type=int, default=4, help="lattices in flight in the end-to-end leg (handles / streams)")
     ap.add_argument("--also-bits", action="store_true", default=True)
     ap.add_argument("--no-also-bits", dest="also_bits", action="store_false")
     ap.add_argument("--no-extras", action="store_true", help="headline only (profiling runs)")

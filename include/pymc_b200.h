@@ -115,6 +115,13 @@ int pymc_debug_raise_async_error(pymc_handle *h, int which);
  * integer image of the reference's float64 config array (examples/ising2D.py:56-70). */
 int pymc_upload_config(pymc_handle *h, int replica, const int8_t *host, size_t nsites);
 int pymc_download_config(pymc_handle *h, int replica, int8_t *host, size_t nsites);
+/* The same two calls without the wait at the end: they only enqueue the copy and the layout kernel on the handle's
+ * stream and return.  `host` must be page-locked (pymc_host_alloc) and must stay untouched (upload) / is not valid
+ * (download) until pymc_synchronize on this handle returns; a failed in-kernel barrier is reported there.  With one
+ * handle per lattice in flight -- each handle has its own stream -- the copies of one lattice overlap the sweeps of
+ * another (py_mc_b200/pipeline.py).  No counterpart in the reference (its arrays never leave host memory). */
+int pymc_upload_config_async(pymc_handle *h, int replica, const int8_t *host, size_t nsites);
+int pymc_download_config_async(pymc_handle *h, int replica, int8_t *host, size_t nsites);
 /* Hot start on the device, rule of ising2D_config.prepare_random (examples/ising2D.py:64-70)
  * applied to stream domain 1 (see oracle/philox.py); all local replicas. */
 int pymc_init_random(pymc_handle *h);
@@ -148,6 +155,9 @@ int pymc_set_sweep_counter(pymc_handle *h, uint64_t counter);
  * pymc_get_tracked returns the incrementally tracked values (energy += dE, mc.py:177). */
 int pymc_reduce_observables(pymc_handle *h, int64_t *bond, int64_t *second);
 int pymc_get_tracked(pymc_handle *h, int64_t *bond, int64_t *second);
+/* pymc_get_tracked without the wait: pairs[2*r] = bond, pairs[2*r+1] = second of local replica r, in page-locked
+ * host memory, valid once pymc_synchronize on this handle has returned. */
+int pymc_get_tracked_async(pymc_handle *h, int64_t *pairs);
 
 /* No counterpart in the reference (it has no device memory to manage).  Same results and same
  * side effect as pymc_reduce_observables, for callers that must not allocate while running: a

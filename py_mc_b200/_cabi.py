@@ -33,6 +33,7 @@ SYMBOLS = [
     "pymc_slab_push_halos", "pymc_slab_status",
     "pymc_discs_timer", "pymc_stats_reset", "pymc_stats_accumulate", "pymc_stats_get",
     "pymc_debug_raise_async_error", "pymc_rx_ipc_export", "pymc_rx_connect",
+    "pymc_upload_config_async", "pymc_download_config_async", "pymc_get_tracked_async",
     "pymc_series_reset", "pymc_series_record", "pymc_series_count", "pymc_series_get", "pymc_series_put", "pymc_series_binning",
 ]
 
@@ -82,6 +83,9 @@ def _load():
         "pymc_debug_raise_async_error": [P, I],
         "pymc_upload_config": [P, I, P, C.c_size_t],
         "pymc_download_config": [P, I, P, C.c_size_t],
+        "pymc_upload_config_async": [P, I, P, C.c_size_t],
+        "pymc_download_config_async": [P, I, P, C.c_size_t],
+        "pymc_get_tracked_async": [P, P],
         "pymc_init_random": [P],
         "pymc_set_accept_tables": [P, P, I, I],
         "pymc_set_replica_to_T": [P, P, I],
@@ -260,6 +264,28 @@ class Lattices:
         assert out.dtype == np.int8 and out.flags.c_contiguous and out.size == int(np.prod(self._local_shape()))
         check(lib.pymc_download_config(self._h, replica, _ptr(out), out.size))
         return out
+
+    def upload_async(self, replica, pinned_int8):
+        """Enqueue the upload and return; ``pinned_int8`` (from ``pinned_empty``) must stay untouched until ``synchronize``."""
+        a = pinned_int8
+        if a.dtype != np.int8 or not a.flags.c_contiguous or a.shape != self._local_shape():
+            raise ValueError("upload_async needs a C-contiguous int8 array of shape %s" % (self._local_shape(),))
+        self._tracked_cache = None
+        check(lib.pymc_upload_config_async(self._h, replica, _ptr(a), a.size))
+
+    def download_async(self, replica, pinned_out):
+        """Enqueue the download into ``pinned_out`` (from ``pinned_empty``); its contents are valid after ``synchronize``."""
+        a = pinned_out
+        if a.dtype != np.int8 or not a.flags.c_contiguous or a.shape != self._local_shape():
+            raise ValueError("download_async needs a C-contiguous int8 array of shape %s" % (self._local_shape(),))
+        check(lib.pymc_download_config_async(self._h, replica, _ptr(a), a.size))
+
+    def tracked_async(self, pinned_pairs):
+        """Enqueue the copy of the tracked (bond, second) pairs into ``pinned_pairs`` (int64 [nreplicas][2])."""
+        a = pinned_pairs
+        if a.dtype != np.int64 or not a.flags.c_contiguous or a.size != 2 * self.nreplicas:
+            raise ValueError("tracked_async needs a C-contiguous int64 array of %d entries" % (2 * self.nreplicas))
+        check(lib.pymc_get_tracked_async(self._h, _ptr(a)))
 
     def init_random(self):
         self._tracked_cache = None

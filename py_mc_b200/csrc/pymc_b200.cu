@@ -1062,7 +1062,7 @@ static int ensure_staging(pymc_handle *h) {
     return PYMC_OK;
 }
 
-int pymc_upload_config(pymc_handle *h, int replica, const int8_t *host, size_t nsites) {
+static int upload_config(pymc_handle *h, int replica, const int8_t *host, size_t nsites, bool wait) {
     ENTER(h);
     REQUIRE(host, PYMC_ERR_BADARG, "pymc_upload_config: null host pointer");
     REQUIRE(replica >= 0 && replica < h->p.nreplicas, PYMC_ERR_BADARG, "pymc_upload_config: replica %d of %d", replica,
@@ -1086,12 +1086,20 @@ int pymc_upload_config(pymc_handle *h, int replica, const int8_t *host, size_t n
     else
         pack_kernel<PYMC_LAYOUT_INT8><<<grid, 128, 0, h->stream>>>(L, replica, h->staging);
     CUDA_TRY(cudaGetLastError());
-    CUDA_TRY(cudaStreamSynchronize(h->stream));  // the host buffer may be reused on return
+    if (wait) CUDA_TRY(cudaStreamSynchronize(h->stream));  // the host buffer may be reused on return
     h->dirty = true;
     return PYMC_OK;
 }
 
-int pymc_download_config(pymc_handle *h, int replica, int8_t *host, size_t nsites) {
+int pymc_upload_config(pymc_handle *h, int replica, const int8_t *host, size_t nsites) {
+    return upload_config(h, replica, host, nsites, true);
+}
+
+int pymc_upload_config_async(pymc_handle *h, int replica, const int8_t *host, size_t nsites) {
+    return upload_config(h, replica, host, nsites, false);
+}
+
+static int download_config(pymc_handle *h, int replica, int8_t *host, size_t nsites, bool wait) {
     ENTER(h);
     REQUIRE(host, PYMC_ERR_BADARG, "pymc_download_config: null host pointer");
     REQUIRE(replica >= 0 && replica < h->p.nreplicas, PYMC_ERR_BADARG, "pymc_download_config: replica %d of %d",
@@ -1112,9 +1120,18 @@ int pymc_download_config(pymc_handle *h, int replica, int8_t *host, size_t nsite
 #undef CALL_UNPACK
     CUDA_TRY(cudaGetLastError());
     CUDA_TRY(cudaMemcpyAsync(host, h->staging, nsites, cudaMemcpyDeviceToHost, h->stream));
+    if (!wait) return PYMC_OK;  // pymc_synchronize completes the copy and reports a failed barrier
     CUDA_TRY(cudaStreamSynchronize(h->stream));
     CHECK_ASYNC(h);
     return PYMC_OK;
+}
+
+int pymc_download_config(pymc_handle *h, int replica, int8_t *host, size_t nsites) {
+    return download_config(h, replica, host, nsites, true);
+}
+
+int pymc_download_config_async(pymc_handle *h, int replica, int8_t *host, size_t nsites) {
+    return download_config(h, replica, host, nsites, false);
 }
 
 static int rebase_tracked(pymc_handle *h);
@@ -1639,6 +1656,17 @@ int pymc_get_tracked(pymc_handle *h, int64_t *bond, int64_t *second) {
         if (rc) return rc;
     }
     return fetch_pairs(h, h->tracked, bond, second);
+}
+
+int pymc_get_tracked_async(pymc_handle *h, int64_t *pairs) {
+    ENTER(h);
+    REQUIRE(pairs, PYMC_ERR_BADARG, "pymc_get_tracked_async: null pointer");
+    if (h->dirty) {
+        int rc = rebase_tracked(h);
+        if (rc) return rc;
+    }
+    CUDA_TRY(cudaMemcpyAsync(pairs, h->tracked, (size_t)h->p.nreplicas * 16, cudaMemcpyDeviceToHost, h->stream));
+    return PYMC_OK;
 }
 
 int pymc_propose(pymc_handle *h, int replica, const int32_t *x, const int32_t *y, int n, int32_t *site_out,
