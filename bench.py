@@ -35,7 +35,7 @@ TC = 2.269185314213022
 SEED = 20260611
 MIN_TIMED_MS = 200.0  # a timed region shorter than this is repeated inside the events ("repeats")
 
-KERNELS = {"auto": 0, "generic": 1, "two_pass": 2, "resident": 3, "persistent": 4, "pbatch": 5}  # PYMC_KERNEL_*
+KERNELS = {"auto": 0, "generic": 1, "two_pass": 2, "resident": 3, "persistent": 4, "pbatch": 5, "rowstream": 6}  # PYMC_KERNEL_*
 
 
 def measured_peak_hbm():
@@ -807,7 +807,7 @@ def run_single(args):
             n3 = max(50, K)
             ms3, _ = timed(lat3, lambda: [lat3.sweep(1) for _ in range(n3)])  # single-sweep calls: the fused kernel
             extra["one_sweep_per_launch"] = {"value": world * nsites * n3 / (ms3 * 1e-3), "unit": UNIT, "ms_per_step": ms3 / n3,
-                                             "kernel": "sweep_fused_i8_kernel" if layout == _cabi.LAYOUT_INT8 else "sweep_bits_rows_kernel",
+                                             "kernel": lat3.sweep_kernel_for(1)[1],
                                              "roofline_frac": 2.0 * bytes_per_site * nsites / (ms3 / n3 * 1e-3) / 1e9 / measured_peak_hbm()[0]}
             lat3.close()
         except Exception as exc:

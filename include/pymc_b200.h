@@ -57,11 +57,15 @@ typedef enum {
                                 /* block of a cooperative launch, grid barrier per colour pass) for all   */
                                 /* sweeps of a call; needs lenY % 128 == 0 and lenX*lenY/8 bytes within    */
                                 /* the GPU's shared memory                                                */
-    PYMC_KERNEL_PBATCH = 5      /* the rows of ALL replicas of the handle cut into one piece per SM and    */
+    PYMC_KERNEL_PBATCH = 5,     /* the rows of ALL replicas of the handle cut into one piece per SM and    */
                                 /* kept in shared memory for all sweeps -- and, on one GPU, all replica   */
                                 /* exchanges -- of a call; neighbour flags instead of grid barriers.      */
                                 /* Needs lenY % 128 == 0 and nreplicas*lenX*lenY/8 bytes within the GPU's  */
                                 /* shared memory.  AUTO takes it from 2^20 sites on (calls of >= 2 sweeps) */
+    PYMC_KERNEL_ROWSTREAM = 6   /* int8 layout, one sweep per launch: a block walks down a piece of whole rows   */
+                                /* that stream through shared memory (bulk asynchronous copies), both colours in   */
+                                /* one pass.  Needs lenY = 128 * 2^k (1024 .. 65536).  AUTO uses it for the sweeps  */
+                                /* the resident kernels do not take (single-sweep calls, lattices beyond the chip) */
 } pymc_kernel;
 
 /* Number of acceptance-table entries per temperature: Ising 5 (index = number of aligned
@@ -143,6 +147,9 @@ int pymc_sweep(pymc_handle *h, int64_t nsweeps);
 /* Which kernel pymc_sweep uses for this handle and how many launches one sweep takes (1 for the
  * fused two-colour int8 kernel, otherwise 2); for benchmarks and logs. */
 int pymc_sweep_kernel_info(pymc_handle *h, int *launches_per_sweep, const char **kernel_name);
+/* The same for a call of exactly nsweeps sweeps: calls of a single sweep take a per-sweep kernel (the row-streaming or
+ * the tiled int8 kernel, the bit-packed row kernel) even on handles whose longer calls stay on chip. */
+int pymc_sweep_kernel_for(pymc_handle *h, int64_t nsweeps, int *launches_per_sweep, const char **kernel_name);
 int pymc_get_sweep_counter(pymc_handle *h, uint64_t *counter);
 int pymc_set_sweep_counter(pymc_handle *h, uint64_t counter);
 

@@ -13,7 +13,7 @@ from ._build import LIBPATH
 ABI_VERSION = 1
 MODEL_ISING, MODEL_LATGAS = 0, 1
 LAYOUT_INT8, LAYOUT_BITS = 0, 1
-KERNEL_AUTO, KERNEL_GENERIC, KERNEL_TWO_PASS, KERNEL_RESIDENT, KERNEL_PERSISTENT, KERNEL_PBATCH = 0, 1, 2, 3, 4, 5
+KERNEL_AUTO, KERNEL_GENERIC, KERNEL_TWO_PASS, KERNEL_RESIDENT, KERNEL_PERSISTENT, KERNEL_PBATCH, KERNEL_ROWSTREAM = 0, 1, 2, 3, 4, 5, 6
 NCLASS = {MODEL_ISING: 5, MODEL_LATGAS: 10}
 
 # every symbol include/pymc_b200.h declares (tests check the library exports all of them)
@@ -33,7 +33,7 @@ SYMBOLS = [
     "pymc_slab_push_halos", "pymc_slab_status",
     "pymc_discs_timer", "pymc_stats_reset", "pymc_stats_accumulate", "pymc_stats_get",
     "pymc_debug_raise_async_error", "pymc_rx_ipc_export", "pymc_rx_connect",
-    "pymc_upload_config_async", "pymc_download_config_async", "pymc_get_tracked_async",
+    "pymc_upload_config_async", "pymc_download_config_async", "pymc_get_tracked_async", "pymc_sweep_kernel_for",
     "pymc_series_reset", "pymc_series_record", "pymc_series_count", "pymc_series_get", "pymc_series_put", "pymc_series_binning",
 ]
 
@@ -92,6 +92,7 @@ def _load():
         "pymc_get_replica_to_T": [P, P, I],
         "pymc_sweep": [P, I64],
         "pymc_sweep_kernel_info": [P, C.POINTER(I), C.POINTER(C.c_char_p)],
+        "pymc_sweep_kernel_for": [P, I64, C.POINTER(I), C.POINTER(C.c_char_p)],
         "pymc_get_sweep_counter": [P, C.POINTER(C.c_uint64)],
         "pymc_set_sweep_counter": [P, C.c_uint64],
         "pymc_reduce_observables": [P, P, P],
@@ -314,6 +315,12 @@ class Lattices:
         """(launches per sweep, kernel name) of the sweep path this handle uses."""
         n, name = C.c_int(0), C.c_char_p()
         check(lib.pymc_sweep_kernel_info(self._h, C.byref(n), C.byref(name)))
+        return n.value, name.value.decode()
+
+    def sweep_kernel_for(self, nsweeps):
+        """(launches per sweep, kernel name) of a call of exactly ``nsweeps`` sweeps."""
+        n, name = C.c_int(0), C.c_char_p()
+        check(lib.pymc_sweep_kernel_for(self._h, int(nsweeps), C.byref(n), C.byref(name)))
         return n.value, name.value.decode()
 
     @property

@@ -23,6 +23,7 @@
 #include "pmc_resident.cuh"
 #include "pmc_persist.cuh"
 #include "pmc_pbatch.cuh"
+#include "pmc_rowstream.cuh"
 #include "pmc_discs.cuh"
 
 // largest bit image (bytes) for which PYMC_KERNEL_AUTO takes the resident kernel: several blocks per SM
@@ -38,6 +39,13 @@ static const size_t PBATCH_AUTO_MIN_SITES = (size_t)1024 * 1024;
 // ... but a single lattice below 4096 x 4096 gives a block so few rows that a pass is shorter than the flag
 // hand-shake between neighbouring blocks; there K11 is as good or better (profiles/r2_pbatch_probe.json)
 static const size_t PBATCH_SINGLE_MIN_SITES = (size_t)4096 * 4096;
+// PYMC_KERNEL_AUTO runs the sweeps the resident kernels do not take (single-sweep calls, lattices beyond the chip) on the
+// row-streaming kernel K13 instead of the tiled one from this many sites (all replicas together) and this many words per
+// colour row on.  Measured (profiles/r2_rowstream_probe.json, ms per sweep K13 / tiled): 16384^2 0.1697 / 0.1760,
+// 16 x 4096^2 0.1732 / 0.1761, 8192^2 0.0499 / 0.0501; below that a piece per resident block is too short (4096^2 0.0226 /
+// 0.0169) and narrow rows put too many row tasks into one iteration (256 x 1024^2: 0.223 / 0.174).
+static const size_t ROWSTREAM_AUTO_MIN_SITES = (size_t)1 << 27;
+static const int ROWSTREAM_AUTO_MIN_NW = 32;
 #ifndef PMC_PERSIST_AUTO
 #define PMC_PERSIST_AUTO 1  // 0: only PYMC_KERNEL_PERSISTENT selects the persistent kernel
 #endif
@@ -611,6 +619,35 @@ __global__ void slab_sync_kernel(volatile unsigned long long *my_flags, unsigned
     __threadfence_system();
 }
 
+// K13: pieces per replica.  Every block recomputes two rows of colour 0 and spends about one iteration on its
+// prologue, so long pieces are cheap; but the grid should fill whole waves of resident blocks.  Score = wave
+// efficiency x 2n / (2n + Q + 2) (n rows per piece, Q row tasks per iteration); 0 if the shape cannot be streamed.
+static int rs_choose_pieces(int lenX, int nk, int nrep, int sms, int smem_per_block_optin) {
+    RSParams p;
+    if (!rs_make_params(lenX, nk, 1, p)) return 0;
+    const size_t smem = rs_smem_bytes(p) + 4096;  // + static shared memory and the per-block reserve
+    if (smem > (size_t)smem_per_block_optin) return 0;
+    int per_sm = (int)((size_t)228 * 1024 / smem);
+    if (per_sm > 1024 / RS_THREADS) per_sm = 1024 / RS_THREADS;  // 64 registers per thread
+    if (per_sm < 1) per_sm = 1;
+    const long slots = (long)sms * per_sm;
+    const int maxP = lenX / rs_min_rows(p.Q);
+    int best = 0;
+    double best_score = 0.0;
+    for (int P = 1; P <= maxP && (long)P * nrep <= 64 * slots; ++P) {
+        const long blocks = (long)P * nrep, waves = (blocks + slots - 1) / slots;
+        const double n = (double)lenX / P;
+        const double score = (double)blocks / (double)(waves * slots) * (2.0 * n) / (2.0 * n + p.Q + 2.0);
+        if (score > best_score + 1e-9) {
+            best_score = score;
+            best = P;
+        }
+    }
+    const char *force = getenv("PYMC_ROWSTREAM_PIECES");  // experiments
+    if (force && atoi(force) >= 1 && atoi(force) <= maxP) best = atoi(force);
+    return best;
+}
+
 // ------------------------------------------------------------------------------------------
 // handle
 // ------------------------------------------------------------------------------------------
@@ -683,6 +720,11 @@ struct pymc_handle {
     unsigned int *peer_xflags[PB_MAXRANKS];
     int32_t *pb_maps;              // [2 maps][2 parities][ntemps] replica <-> temperature maps of the kernel
     bool pb_attr[2];
+    // K13 (pmc_rowstream.cuh): one sweep per launch with the rows streamed through shared memory (int8 layout)
+    bool rowstream;                // single sweeps (and sweeps the resident kernels do not take) run on the row-streaming kernel
+    RSParams rs;
+    size_t rs_smem;
+    bool rs_attr[2];
     // Time-outs of the in-kernel barriers are raised by the kernels in two ints of mapped pinned host memory, so
     // that every entry point which synchronises and returns data can look at them for free (check_async_errors).
     volatile int *err_host;        // [0] persistent kernel, [1] slab neighbour barrier
@@ -770,6 +812,47 @@ static int check_async_errors(pymc_handle *h, const char *where) {
         int _rc = check_async_errors((h), __func__);     \
         if (_rc) return _rc;                             \
     } while (0)
+
+// K13: one launch per sweep, out of place (the two int8 buffers swap after every sweep).
+template <int MODEL, int NWL2>
+static int rowstream_launch(pymc_handle *h, const Lat &L, const dim3 &grid, bool set_attr) {
+    if (set_attr)
+        CUDA_TRY(cudaFuncSetAttribute(rowstream_kernel<MODEL, NWL2, Lat>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->rs_smem));
+    rowstream_kernel<MODEL, NWL2, Lat><<<grid, RS_THREADS, h->rs_smem, h->stream>>>(L, h->rs, h->i8, h->i8_alt, h->sweep_counter,
+                                                                                  h->persist_err);
+    return PYMC_OK;
+}
+
+template <int MODEL>
+static int rowstream_dispatch(pymc_handle *h, const Lat &L, const dim3 &grid, bool set_attr) {
+    switch (h->rs.nw_log2) {
+#define RS_CASE(K) \
+    case K:        \
+        if constexpr ((RS_THREADS >> K) >= 1 && (RS_THREADS >> K) <= RS_MAXQ) return rowstream_launch<MODEL, K>(h, L, grid, set_attr); \
+        break;
+        RS_CASE(2) RS_CASE(3) RS_CASE(4) RS_CASE(5) RS_CASE(6) RS_CASE(7) RS_CASE(8) RS_CASE(9)
+#undef RS_CASE
+    }
+    return fail(PYMC_ERR_UNSUPPORTED, "row-streaming kernel: no instantiation for %d words per row", h->rs.nw);
+}
+
+static int launch_rowstream(pymc_handle *h, const Lat &L, int64_t nsweeps) {
+    if (nsweeps <= 0) return PYMC_OK;
+    const int m = h->p.model == PYMC_MODEL_ISING ? 0 : 1;
+    if (!h->i8_alt) CUDA_TRY(cudaMalloc(&h->i8_alt, (size_t)h->p.nreplicas * 2 * h->p.lenX * h->nk));
+    const dim3 grid(h->rs.pieces, h->p.nreplicas);
+    for (int64_t s = 0; s < nsweeps; ++s) {
+        const int rc = m ? rowstream_dispatch<MODEL_LATGAS>(h, L, grid, !h->rs_attr[m]) : rowstream_dispatch<MODEL_ISING>(h, L, grid, !h->rs_attr[m]);
+        if (rc) return rc;
+        h->rs_attr[m] = true;
+        int8_t *tmp = h->i8;
+        h->i8 = h->i8_alt;
+        h->i8_alt = tmp;
+        h->sweep_counter++;
+    }
+    CUDA_TRY(cudaGetLastError());
+    return PYMC_OK;
+}
 
 extern "C" {
 
@@ -875,7 +958,7 @@ int pymc_create(const pymc_params *p, pymc_handle **out) {
     h->nw = (h->nk + 63) / 64;
     h->nclass = p->model == PYMC_MODEL_ISING ? PYMC_NCLASS_ISING : PYMC_NCLASS_LATGAS;
     REQUIRE((uint64_t)p->lenX * h->nw < (1ull << 31), PYMC_ERR_UNSUPPORTED, "pymc_create: lattice too large");
-    REQUIRE(p->kernel >= PYMC_KERNEL_AUTO && p->kernel <= PYMC_KERNEL_PBATCH, PYMC_ERR_BADARG, "pymc_create: kernel %d",
+    REQUIRE(p->kernel >= PYMC_KERNEL_AUTO && p->kernel <= PYMC_KERNEL_ROWSTREAM, PYMC_ERR_BADARG, "pymc_create: kernel %d",
             p->kernel);
 
     DeviceGuard guard(p->device);
@@ -976,6 +1059,22 @@ int pymc_create(const pymc_params *p, pymc_handle **out) {
             h->pb_blocks = blocks;
             h->pb_threads = (int)threads;
             h->pb_smem = rows_bytes;
+        }
+        // K13 (pmc_rowstream.cuh): int8 sweeps one at a time, rows streamed through shared memory
+        {
+            const int pieces = p->layout == PYMC_LAYOUT_INT8 ? rs_choose_pieces(p->lenX, h->nk, p->nreplicas, sms, smem) : 0;
+            const bool rs_ok = pieces > 0 && rs_make_params(p->lenX, h->nk, pieces, h->rs);
+            if (p->kernel == PYMC_KERNEL_ROWSTREAM && !rs_ok) {
+                delete h;
+                return fail(PYMC_ERR_UNSUPPORTED,
+                            "pymc_create: the row-streaming kernel needs the int8 layout, lenY = 128 * 2^k with %d <= lenY/128 <= %d "
+                            "and at least 2 * %d / (lenY/128) + 2 rows", RS_THREADS / RS_MAXQ, RS_THREADS, RS_THREADS);
+            }
+            const char *off = getenv("PYMC_NO_ROWSTREAM");  // escape hatch: keep AUTO on the tiled per-sweep kernel
+            h->rowstream = rs_ok && (p->kernel == PYMC_KERNEL_ROWSTREAM ||
+                                     (p->kernel == PYMC_KERNEL_AUTO && !(off && off[0] == '1') && !h->resident &&
+                                      (size_t)p->nreplicas * p->lenX * p->lenY >= ROWSTREAM_AUTO_MIN_SITES && h->nw >= ROWSTREAM_AUTO_MIN_NW));
+            h->rs_smem = rs_ok ? rs_smem_bytes(h->rs) : 0;
         }
         int threads = (int)(((size_t)p->lenX * h->nw / 2 + 31) / 32 * 32);
         h->resident_threads = threads < 128 ? 128 : (threads > RESIDENT_MAX_THREADS ? RESIDENT_MAX_THREADS : threads);
@@ -1456,19 +1555,21 @@ static bool uses_fused(const pymc_handle *h) {
 
 static int slab_sync_async(pymc_handle *h);
 
-int pymc_sweep_kernel_info(pymc_handle *h, int *launches_per_sweep, const char **kernel_name) {
-    REQUIRE(h, PYMC_ERR_BADARG, "pymc_sweep_kernel_info: null handle");
-    const char *name;
+// the kernel a call of pymc_sweep(h, nsweeps) runs on (the order of the tests is that of pymc_sweep)
+static const char *sweep_kernel_for(const pymc_handle *h, int64_t nsweeps, int *launches_per_sweep) {
     int n = 2;
-    if (h->pbatch) {
+    const char *name;
+    if (h->pbatch && nsweeps >= 2 && !h->slab) {
         name = "pbatch_kernel";  // one cooperative launch per call of >= 2 sweeps (and per exchange cycle on one GPU)
         n = 1;
-    } else if (h->persist) {
+    } else if (h->resident || (h->resident_big && nsweeps >= 2)) {
+        name = "resident_kernel";  // one launch per call (up to 4096 sweeps), not per sweep
+        n = 1;
+    } else if (h->persist && nsweeps >= 2) {
         name = "persistent_kernel";  // one cooperative launch per call of >= 2 sweeps
         n = 1;
-    } else if (h->resident || h->resident_big) {
-        // one launch per call (up to 4096 sweeps), not per sweep; resident_big: calls of a single sweep take the fused kernel
-        name = "resident_kernel";
+    } else if (h->rowstream && !h->slab) {
+        name = "rowstream_kernel";
         n = 1;
     } else if (uses_fused(h)) {
         name = "sweep_fused_i8_kernel";
@@ -1481,6 +1582,19 @@ int pymc_sweep_kernel_info(pymc_handle *h, int *launches_per_sweep, const char *
         name = "sweep_word_kernel";
     }
     if (launches_per_sweep) *launches_per_sweep = n;
+    return name;
+}
+
+int pymc_sweep_kernel_info(pymc_handle *h, int *launches_per_sweep, const char **kernel_name) {
+    REQUIRE(h, PYMC_ERR_BADARG, "pymc_sweep_kernel_info: null handle");
+    const char *name = sweep_kernel_for(h, 1 << 20, launches_per_sweep);  // a call of many sweeps
+    if (kernel_name) *kernel_name = name;
+    return PYMC_OK;
+}
+
+int pymc_sweep_kernel_for(pymc_handle *h, int64_t nsweeps, int *launches_per_sweep, const char **kernel_name) {
+    REQUIRE(h, PYMC_ERR_BADARG, "pymc_sweep_kernel_for: null handle");
+    const char *name = sweep_kernel_for(h, nsweeps, launches_per_sweep);
     if (kernel_name) *kernel_name = name;
     return PYMC_OK;
 }
@@ -1506,6 +1620,7 @@ int pymc_sweep(pymc_handle *h, int64_t nsweeps) {
         if (rc) return rc;
     }
     Lat L = make_lat(h);
+    if (h->rowstream && !h->slab) return launch_rowstream(h, L, nsweeps);
     dim3 grid((h->p.lenX * h->nw + 127) / 128, h->p.nreplicas);
     // K1 tiled int8 kernel: needs whole words (lenY % 128 == 0); tile = TH rows x TW words, TW | nw
     const bool tiled = h->p.layout == PYMC_LAYOUT_INT8 && h->p.kernel != PYMC_KERNEL_GENERIC && h->nk % 64 == 0;

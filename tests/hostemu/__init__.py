@@ -13,7 +13,7 @@ SRC = os.path.join(HERE, "hostemu.cpp")
 OUTDIR = os.path.join(HERE, "_build")
 LIB = os.path.join(OUTDIR, "libhostemu.so")
 DEPS = [SRC, os.path.join(HERE, "cuda_host_shim.h")] + [os.path.join(CSRC, f) for f in
-                                                         ("pmc_stream.cuh", "pmc_core.cuh", "pmc_pair.cuh", "pmc_persist.cuh", "pmc_pbatch.cuh")]
+                                                         ("pmc_stream.cuh", "pmc_core.cuh", "pmc_pair.cuh", "pmc_persist.cuh", "pmc_pbatch.cuh", "pmc_rowstream.cuh", "pmc_pack.cuh")]
 
 
 def build(force=False):
@@ -41,6 +41,8 @@ class HostCore:
                                                     C.c_uint64, C.c_int, C.c_int, C.c_int, LL, LL]
         self.lib.hostemu_pbatch_sweeps.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_uint64,
                                                    C.c_uint32, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        self.lib.hostemu_rowstream_sweep.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_uint32,
+                                                     C.c_uint64, C.c_int, LL, LL]
         self.lib.hostemu_pair_sweep.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_uint32,
                                                 C.c_uint64, C.c_uint32, LL]
 
@@ -53,6 +55,21 @@ class HostCore:
                                              replica, sweep0, nsweeps, nblocks, nthreads, C.byref(dB), C.byref(dS))
         assert rc == 0, rc
         return dB.value, dS.value
+
+    def rowstream_sweep(self, model, img, thr, seed, replica, sweep, pieces):
+        """One sweep (in place) through the row-streaming kernel's schedule and per-thread phases with `pieces` emulated
+        blocks; returns (dB, dS).  A negative return code of the emulation (a hazard it checks for) raises."""
+        assert img.dtype == np.int8 and img.flags.c_contiguous
+        t = np.ascontiguousarray(thr, dtype=np.uint32)
+        dB, dS = C.c_longlong(0), C.c_longlong(0)
+        rc = self.lib.hostemu_rowstream_sweep(model, img.ctypes.data, img.shape[0], img.shape[1], t.ctypes.data, seed, replica,
+                                              sweep, pieces, C.byref(dB), C.byref(dS))
+        if rc:
+            raise RuntimeError("rowstream emulation: code %d" % rc)
+        return dB.value, dS.value
+
+    def rowstream_threads(self):
+        return self.lib.hostemu_rowstream_threads()
 
     def pbatch_sweeps(self, model, imgs, thr, seed, rep_offset, sweep0, nsweeps, nblocks, nthreads):
         """nsweeps sweeps of all replicas imgs[nrep, lenX, lenY] (in place) through the batch-resident kernel's logic with

@@ -11,7 +11,9 @@
 #include "../../py_mc_b200/csrc/pmc_pair.cuh"
 #include "../../py_mc_b200/csrc/pmc_persist.cuh"
 #include "../../py_mc_b200/csrc/pmc_pbatch.cuh"
+#include "../../py_mc_b200/csrc/pmc_rowstream.cuh"
 
+#include <cstring>
 #include <vector>
 
 using namespace pmc;
@@ -332,3 +334,168 @@ extern "C" int hostemu_pbatch_sweeps(int model, int8_t *imgs, int nrep, int lenX
         return pbatch_sweeps<MODEL_LATGAS>(imgs, nrep, lenX, lenY, thr, 10, seed, rep_offset, sweep0, nsweeps, nblocks, nthreads, sums);
     return -1;
 }
+
+namespace {
+
+// The row-streaming kernel's schedule and per-thread phases (pmc_rowstream.cuh) on the host: piece after piece,
+// iteration after iteration, thread after thread, with the bulk copies replaced by memcpy at the point where the kernel
+// issues them.  Besides the result (compared by the caller with the plain sweep) it checks what the sequential
+// order of the emulation would otherwise hide: every ring slot read holds the row the reader means, in the state it
+// needs (old / new), written in an EARLIER iteration; no slot is written in the iteration in which another task
+// reads it; a staging slot is refilled only after it has been packed.
+template <int MODEL, int NWL2>
+int rowstream_sweep(Image &im, const uint32_t *thr, uint64_t seed, uint32_t replica, uint64_t sweep, int pieces, long long *dB,
+                    long long *dS) {
+    const int lenX = im.lenX, nk = im.lenY / 2;
+    RSParams p;
+    if (!rs_make_params(lenX, nk, pieces, p)) return -2;
+    if (p.nw_log2 != NWL2) return -2;
+
+    const int nw = p.nw, RW = p.rw, T = RS_THREADS;
+    // colour-split int8 source and destination [2][lenX][nk]
+    std::vector<int8_t> src((size_t)2 * lenX * nk), dst((size_t)2 * lenX * nk, 77);
+    for (int i = 0; i < lenX; ++i)
+        for (int j = 0; j < im.lenY; ++j) src[((size_t)((i + j) & 1) * lenX + i) * nk + (j >> 1)] = im.p[(size_t)i * im.lenY + j];
+    uint32_t row[PLAN_WORDS];
+    Plan<MODEL>::build_row(thr, row);
+    const uint32_t(&rowref)[PLAN_WORDS] = row;
+    Plan<MODEL> plan;
+    plan.init(ParamRow{rowref});
+    const PhiloxKey key = make_key(seed);
+    int tdB = 0, tdS = 0;
+    for (int piece = 0; piece < pieces; ++piece) {
+        int a, n;
+        rs_piece(p, piece, a, n);
+        if (n < rs_min_rows(p.Q)) return -3;
+        const int ntasks = 2 * n + 2, npacks = 2 * n + 6;
+        const int niter = p.prologue + ((ntasks + p.Q - 1) >> p.q_log2) + 1;
+        std::vector<uint4> stage((size_t)RS_STAGES * T * 4);
+        std::vector<int> stage_group(RS_STAGES, -1), stage_packed(RS_STAGES, 1);
+        std::vector<uint64_t> W((size_t)(2 * RW + 1) * nw, 0xAAAAAAAAAAAAAAAAull);
+        // per ring slot: index held, state (0 old, 1 new), iteration of the last write / of the last read by another task
+        struct Slot {
+            int idx = -1000, state = -1, wr = -1, rd = -1;
+        };
+        std::vector<Slot> r0(RW), r1(RW);
+        RSCompute ct[2][RS_MAXQ];
+        RSMove pt[2][RS_MAXQ], ut[2][RS_MAXQ];
+        auto build_tables = [&](int it, int buf) {
+            const int kc = it - p.prologue;
+            for (int k = 0; k < p.Q; ++k) {
+                ct[buf][k] = rs_build_compute(p, a, n, (kc << p.q_log2) + k);
+                pt[buf][k] = rs_build_pack(p, n, (it << p.q_log2) + k);
+                ut[buf][k] = rs_build_unpack(p, a, n, ((kc - 1) << p.q_log2) + k);
+            }
+        };
+        auto issue_group = [&](int g) -> int {
+            const int first = g << p.q_log2;
+            if (first >= npacks) return 0;
+            const int slot = g % RS_STAGES;
+            if (!stage_packed[slot]) return -10;  // refilled before it was packed
+            const int nvalid = npacks - first < p.Q ? npacks - first : p.Q;
+            for (int k = 0; k < nvalid; ++k) {
+                const RSTask task = rs_pack_task(p, a, n, first + k);
+                const int colour = (task.info >> 16) & 1;
+                memcpy(reinterpret_cast<int8_t *>(stage.data()) + (size_t)slot * T * 64 + (size_t)k * nk,
+                       src.data() + ((size_t)colour * lenX + task.row) * nk, nk);
+            }
+            stage_group[slot] = g;
+            stage_packed[slot] = 0;
+            return 0;
+        };
+        build_tables(0, 0);
+        for (int g = 0; g < RS_STAGES; ++g)
+            if (int rc = issue_group(g)) return rc;
+        for (int it = 0; it < niter; ++it) {
+            const int kc = it - p.prologue, buf = it & 1;
+            // ---- unpack of what the previous iteration computed
+            if (kc >= 1) {
+                for (int q = 0; q < p.Q; ++q) {
+                    int colour, idx;
+                    if (!rs_task_index(p, n, ((kc - 1) << p.q_log2) + q, colour, idx)) continue;
+                    if (colour == 0 && (idx < 1 || idx > n)) continue;
+                    Slot &sl = colour ? r1[(idx + 2) % p.rw] : r0[idx % p.rw];
+                    if (sl.idx != (colour ? idx + 2 : idx) || sl.state != 1 || sl.wr != it - 1) return -20;
+                    sl.rd = it;
+                }
+                for (int t = 0; t < T; ++t) rs_unpack<MODEL, NWL2>(ut[buf], W.data(), reinterpret_cast<uint4 *>(dst.data()), t);
+            }
+            // ---- compute
+            if (kc >= 0 && (kc << p.q_log2) < ntasks) {
+                for (int q = 0; q < p.Q; ++q) {  // reads first (all tasks of the iteration run concurrently on the GPU)
+                    int colour, idx;
+                    if (!rs_task_index(p, n, (kc << p.q_log2) + q, colour, idx)) continue;
+                    for (int d = 0; d < 3; ++d) {
+                        // c0[m] reads OLD c1h[m .. m+2]; c1[j] reads NEW c0[j .. j+2]
+                        Slot &sl = colour ? r0[(idx + d) % p.rw] : r1[(idx + d) % p.rw];
+                        if (sl.idx != idx + d || sl.state != (colour ? 1 : 0) || sl.wr >= it) return -30 - colour;
+                        sl.rd = it;
+                    }
+                }
+                for (int q = 0; q < p.Q; ++q) {  // then the writes
+                    int colour, idx;
+                    if (!rs_task_index(p, n, (kc << p.q_log2) + q, colour, idx)) continue;
+                    Slot &sl = colour ? r1[(idx + 2) % p.rw] : r0[idx % p.rw];
+                    if (sl.idx != (colour ? idx + 2 : idx) || sl.state != 0 || sl.wr >= it || sl.rd >= it) return -40 - colour;
+                    sl.state = 1;
+                    sl.wr = it;
+                }
+                for (int t = 0; t < T; ++t)
+                    rs_compute<MODEL, NWL2>(ct[buf], W.data(), plan, replica, sweep, key, t, tdB, tdS);
+            }
+            // ---- pack
+            if ((it << p.q_log2) < npacks) {
+                const int slot = it % RS_STAGES;
+                if (stage_group[slot] != it) return -50;  // the copy for this group was never issued
+                for (int q = 0; q < p.Q; ++q) {
+                    int colour, idx;
+                    if (!rs_pack_index(n, (it << p.q_log2) + q, colour, idx)) continue;
+                    Slot &sl = colour ? r1[idx % p.rw] : r0[idx % p.rw];
+                    if (sl.wr >= it || sl.rd >= it) return -60;  // somebody uses this slot in this very iteration
+                    // what it held must be finished: a stored new row, a halo row, or nothing yet
+                    if (sl.idx >= 0 && sl.state == 0 && !(colour == 1 && (sl.idx < 2 || sl.idx > n + 1))) return -61;
+                    sl.idx = idx;
+                    sl.state = 0;
+                    sl.wr = it;
+                }
+                for (int t = 0; t < T; ++t)
+                    rs_pack<MODEL, NWL2>(pt[buf], stage.data() + (size_t)slot * T * 4, W.data(), t);
+                stage_packed[slot] = 1;
+            }
+            build_tables(it + 1, buf ^ 1);
+            if (int rc = issue_group(it + RS_STAGES)) return rc;
+        }
+    }
+    for (size_t k = 0; k < dst.size(); ++k)
+        if (dst[k] == 77) return -70;  // a site was never stored
+    for (int i = 0; i < lenX; ++i)
+        for (int j = 0; j < im.lenY; ++j) im.p[(size_t)i * im.lenY + j] = dst[((size_t)((i + j) & 1) * lenX + i) * nk + (j >> 1)];
+    *dB = tdB;
+    *dS = tdS;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int hostemu_rowstream_sweep(int model, int8_t *img, int lenX, int lenY, const uint32_t *thr, uint64_t seed,
+                                       uint32_t replica, uint64_t sweep, int pieces, long long *dB, long long *dS) {
+    if (lenY % 128 || (lenX & 1) || pieces < 1) return -1;
+    Image im = {img, lenX, lenY};
+    *dB = *dS = 0;
+    if (model != MODEL_ISING && model != MODEL_LATGAS) return -1;
+    int nwl2 = 0;
+    while ((1 << nwl2) < lenY / 128) ++nwl2;
+    switch (nwl2) {
+#define RS_CASE(K)                                                                                                       \
+    case K:                                                                                                              \
+        if constexpr ((RS_THREADS >> K) >= 1 && (RS_THREADS >> K) <= RS_MAXQ)                                            \
+            return model == MODEL_ISING ? rowstream_sweep<MODEL_ISING, K>(im, thr, seed, replica, sweep, pieces, dB, dS) \
+                                        : rowstream_sweep<MODEL_LATGAS, K>(im, thr, seed, replica, sweep, pieces, dB, dS); \
+        break;
+        RS_CASE(2) RS_CASE(3) RS_CASE(4) RS_CASE(5) RS_CASE(6) RS_CASE(7) RS_CASE(8) RS_CASE(9)
+#undef RS_CASE
+    }
+    return -2;
+}
+
+extern "C" int hostemu_rowstream_threads(void) { return RS_THREADS; }

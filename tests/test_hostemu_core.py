@@ -141,3 +141,39 @@ def test_batch_resident_kernel_logic_matches_specification(core, nrep, shape, nb
             o_latgas.sweep(ref[r], thr[r], seed, offset + r, sw)
         assert np.array_equal(cfg[r], ref[r]), r
         assert int(sums[r, 0]) == o_latgas.bond_sum(ref[r]) and int(sums[r, 1]) == int(ref[r].sum())
+
+
+@pytest.mark.parametrize("shape,pieces", [
+    ((130, 1024), 1),    # 8 words per row, 64 row tasks per iteration: the smallest piece the task order allows
+    ((262, 1024), 2),    # two ragged pieces; the halo rows of one are the first / last rows of the other
+    ((70, 2048), 1),
+    ((38, 4096), 1),
+    ((56, 8192), 3),
+    ((10, 16384), 1),    # 128 words per row, 4 row tasks per iteration (the headline geometry), shortest piece
+    ((62, 16384), 3),
+    ((46, 16384), 2),
+])
+def test_row_streaming_kernel_logic_matches_specification(core, shape, pieces):
+    """pmc_rowstream.cuh piece after piece on the host: the task order (colour 1 of row j a fixed distance behind
+    colour 0 of row j+1), the packing order running ahead of it, the ring of bit rows, the staging slots and the
+    per-iteration tables.  The emulation checks every read of a ring slot against what the slot holds at that time
+    and refuses a write into a slot another task of the same iteration reads (tests/hostemu/hostemu.cpp); the result
+    is compared with the numpy specification, sums included."""
+    seed, replica, J, kT = 91, 2, -1.0, 2.3
+    ref = o_ising.init_config(seed, replica, *shape)
+    cfg = ref.copy()
+    B0 = o_ising.bond_sum(ref)
+    dB = dS = 0
+    for sw in range(2):
+        b, s = core.rowstream_sweep(core.MODEL_ISING, cfg, ising_table(J, kT), seed, replica, sw, pieces)
+        dB += b
+        dS += s
+        o_ising.sweep(ref, J, kT, seed, replica, sw)
+        assert np.array_equal(cfg, ref), sw
+    assert B0 + dB == o_ising.bond_sum(ref)
+    ref = o_latgas.init_config(seed, replica, *shape)
+    cfg = ref.copy()
+    thr = o_latgas.threshold_table(-0.7, -0.2, 0.1, 0.8)
+    core.rowstream_sweep(core.MODEL_LATGAS, cfg, thr, seed, replica, 0, pieces)
+    o_latgas.sweep(ref, thr, seed, replica, 0)
+    assert np.array_equal(cfg, ref)
