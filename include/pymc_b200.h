@@ -61,7 +61,7 @@ typedef enum {
                                 /* kept in shared memory for all sweeps -- and, on one GPU, all replica   */
                                 /* exchanges -- of a call; neighbour flags instead of grid barriers.      */
                                 /* Needs lenY % 128 == 0 and nreplicas*lenX*lenY/8 bytes within the GPU's  */
-                                /* shared memory.  AUTO takes it from 2^20 sites on (calls of >= 2 sweeps) */
+                                /* shared memory.  AUTO takes it from 128 x 128 sites on (calls of >= 2 sweeps) */
     PYMC_KERNEL_ROWSTREAM = 6   /* int8 layout, one sweep per launch: a block walks down a piece of whole rows   */
                                 /* that stream through shared memory (bulk asynchronous copies), both colours in   */
                                 /* one pass.  Needs lenY = 128 * 2^k (1024 .. 65536).  AUTO uses it for the sweeps  */

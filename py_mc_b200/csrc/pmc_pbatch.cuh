@@ -15,16 +15,23 @@
 //
 // Rows a block needs from other blocks (at most four per colour: the row above its first row, the row below its
 // last row, and -- because lattices are periodic -- row 0 / row lenX-1 of a replica that starts / ends in
-// another block) travel through a small exchange buffer in global memory.  There is NO grid barrier in a sweep:
-//   * the rows other blocks need ("export rows") are updated FIRST in every colour pass and written straight to
-//     the exchange buffer by the threads that computed them; the last of those warps then raises the block's
-//     flag (a pass counter) -- all of this while the rest of the block is already working on the other rows;
-//   * the only readers of remote rows are those same first items of the NEXT pass; each polls the flag of the
-//     block it depends on (already raised, unless that block lags a whole pass behind) and reads the word
-//     from L2.
+// another block) travel through a small exchange buffer in global memory.  There is NO grid barrier in a sweep and
+// no flag either: every 64-bit word of an exported row travels as two 8-byte packets, each holding 32 bits of the
+// word and the number of the pass that produced it (the low-latency protocol of collective libraries: the flag
+// rides in the same atomic store as the data, so the writer needs no fence and the reader a single load):
+//   * the rows other blocks need ("export rows") are updated FIRST in every colour pass and stored to the exchange
+//     buffer by the threads that computed them -- while the rest of the block is already working on the other rows;
+//   * the only readers of remote rows are those same first items of the NEXT pass; each loads the packet pair of the
+//     word it needs from L2 and repeats the load until both packets carry that pass number (they do already,
+//     unless the other block lags a whole pass behind).
 // So the neighbour exchange is fully overlapped with the update and costs no block-wide synchronisation beyond
 // the one __syncthreads that ends a colour pass.  (The single-lattice kernel K11, pmc_persist.cuh, meets at a
-// grid barrier twice per sweep: measured 2.9 us per pass, 5.5 % of a 16384^2 sweep and half of a 1024^2 one.)
+// grid barrier twice per sweep: measured 2.9 us per pass, 5.5 % of a 16384^2 sweep and half of a 1024^2 one.  The
+// first form of this kernel published a per-block flag after a fence and a count of the exporting warps: three
+// dependent trips to L2 per hand-shake, about 3 us per pass once a block holds only a few rows.)
+// A word is never overwritten before it has been read: the thread that stores word w of an export row in pass p+2
+// has, in that same item, loaded word w of the neighbour's row from pass p+1, which the neighbour's thread stored
+// after loading my word w of pass p.
 //
 // Replica exchange inside the kernel (one GPU holds all replicas): after the sweeps of an exchange interval the
 // blocks recompute the exact bond sum and magnetisation of their rows per replica, publish them, meet at ONE grid
@@ -142,15 +149,18 @@ __host__ __device__ inline void pb_geometry(int b, int B, int nrep, int lenX, PB
     }
 }
 
+// One 64-bit word in the exchange buffer: two 8-byte packets {32 bits of the word, pass number}.
+struct alignas(16) PBPacket {
+    uint64_t lo, hi;
+};
+
 // What a thread needs besides the geometry: everything that sits in shared or global memory.
 struct PBCtx {
     uint64_t *s;                 // [2 colours][nrows][nw] resident rows of this block
     const int *segoff;           // [nseg] row-in-replica minus local row, per replica of this block
     const int *segstart;         // [nseg] first local row of each replica of this block (segstart[0] = 0)
     const uint32_t *splan;       // [nseg][PLAN_WORDS] plan row of each replica (its current temperature)
-    uint64_t *xbuf;              // [2 colours][nslots][nw] exchange buffer (global)
-    unsigned int *flags;         // [B] number of export events of each block (1 after the load)
-    unsigned int *cnt;           // shared: export warps that have finished, summed over all passes
+    PBPacket *xbuf;              // [2 colours][nslots][nw] exchange buffer (global), zeroed before the launch
     unsigned int *abort_word;    // global: set when a wait has timed out
     int *err;
     int lenX, nw, nw_shift;      // nw_shift >= 0: nw is that power of two
@@ -164,15 +174,52 @@ struct SmemRow {
     __device__ __forceinline__ uint32_t operator[](int k) const { return p[k]; }
 };
 
-__device__ __forceinline__ uint64_t pb_ldcg(const uint64_t *p) {
+// Store word v of an export row as the packet pair of pass `ev` (each 8-byte half is one atomic store).
+__device__ __forceinline__ void pb_put(PBPacket *p, uint64_t v, unsigned int ev) {
+    const uint64_t a = (v & 0xFFFFFFFFull) | ((uint64_t)ev << 32), b = (v >> 32) | ((uint64_t)ev << 32);
 #ifdef __CUDA_ARCH__
-    return __ldcg(p);
+    asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(a), "l"(b) : "memory");
 #else
-    return *p;
+    p->lo = a;
+    p->hi = b;
 #endif
 }
 
-// Acquire / release at GPU scope without the full (sequentially consistent) __threadfence.
+// Load the word whose packets carry pass number `need` (or a later one: see the header).  The poll backs off and is
+// bounded: after about two seconds *err is raised, and so is the abort word in device memory that lets every other
+// waiter of the launch give up at once.
+__device__ __forceinline__ uint64_t pb_get(const PBPacket *p, unsigned int need, int *err, unsigned int *abort_word) {
+#ifdef __CUDA_ARCH__
+    uint64_t a, b;
+    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
+    if ((unsigned int)(a >> 32) < need || (unsigned int)(b >> 32) < need) {
+        const long long t0 = clock64();
+        unsigned int spins = 0;
+        for (;;) {
+            __nanosleep(20);
+            asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
+            if ((unsigned int)(a >> 32) >= need && (unsigned int)(b >> 32) >= need) break;
+            if ((++spins & 1023u) == 0) {
+                if (*(volatile unsigned int *)abort_word) break;
+                if (clock64() - t0 > 4000000000LL) {
+                    *(volatile unsigned int *)abort_word = 1u;
+                    *err = 1;
+                    break;
+                }
+            }
+        }
+    }
+    return (a & 0xFFFFFFFFull) | (b << 32);
+#else
+    // the host drives the blocks in lock step: the packets must be there already
+    if ((unsigned int)(p->lo >> 32) < need || (unsigned int)(p->hi >> 32) < need) *err = 1;
+    (void)abort_word;
+    return (p->lo & 0xFFFFFFFFull) | (p->hi << 32);
+#endif
+}
+
+// Acquire / release at GPU scope without the full (sequentially consistent) __threadfence (grid barrier of the
+// exchange step).
 __device__ __forceinline__ unsigned int pb_ld_acquire(const unsigned int *p) {
 #ifdef __CUDA_ARCH__
     unsigned int v;
@@ -185,31 +232,6 @@ __device__ __forceinline__ unsigned int pb_ld_acquire(const unsigned int *p) {
 __device__ __forceinline__ void pb_fence() {
 #ifdef __CUDA_ARCH__
     asm volatile("fence.acq_rel.gpu;" ::: "memory");
-#endif
-}
-
-// Wait until block `blk` has published `need` export events.  The poll backs off (many threads of many blocks may
-// watch the same few cache lines) and is bounded: after about two seconds *err is raised, and so is the abort word
-// in device memory that lets every other waiter of the launch give up at once.
-__device__ __forceinline__ void pb_wait(const unsigned int *flag, unsigned int need, int *err, unsigned int *abort_word) {
-#ifdef __CUDA_ARCH__
-    if (pb_ld_acquire(flag) >= need) return;
-    const long long t0 = clock64();
-    unsigned int spins = 0;
-    while (pb_ld_acquire(flag) < need) {
-        __nanosleep(40);
-        if ((++spins & 1023u) == 0) {
-            if (*(volatile unsigned int *)abort_word) return;
-            if (clock64() - t0 > 4000000000LL) {
-                *(volatile unsigned int *)abort_word = 1u;
-                *err = 1;
-                return;
-            }
-        }
-    }
-#else
-    if (*flag < need) *err = 1;  // the host drives the blocks in lock step: the flag must be there already
-    (void)abort_word;
 #endif
 }
 
@@ -261,17 +283,17 @@ __device__ __forceinline__ void pb_neighbours(const PBGeom &g, int lenX, int lr,
 __device__ __forceinline__ uint64_t pb_row_word(const PBGeom &g, const PBCtx &c, int oc, int row, int w, unsigned int need) {
     if (row >= 0) return c.s[((size_t)oc * g.nrows + row) * c.nw + w];
     const int k = -1 - row;
-    pb_wait(c.flags + g.imp_blk[k], need, c.err, c.abort_word);
-    return pb_ldcg(c.xbuf + ((size_t)oc * c.nslots + g.imp_slot[k]) * c.nw + w);
+    return pb_get(c.xbuf + ((size_t)oc * c.nslots + g.imp_slot[k]) * c.nw + w, need, c.err, c.abort_word);
 }
 
-// One colour pass of one thread.  `events` = export events every block has completed before this pass (1 + number
-// of passes since the load).  Every thread of a warp must call this together (update_word votes).
+// One colour pass of one thread.  `events` = 1 + number of passes since the load: the pass number the packets of
+// the rows this pass reads must carry; what it exports carries events + 1.  Every thread of a warp must call this
+// together (update_word votes).
 //
 // Items are taken export rows first, then the other rows in their natural order: ordinal o = base + t, ordinal row
 // o / nw, column o % nw.  The first round (ordinals 0 .. T-1) holds all items of the export rows (the host makes T at
 // least that large): it takes the general path -- rows of other blocks from the exchange buffer, new words to the
-// exchange buffer, flag.  Every later round touches only rows whose neighbours are all in this block, and a thread
+// exchange buffer.  Every later round touches only rows whose neighbours are all in this block, and a thread
 // walks down the rows with a fixed stride: its row, replica segment and plan are carried from one item to the next
 // instead of being recomputed.  (Measured alternatives, slower: recomputing the row from the ordinal per item; the
 // natural order with the export items pulled forward by their owners -- with few words per row those owners' warps do
@@ -312,32 +334,7 @@ __device__ __forceinline__ void pb_pass(const PBGeom &g, const PBCtx &c, int col
             sc[idx] = Snew;
             if (o < nexport)
                 for (int e = 0; e < g.nexp; ++e)
-                    if (g.exp_row[e] == lr) c.xbuf[((size_t)colour * c.nslots + g.exp_slot[e]) * nw + w] = Snew;
-        }
-        if (nexport > 0 && (t - t % PMC_WARP) < nexport) {
-            // This warp held export items: once all such warps are through, the block's flag goes up.  Ordering: the
-            // lanes' stores to the exchange buffer -> __syncwarp -> lane 0: fence, count (release pattern on the shared
-            // counter); the last warp: count, fence (acquire pattern), flag.  Readers load the flag with acquire.
-#ifdef __CUDA_ARCH__
-            __syncwarp();
-#endif
-            if (t % PMC_WARP == 0) {
-                const unsigned int nwarps = (unsigned int)((nexport + PMC_WARP - 1) / PMC_WARP);
-                pb_fence();
-#ifdef __CUDA_ARCH__
-                const unsigned int arrived = atomicAdd(c.cnt, 1u) + 1u;
-#else
-                const unsigned int arrived = ++*c.cnt;
-#endif
-                if (arrived == events * nwarps) {  // cnt counts over all passes; the load was event 1
-                    pb_fence();
-#ifdef __CUDA_ARCH__
-                    *(volatile unsigned int *)(c.flags + c.b) = events + 1u;
-#else
-                    c.flags[c.b] = events + 1u;
-#endif
-                }
-            }
+                    if (g.exp_row[e] == lr) pb_put(c.xbuf + ((size_t)colour * c.nslots + g.exp_slot[e]) * nw + w, Snew, events + 1u);
         }
     }
     if (T >= items) return;
@@ -404,13 +401,12 @@ __device__ __forceinline__ void pb_pass(const PBGeom &g, const PBCtx &c, int col
     }
 }
 
-// After the load: the export rows of both colours go to the exchange buffer (event 1).  The caller synchronises the
-// block and raises the flag.
+// After the load: the export rows of both colours go to the exchange buffer as pass 1.
 __device__ __forceinline__ void pb_publish_loaded(const PBGeom &g, const PBCtx &c, int t, int T) {
     for (int k = t; k < 2 * g.nexp * c.nw; k += T) {
         const int colour = k / (g.nexp * c.nw), r = k - colour * g.nexp * c.nw;
         const int e = r / c.nw, w = r - e * c.nw;
-        c.xbuf[((size_t)colour * c.nslots + g.exp_slot[e]) * c.nw + w] = c.s[((size_t)colour * g.nrows + g.exp_row[e]) * c.nw + w];
+        pb_put(c.xbuf + ((size_t)colour * c.nslots + g.exp_slot[e]) * c.nw + w, c.s[((size_t)colour * g.nrows + g.exp_row[e]) * c.nw + w], 1u);
     }
 }
 
@@ -518,10 +514,9 @@ struct PBatchArgs {
     int xchg_phase;                // sweeps already done since the last exchange
     int scheme0;                   // XCscheme of the first exchange of this launch (alternates from there)
     unsigned long long round0;     // the handle's exchange round at entry
-    unsigned int *flags;           // [B] zeroed by the host before the launch
     unsigned int *bar;             // [2] grid barrier arrivals and the abort word, zeroed by the host before the launch
     int *err;
-    uint64_t *xbuf;                // [2][nslots][nw]
+    PBPacket *xbuf;                // [2][nslots][nw], zeroed by the host before the launch (pass numbers start at 1)
     long long *esum;               // [2 parities][R][2] per-replica exact sums of an exchange, indexed by GLOBAL replica;
                                    // the local slice is zeroed by the host before the launch (blocks add deltas)
     // replicas spread over several GPUs (pymc_rx_connect): the all-gather of the energies is done by this kernel
@@ -570,15 +565,11 @@ __global__ void __launch_bounds__(PB_MAX_THREADS, 1) pbatch_kernel(const __grid_
     __shared__ uint32_t s_plan[PB_MAXSEG * PLAN_WORDS];
     __shared__ int s_segoff[PB_MAXSEG], s_segstart[PB_MAXSEG], s_T[PB_MAXSEG];
     __shared__ long long s_acc[PB_MAXSEG * 2], s_prev[2][PB_MAXSEG * 2];
-    __shared__ unsigned int s_cnt;
     __shared__ PBGeom s_geom;
     const int b = blockIdx.x, B = gridDim.x, t = threadIdx.x, T = blockDim.x;
     const int lenX = L.lenX, nw = L.nw, nk = L.nk, nrep = L.nrep;
 
-    if (t == 0) {
-        pb_geometry(b, B, nrep, lenX, s_geom);
-        s_cnt = 0;
-    }
+    if (t == 0) pb_geometry(b, B, nrep, lenX, s_geom);
     __syncthreads();
     const PBGeom &g = s_geom;  // stays in shared memory: block-uniform, read where needed
     if (t < g.nseg) {
@@ -593,8 +584,6 @@ __global__ void __launch_bounds__(PB_MAX_THREADS, 1) pbatch_kernel(const __grid_
     c.segstart = s_segstart;
     c.splan = s_plan;
     c.xbuf = a.xbuf;
-    c.flags = a.flags;
-    c.cnt = &s_cnt;
     c.abort_word = a.bar + 1;
     c.err = a.err;
     c.lenX = lenX;
@@ -632,10 +621,6 @@ __global__ void __launch_bounds__(PB_MAX_THREADS, 1) pbatch_kernel(const __grid_
     load_plans();
     pb_publish_loaded(g, c, t, T);
     __syncthreads();
-    if (t == 0) {
-        pb_fence();  // the block's stores to the exchange buffer (ordered before me by the barrier) before the flag
-        *(volatile unsigned int *)(a.flags + b) = 1u;
-    }
 
     unsigned int events = 1, arrivals = 0;
     int scheme = a.scheme0, cur = 0;

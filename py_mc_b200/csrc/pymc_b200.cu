@@ -34,11 +34,12 @@ static const size_t RESIDENT_AUTO_MAX_IMAGE = 32 * 1024;
 // on the batch-resident kernel K12 (no grid barrier) is faster still and takes over.
 static const size_t PERSIST_AUTO_MIN_SITES = (size_t)1024 * 1024;
 // smallest batch (sites of all replicas together) for which PYMC_KERNEL_AUTO takes the batch-resident kernel K12
-// on calls of >= 2 sweeps: from 1024 x 1024 on the resident kernels beat the per-sweep ones (profiles/README.md)
-static const size_t PBATCH_AUTO_MIN_SITES = (size_t)1024 * 1024;
-// ... but a single lattice below 4096 x 4096 gives a block so few rows that a pass is shorter than the flag
-// hand-shake between neighbouring blocks; there K11 is as good or better (profiles/r2_pbatch_probe.json)
-static const size_t PBATCH_SINGLE_MIN_SITES = (size_t)4096 * 4096;
+// on calls of >= 2 sweeps.  Since its rows travel between blocks as {data, pass number} packets it is the fastest
+// kernel at every size measured (profiles/r2_pbatch_probe.json, us per sweep K12 / K11 / per-sweep kernels: 128^2
+// 3.7 / 5.7 / 12.1, 1024^2 4.8 / 6.4 / 8.2, 4096^2 8.0 / 11.6 / 17.2, 16384^2 103.7 / 104.3 / 170.0), so the
+// threshold only keeps it away from lattices of a few rows, where a launch has nothing to amortise.
+static const size_t PBATCH_AUTO_MIN_SITES = (size_t)128 * 128;
+static const size_t PBATCH_SINGLE_MIN_SITES = (size_t)128 * 128;
 // PYMC_KERNEL_AUTO runs the sweeps the resident kernels do not take (single-sweep calls, lattices beyond the chip) on the
 // row-streaming kernel K13 instead of the tiled one from this many sites (all replicas together) and this many words per
 // colour row on.  Measured (profiles/r2_rowstream_probe.json, ms per sweep K13 / tiled): 16384^2 0.1697 / 0.1760,
@@ -711,8 +712,8 @@ struct pymc_handle {
     bool pbatch;                   // calls of >= 2 sweeps (and single-GPU exchange cycles) run on the batch kernel
     int pb_blocks, pb_threads;
     size_t pb_smem;
-    unsigned int *pb_sync;         // [pb_blocks] export-event flags + grid-barrier counter + abort word (zeroed per launch)
-    uint64_t *pb_xbuf;             // [2][2*blocks + 2*nrep][nw] rows exchanged between blocks
+    unsigned int *pb_sync;         // [2] grid-barrier counter + abort word (zeroed per launch)
+    PBPacket *pb_xbuf;             // [2][2*blocks + 2*nrep][nw] rows exchanged between blocks, as packets (zeroed per launch)
     long long *pb_esum;            // [2 parities][ntemps][2] exact sums per GLOBAL replica at an exchange
     unsigned int *pb_xflags;       // [PB_MAXRANKS] exchange rounds whose sums each other GPU has delivered here
     int rx_nranks, rx_rank;        // > 1 after pymc_rx_connect: the ladder is spread over that many GPUs
@@ -1416,8 +1417,8 @@ static int launch_pbatch(pymc_handle *h, int64_t nsweeps, int xchg_every, int *s
     }
     const int B = h->pb_blocks, R = h->p.ntemps;
     if (!h->pb_sync) {
-        CUDA_TRY(cudaMalloc(&h->pb_sync, (size_t)(B + 2) * sizeof(unsigned int)));
-        CUDA_TRY(cudaMalloc(&h->pb_xbuf, (size_t)2 * pb_nslots(B, h->p.nreplicas) * h->nw * 8));
+        CUDA_TRY(cudaMalloc(&h->pb_sync, 2 * sizeof(unsigned int)));
+        CUDA_TRY(cudaMalloc(&h->pb_xbuf, (size_t)2 * pb_nslots(B, h->p.nreplicas) * h->nw * sizeof(PBPacket)));
     }
     if (xchg_every > 0 && !h->pb_maps) CUDA_TRY(cudaMalloc(&h->pb_maps, (size_t)4 * R * sizeof(int32_t)));
     if (xchg_every > 0) {
@@ -1438,8 +1439,7 @@ static int launch_pbatch(pymc_handle *h, int64_t nsweeps, int xchg_every, int *s
         a.xchg_phase = 0;
         a.scheme0 = scheme;
         a.round0 = h->rx_round;
-        a.flags = h->pb_sync;
-        a.bar = h->pb_sync + B;
+        a.bar = h->pb_sync;
         a.err = h->persist_err;
         a.xbuf = h->pb_xbuf;
         a.esum = h->pb_esum;
@@ -1466,7 +1466,8 @@ static int launch_pbatch(pymc_handle *h, int64_t nsweeps, int xchg_every, int *s
             a.accepted = h->rx_accepted;
             a.energies = h->energies;
         }
-        CUDA_TRY(cudaMemsetAsync(h->pb_sync, 0, (size_t)(B + 2) * sizeof(unsigned int), h->stream));
+        CUDA_TRY(cudaMemsetAsync(h->pb_sync, 0, 2 * sizeof(unsigned int), h->stream));
+        CUDA_TRY(cudaMemsetAsync(h->pb_xbuf, 0, (size_t)2 * pb_nslots(B, h->p.nreplicas) * h->nw * sizeof(PBPacket), h->stream));
         CUDA_TRY(cudaMemsetAsync(h->reduced, 0, (size_t)h->p.nreplicas * 16, h->stream));
         if (xchg_every > 0)  // the blocks add deltas to the sums of MY replicas (other GPUs store theirs whole)
             for (int par = 0; par < 2; ++par)

@@ -236,8 +236,7 @@ int pbatch_sweeps(int8_t *imgs, int nrep, int lenX, int lenY, const uint32_t *th
     std::vector<std::vector<int>> segoff(B), segstart(B);
     std::vector<std::vector<uint32_t>> splan(B);
     const int nslots = pb_nslots(B, nrep);
-    std::vector<uint64_t> xbuf((size_t)2 * nslots * nw, 0xDEADBEEFDEADBEEFull);
-    std::vector<unsigned int> flags(B, 0), cnt(B, 0);
+    std::vector<PBPacket> xbuf((size_t)2 * nslots * nw, PBPacket{0, 0});
     int err = 0;
     unsigned int abort_word = 0;
     const PhiloxKey keys = make_key(seed);
@@ -267,8 +266,6 @@ int pbatch_sweeps(int8_t *imgs, int nrep, int lenX, int lenY, const uint32_t *th
         c.segstart = segstart[b].data();
         c.splan = splan[b].data();
         c.xbuf = xbuf.data();
-        c.flags = flags.data();
-        c.cnt = &cnt[b];
         c.abort_word = &abort_word;
         c.err = &err;
         c.lenX = lenX;
@@ -281,18 +278,14 @@ int pbatch_sweeps(int8_t *imgs, int nrep, int lenX, int lenY, const uint32_t *th
         c.rep_offset = rep_offset;
         c.key = &keys;
     }
-    for (int b = 0; b < B; ++b) {
+    for (int b = 0; b < B; ++b)
         for (int t = 0; t < T; ++t) pb_publish_loaded(geo[b], ctx[b], t, T);
-        flags[b] = 1;
-    }
     unsigned int events = 1;
     for (int sw = 0; sw < nsweeps; ++sw)
         for (int colour = 0; colour < 2; ++colour) {
             for (int b = 0; b < B; ++b)
                 for (int t = 0; t < T; ++t) pb_pass<MODEL>(geo[b], ctx[b], colour, 2 * (sweep0 + sw) + colour, events, t, T);
             ++events;
-            for (int b = 0; b < B; ++b)  // every block with export rows must have raised its flag by now
-                if (geo[b].nexp > 0 && flags[b] != events) return -3;
         }
     for (int r = 0; r < 2 * nrep; ++r) sums[r] = 0;
     for (int b = 0; b < B; ++b) {

@@ -37,7 +37,7 @@ def main():
     model = ising2D(-1.0)
     res = {"single": {}, "rx": {}, "latgas": {}}
     t0 = time.time()
-    for L in (1024, 2048, 4096, 8192, 16384):
+    for L in (128, 256, 512, 1024, 2048, 4096, 8192, 16384):
         row = {}
         for layout, lname in ((0, "int8"), (1, "bits")):
             for kname in ("pbatch", "persistent", "per_sweep"):

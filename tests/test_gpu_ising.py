@@ -198,10 +198,11 @@ def test_fused_two_pass_and_generic_kernels_agree(shape, nrep):
         lat.init_random()
         lat.set_accept_tables(thr)
         lats[name] = lat
-    assert lats["fused"].sweep_kernel_info() == (1, "sweep_fused_i8_kernel")
-    assert lats["two_pass"].sweep_kernel_info() == (2, "sweep_tiled_i8_kernel")
-    assert lats["generic"].sweep_kernel_info() == (2, "sweep_word_kernel")
-    assert lats["bits"].sweep_kernel_info() == (2, "sweep_bits_rows_kernel")
+    # the kernels that serve calls of a single sweep (longer calls of the AUTO handles stay on chip: test_zx_gpu_pbatch.py)
+    assert lats["fused"].sweep_kernel_for(1) == (1, "sweep_fused_i8_kernel")
+    assert lats["two_pass"].sweep_kernel_for(1) == (2, "sweep_tiled_i8_kernel")
+    assert lats["generic"].sweep_kernel_for(1) == (2, "sweep_word_kernel")
+    assert lats["bits"].sweep_kernel_for(1) == (2, "sweep_bits_rows_kernel")
     ref = o_ising.init_config(seed, nrep - 1, *shape)
     for sw in range(5):  # odd number of sweeps: the fused kernel ends in its second buffer
         for lat in lats.values():
