@@ -53,6 +53,7 @@ PROFILED = {
     ("sweep_fused_i8_kernel", "single16k"): ("r1_fused_final_summary.csv", "16384x16384 int8, one sweep per launch"),
     ("sweep_bits_rows_kernel", "single16k"): ("r1_bits_final_summary.csv", "16384x16384 bits, one colour pass per launch"),
     ("resident_kernel", "rx256"): ("r1_resident_rx_summary.csv", "256 x 1024^2 int8, 10 sweeps per launch"),
+    ("rowstream_kernel", "single16k"): ("r2_rowstream_summary.csv", "16384x16384 int8, one sweep per launch"),
     ("persistent_kernel", "single16k"): ("r2_persist_summary.csv", "16384x16384 int8, 20 sweeps per launch"),
     ("pbatch_kernel", "single16k"): ("r2_pbatch_summary.csv", "16384x16384 int8, 20 sweeps per launch"),
     ("pbatch_kernel", "rx256"): ("r2_pbatch_rx_summary.csv", "256 x 1024^2 int8, 20 sweeps + 2 exchanges per launch"),
@@ -462,7 +463,11 @@ def run_rx(args):
     # end to end: host configurations in, sweeps + exchanges, observables and the map out, every step
     import numpy as np
     from py_mc_b200 import _cabi
-    host = [lat.download(r) for r in range(min(nloc, 4))]
+    host = []
+    for r in range(min(nloc, 4)):  # pinned host images: the uploads below are enqueued, not waited for one by one
+        a = _cabi.pinned_empty((args.rx_L, args.rx_L), np.int8)
+        lat.download(r, out=a)
+        host.append(a)
     e2e = {}
     for spp in sorted(set([1, args.e2e_sweeps])):
         reps = 2
@@ -471,7 +476,7 @@ def run_rx(args):
         t0 = time.perf_counter()
         for _ in range(reps):
             for r in range(nloc):
-                lat.upload(r, host[r % len(host)])
+                lat.upload_async(r, host[r % len(host)])
             head["steps"](spp)
             lat.tracked()
             lat.get_replica_to_T()
@@ -806,8 +811,11 @@ def run_single(args):
             lat3 = make(layout)
             n3 = max(50, K)
             ms3, _ = timed(lat3, lambda: [lat3.sweep(1) for _ in range(n3)])  # single-sweep calls: the fused kernel
-            extra["one_sweep_per_launch"] = {"value": world * nsites * n3 / (ms3 * 1e-3), "unit": UNIT, "ms_per_step": ms3 / n3,
-                                             "kernel": lat3.sweep_kernel_for(1)[1],
+            k3 = lat3.sweep_kernel_for(1)[1]
+            extra["one_sweep_per_launch"] = {"value": world * nsites * n3 / (ms3 * 1e-3), "unit": UNIT, "ms_per_step": ms3 / n3, "kernel": k3,
+                                             "roofline": roofline_block(k3, 2.0 * bytes_per_site * nsites / (1 if layout == _cabi.LAYOUT_INT8 else 2),
+                                                                        ms3 / n3 / (1 if layout == _cabi.LAYOUT_INT8 else 2), False,
+                                                                        "single16k" if L == 16384 else None),
                                              "roofline_frac": 2.0 * bytes_per_site * nsites / (ms3 / n3 * 1e-3) / 1e9 / measured_peak_hbm()[0]}
             lat3.close()
         except Exception as exc:
