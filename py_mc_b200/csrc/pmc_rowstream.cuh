@@ -43,6 +43,10 @@ namespace pmc {
 constexpr int RS_THREADS = PMC_RS_THREADS;
 constexpr int RS_STAGES = 2;   // staging slots for the bulk copies (one iteration's rows each)
 constexpr int RS_MAXQ = 64;    // row tasks per iteration: words per colour row >= RS_THREADS / 64
+#ifndef PMC_RS_TABLE_ENTRIES
+#define PMC_RS_TABLE_ENTRIES 160
+#endif
+constexpr int RS_TABLE_ENTRIES = PMC_RS_TABLE_ENTRIES;  // per-iteration tables kept for a whole piece if it has no more row-task slots
 
 // launch-uniform schedule constants (kernel parameter: constant memory)
 struct RSParams {
@@ -54,7 +58,10 @@ struct RSParams {
     int pieces;        // pieces per replica
 };
 
-__host__ __device__ inline int rs_ring_rows(int Q) { return 3 * Q + 4; }  // checked by the emulation in tests/hostemu
+__host__ __device__ constexpr int rs_ring_rows(int Q) { return 3 * Q + 4 + (Q + 1) / 2; }  // checked by the emulation in tests/hostemu
+// iterations that only pack: the rows a task reads must have been packed two iterations before it runs (a warp packs
+// after it has arrived at the barrier of an iteration, so only the packing of the iteration before last is complete)
+__host__ __device__ constexpr int rs_prologue(int Q) { return (2 * Q + 4 + Q - 1) / Q + 1; }
 __host__ __device__ inline int rs_min_rows(int Q) { return 2 * Q + 2; }  // smallest piece the task order is valid for
 
 // false if the shape cannot be streamed with RS_THREADS threads
@@ -71,7 +78,7 @@ __host__ inline bool rs_make_params(int lenX, int nk, int pieces, RSParams &p) {
     p.q_log2 = 0;
     while ((1 << p.q_log2) < p.Q) ++p.q_log2;
     p.lead = p.Q + 1;
-    p.prologue = (2 * p.Q + 4 + p.Q - 1) / p.Q;
+    p.prologue = rs_prologue(p.Q);
     p.rw = rs_ring_rows(p.Q);
     p.pieces = pieces;
     return pieces >= 1 && lenX / pieces >= rs_min_rows(p.Q);
@@ -141,7 +148,7 @@ __host__ __device__ inline RSTask rs_pack_task(const RSParams &p, int a, int n, 
 // ---- per-iteration tables ------------------------------------------------------------------------------------
 // Everything a thread needs about the row task it works on is worked out once per task and iteration (by one lane
 // per task) and read from shared memory, instead of being re-derived by every thread.  The two rings are one array W
-// of 2*RW + 1 rows (colour 1 follows colour 0); "word base" / "u16 base" index it as 64-bit words / as 16-bit pieces.
+// of 2*RW + 1 rows (colour 1 follows colour 0); a "word base" indexes it as 64-bit words.
 // The last row is a spare: a position beyond the end of a sequence is given that row to work on, so that the phases
 // need no branch around their loads and stores (only the store to global memory is predicated).
 struct RSCompute {
@@ -151,7 +158,7 @@ struct RSCompute {
     int pad0, pad1;
 };
 struct RSMove {
-    int base;  // u16 base of the row in W (the spare row if there is nothing to do)
+    int base;  // word base of the row in W (the spare row if there is nothing to do)
     int off;   // unpack: offset of the row in the destination, in 16-byte units, or -1: do not store
 };
 
@@ -174,21 +181,21 @@ __host__ __device__ inline RSCompute rs_build_compute(const RSParams &p, int a, 
 }
 
 __host__ __device__ inline RSMove rs_build_pack(const RSParams &p, int n, int pp) {
-    RSMove m = {(2 * p.rw) << (p.nw_log2 + 2), -1};
+    RSMove m = {(2 * p.rw) << p.nw_log2, -1};
     int colour, idx;
     if (!rs_pack_index(n, pp, colour, idx)) return m;
-    m.base = ((colour ? p.rw : 0) + idx % p.rw) << (p.nw_log2 + 2);
+    m.base = ((colour ? p.rw : 0) + idx % p.rw) << p.nw_log2;
     return m;
 }
 
 // the task at position pos was computed in the previous iteration: where its row goes
 __host__ __device__ inline RSMove rs_build_unpack(const RSParams &p, int a, int n, int pos) {
-    RSMove m = {(2 * p.rw) << (p.nw_log2 + 2), -1};
+    RSMove m = {(2 * p.rw) << p.nw_log2, -1};
     int colour, idx;
     if (!rs_task_index(p, n, pos, colour, idx)) return m;
     if (!colour && (idx < 1 || idx > n)) return m;  // recomputed halo row: another piece stores it
     const int r = colour ? idx + 2 : idx, row = rs_wrap(a - 1 + idx + colour, p.lenX);
-    m.base = ((colour ? p.rw : 0) + r % p.rw) << (p.nw_log2 + 2);
+    m.base = ((colour ? p.rw : 0) + r % p.rw) << p.nw_log2;
     m.off = (int)((((long long)colour * p.lenX + row) * p.nk) >> 4);
     return m;
 }
@@ -215,8 +222,12 @@ __device__ __forceinline__ uint32_t rs_pack16(uint4 v) {
 }
 
 // ---- the three per-thread phases of an iteration (also driven on the host by tests/hostemu) --------------------
-// chunk = 16 bytes = 16 sites of one colour row; a row has 4*nw chunks; thread t handles chunks t + e*RS_THREADS,
-// e = 0..3.  NWL2 = log2(words per colour row) is a template parameter: the index arithmetic folds into constants.
+// chunk = 16 bytes = 16 sites of one colour row; a row has 4*nw chunks.  In the packing and unpacking phases thread t
+// handles chunks t + e*RS_THREADS, e = 0..3 (four different rows): consecutive lanes read / store consecutive 16 bytes.
+// (Measured slower: one whole word = 64 contiguous bytes per thread, with the four 128-bit shared-memory loads rotated
+// so that they do not conflict -- +4 % instructions for the variable shifts when packing, and 128-bit global stores
+// 64 bytes apart when unpacking: 0.164 and 0.185 ms against 0.160.)  NWL2 = log2(words per colour row) is a template
+// parameter: the index arithmetic folds into constants.
 
 // bytes of the rows of this iteration's packing tasks (staged contiguously, chunk c at stage[c]) -> bits in the rings
 template <int MODEL, int NWL2>
@@ -226,7 +237,7 @@ __device__ __forceinline__ void rs_pack(const RSMove *tab, const uint4 *stage, u
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
         const int c = t + e * RS_THREADS;
-        s16[tab[c >> CSH].base + (c & ((1 << CSH) - 1))] = (uint16_t)rs_pack16<MODEL>(stage[c]);
+        s16[4 * tab[c >> CSH].base + (c & ((1 << CSH) - 1))] = (uint16_t)rs_pack16<MODEL>(stage[c]);
     }
 }
 
@@ -262,7 +273,7 @@ __device__ __forceinline__ void rs_unpack(const RSMove *tab, const uint64_t *W, 
     for (int e = 0; e < 4; ++e) {
         const int c = t + e * RS_THREADS, cm = c & ((1 << CSH) - 1);
         const RSMove m = tab[c >> CSH];
-        const uint4 v = unpack16<MODEL>(s16[m.base + cm]);
+        const uint4 v = unpack16<MODEL>(s16[4 * m.base + cm]);
         if (m.off >= 0) dst16[(uint32_t)(m.off + cm)] = v;
     }
 }
@@ -276,6 +287,9 @@ __device__ __forceinline__ void rs_mbar_init(uint64_t *bar, uint32_t count) {
 }
 __device__ __forceinline__ void rs_mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(rs_smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void rs_mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(rs_smem_addr(bar)) : "memory");
 }
 __device__ __forceinline__ bool rs_mbar_try_wait(uint64_t *bar, uint32_t parity) {
     uint32_t ok;
@@ -312,8 +326,11 @@ __global__ void __launch_bounds__(RS_THREADS, 1024 / RS_THREADS)
     static_assert((1 << QL2) == Q && Q >= 1 && Q <= RS_MAXQ, "row tasks per iteration");
     extern __shared__ __align__(128) unsigned char rs_smem[];
     __shared__ __align__(8) uint64_t s_full[RS_STAGES];
-    __shared__ __align__(16) RSCompute s_ct[2][Q];
-    __shared__ __align__(8) RSMove s_pt[2][Q], s_ut[2][Q];
+    __shared__ __align__(8) uint64_t s_done;  // one arrival per warp and iteration: the split block barrier
+    // tables of all iterations of the piece when they fit (built once, one entry per thread), else of three iterations
+    constexpr int TBL = RS_TABLE_ENTRIES > 3 * Q ? RS_TABLE_ENTRIES : 3 * Q;
+    __shared__ __align__(16) RSCompute s_ct[TBL];
+    __shared__ __align__(8) RSMove s_pt[TBL], s_ut[TBL];
     __shared__ RSBlock s_blk;
     __shared__ int s_red[2][RS_THREADS / 32];
     uint4 *const stage = reinterpret_cast<uint4 *>(rs_smem);
@@ -327,8 +344,8 @@ __global__ void __launch_bounds__(RS_THREADS, 1024 / RS_THREADS)
     p.Q = Q;
     p.q_log2 = QL2;
     p.lead = Q + 1;
-    p.prologue = (2 * Q + 4 + Q - 1) / Q;
-    p.rw = 3 * Q + 4;
+    p.prologue = rs_prologue(Q);
+    p.rw = rs_ring_rows(Q);
 
     const int t = threadIdx.x, rep = blockIdx.y;
     if (t == 0) {
@@ -342,6 +359,7 @@ __global__ void __launch_bounds__(RS_THREADS, 1024 / RS_THREADS)
         s_blk.src_rep = src + (size_t)rep * 2 * p.lenX * p.nk;
         s_blk.dst16 = reinterpret_cast<uint4 *>(dst + (size_t)rep * 2 * p.lenX * p.nk);
         for (int s = 0; s < RS_STAGES; ++s) rs_mbar_init(&s_full[s], 1);
+        rs_mbar_init(&s_done, RS_THREADS / 32);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
@@ -364,69 +382,74 @@ __global__ void __launch_bounds__(RS_THREADS, 1024 / RS_THREADS)
             rs_bulk_load(slot + (size_t)k * p.nk, s_blk.src_rep + ((size_t)colour * p.lenX + task.row) * p.nk, (uint32_t)p.nk, bar);
         }
     };
-    // tables of iteration `it` (one lane per task, in the LAST warps of the block: warp 0 issues the copies)
-    auto build_tables = [&](int it, int buf) {
-        const int k = RS_THREADS - 1 - t;
-        if (k < Q) {
-            const int kc = it - p.prologue, a = s_blk.a, n = s_blk.n;
-            s_ct[buf][k] = rs_build_compute(p, a, n, (kc << QL2) + k);
-            s_pt[buf][k] = rs_build_pack(p, n, (it << QL2) + k);
-            s_ut[buf][k] = rs_build_unpack(p, a, n, ((kc - 1) << QL2) + k);
-        }
+    // Tables.  A piece of few enough iterations gets all of them at once (one entry per thread, here); otherwise the
+    // tables of iteration it + 1 are built during iteration it by one lane per task, in the LAST warps of the block
+    // (warp 0 issues the copies), and three iterations' worth of entries rotate (a warp that has arrived at the barrier of
+    // iteration it - 1 may still be packing from that iteration's table while the builder is already in iteration it).
+    const bool all_tables = s_blk.niter * Q <= TBL;
+    auto build_entry = [&](int it, int k, int at) {
+        const int kc = it - p.prologue, a = s_blk.a, n = s_blk.n;
+        s_ct[at] = rs_build_compute(p, a, n, (kc << QL2) + k);
+        s_pt[at] = rs_build_pack(p, n, (it << QL2) + k);
+        s_ut[at] = rs_build_unpack(p, a, n, ((kc - 1) << QL2) + k);
     };
-
-    build_tables(0, 0);
+    auto build_tables = [&](int it) {
+        if (all_tables) return;
+        const int k = RS_THREADS - 1 - t;
+        if (k < Q) build_entry(it, k, ((it % 3) << QL2) + k);
+    };
+    auto table_base = [&](int it) { return all_tables ? it << QL2 : (it % 3) << QL2; };
+    if (all_tables) {
+        for (int e = t; e < s_blk.niter * Q; e += RS_THREADS) build_entry(e >> QL2, e & (Q - 1), e);
+    } else {
+        build_tables(0);
+    }
     __syncthreads();
     if (t < 32)
         for (int g = 0; g < RS_STAGES; ++g) issue_group(g);
 
     int dB = 0, dS = 0;
     const uint32_t greplica = (uint32_t)(L.rep_offset + rep);
-    auto wait_staged = [&](int it) {  // the rows of packing group `it` have landed in their staging slot
-        uint64_t *bar = &s_full[it % RS_STAGES];
-        const uint32_t parity = (uint32_t)(it / RS_STAGES) & 1u;
+    auto wait_on = [&](uint64_t *bar, uint32_t parity) {
         if (!rs_mbar_try_wait(bar, parity)) {
             const long long t0 = clock64();
             while (!rs_mbar_try_wait(bar, parity)) {
-                if (clock64() - t0 > 4000000000LL) {  // about two seconds: the copy never arrived
+                if (clock64() - t0 > 4000000000LL) {  // about two seconds: a copy never arrived / a warp never did
                     *err = 1;
                     break;
                 }
             }
         }
     };
-    auto end_iteration = [&](int it) {
-        build_tables(it + 1, (it & 1) ^ 1);
-        __syncthreads();
-        if (t < 32) issue_group(it + RS_STAGES);  // the slot this iteration packed from is free again
+    // The block barrier of an iteration, split.  A warp ARRIVES when it has finished its share of the task sequence
+    // (what the other warps wait for), then packs rows for a later iteration -- nobody reads those before the
+    // barrier after next -- and only then WAITS for the slowest warp: the spread of the per-lane tail rounds between
+    // warps is absorbed by the packing instead of idling.  What follows the wait may read what any warp computed
+    // before its arrival.  A staging slot is free again once every warp has arrived for the iteration AFTER the one
+    // that packed from it (a warp packs after arriving), so the copies for group it + 1 are issued at the start of
+    // iteration it + 1 and have one compute phase to land.
+    auto arrive = [&]() {
+        __syncwarp();
+        if ((t & 31) == 0) rs_mbar_arrive(&s_done);
     };
-    int it = 0;
-    // prologue: packing runs ahead of the task sequence
+    auto pack_group = [&](int it) {
+        if ((it << QL2) >= s_blk.npacks) return;
+        wait_on(&s_full[it % RS_STAGES], (uint32_t)(it / RS_STAGES) & 1u);
+        rs_pack<MODEL, NWL2>(s_pt + table_base(it), stage + (size_t)(it % RS_STAGES) * RS_THREADS * 4, W, t);
+    };
+    const int niter = s_blk.niter, prologue = p.prologue;
 #pragma unroll 1
-    for (; it < p.prologue; ++it) {
-        wait_staged(it);
-        rs_pack<MODEL, NWL2>(s_pt[it & 1], stage + (size_t)(it % RS_STAGES) * RS_THREADS * 4, W, t);
-        end_iteration(it);
-    }
-    // steady state: store what the previous iteration computed, one word of the task sequence, pack for a later one.
-    // One straight-line body: the tables send a position beyond an end to the spare row instead of branching.
-    const int last_pack = ((s_blk.npacks + Q - 1) >> QL2) - 1;
-#pragma unroll 1
-    for (; it <= last_pack; ++it) {
-        const int buf = it & 1;
-        wait_staged(it);  // issued two iterations ago: there by now, and the three phases below become one block of code
-        rs_unpack<MODEL, NWL2>(s_ut[buf], W, s_blk.dst16, t);
-        rs_pack<MODEL, NWL2>(s_pt[buf], stage + (size_t)(it % RS_STAGES) * RS_THREADS * 4, W, t);
-        rs_compute<MODEL, NWL2>(s_ct[buf], W, plan, greplica, sweep, L.key, t, dB, dS);
-        end_iteration(it);
-    }
-    // drain: the rest of the sequence, then the last stores
-#pragma unroll 1
-    for (; it < s_blk.niter; ++it) {
-        const int buf = it & 1;
-        rs_unpack<MODEL, NWL2>(s_ut[buf], W, s_blk.dst16, t);
-        if (((it - p.prologue) << QL2) < s_blk.ntasks) rs_compute<MODEL, NWL2>(s_ct[buf], W, plan, greplica, sweep, L.key, t, dB, dS);
-        end_iteration(it);
+    for (int it = 0; it < niter; ++it) {
+        const int tb = table_base(it), kc = it - prologue;
+        if (it >= 2 && t < 32) issue_group(it);  // its slot was packed from in iteration it - 2: every warp is past that
+        if (kc >= 0) {
+            rs_unpack<MODEL, NWL2>(s_ut + tb, W, s_blk.dst16, t);
+            if ((kc << QL2) < s_blk.ntasks) rs_compute<MODEL, NWL2>(s_ct + tb, W, plan, greplica, sweep, L.key, t, dB, dS);
+        }
+        build_tables(it + 1);
+        arrive();
+        pack_group(it);
+        wait_on(&s_done, (uint32_t)it & 1u);
     }
 
     // tracked observables: block sum, one atomic pair

@@ -399,8 +399,14 @@ int rowstream_sweep(Image &im, const uint32_t *thr, uint64_t seed, uint32_t repl
         build_tables(0, 0);
         for (int g = 0; g < RS_STAGES; ++g)
             if (int rc = issue_group(g)) return rc;
+        // A warp arrives at the barrier of an iteration after its share of the task sequence and packs AFTER that: when a
+        // warp starts iteration `it`, every warp has finished the tasks of it - 1 and the packing of it - 2, while the
+        // packing of it - 1 may still be going on in other warps.  So a task may only read packed rows written two
+        // iterations earlier, and a staging slot is refilled two iterations after it was packed from.
         for (int it = 0; it < niter; ++it) {
             const int kc = it - p.prologue, buf = it & 1;
+            if (it >= 2)
+                if (int rc = issue_group(it)) return rc;
             // ---- unpack of what the previous iteration computed
             if (kc >= 1) {
                 for (int q = 0; q < p.Q; ++q) {
@@ -411,17 +417,18 @@ int rowstream_sweep(Image &im, const uint32_t *thr, uint64_t seed, uint32_t repl
                     if (sl.idx != (colour ? idx + 2 : idx) || sl.state != 1 || sl.wr != it - 1) return -20;
                     sl.rd = it;
                 }
-                for (int t = 0; t < T; ++t) rs_unpack<MODEL, NWL2>(ut[buf], W.data(), reinterpret_cast<uint4 *>(dst.data()), t);
             }
+            if (kc >= 0)
+                for (int t = 0; t < T; ++t) rs_unpack<MODEL, NWL2>(ut[buf], W.data(), reinterpret_cast<uint4 *>(dst.data()), t);
             // ---- compute
             if (kc >= 0 && (kc << p.q_log2) < ntasks) {
                 for (int q = 0; q < p.Q; ++q) {  // reads first (all tasks of the iteration run concurrently on the GPU)
                     int colour, idx;
                     if (!rs_task_index(p, n, (kc << p.q_log2) + q, colour, idx)) continue;
                     for (int d = 0; d < 3; ++d) {
-                        // c0[m] reads OLD c1h[m .. m+2]; c1[j] reads NEW c0[j .. j+2]
+                        // c0[m] reads OLD c1h[m .. m+2] (packed: two iterations ago at the latest); c1[j] reads NEW c0[j .. j+2]
                         Slot &sl = colour ? r0[(idx + d) % p.rw] : r1[(idx + d) % p.rw];
-                        if (sl.idx != idx + d || sl.state != (colour ? 1 : 0) || sl.wr >= it) return -30 - colour;
+                        if (sl.idx != idx + d || sl.state != (colour ? 1 : 0) || sl.wr > it - (colour ? 1 : 2)) return -30 - colour;
                         sl.rd = it;
                     }
                 }
@@ -429,14 +436,14 @@ int rowstream_sweep(Image &im, const uint32_t *thr, uint64_t seed, uint32_t repl
                     int colour, idx;
                     if (!rs_task_index(p, n, (kc << p.q_log2) + q, colour, idx)) continue;
                     Slot &sl = colour ? r1[(idx + 2) % p.rw] : r0[idx % p.rw];
-                    if (sl.idx != (colour ? idx + 2 : idx) || sl.state != 0 || sl.wr >= it || sl.rd >= it) return -40 - colour;
+                    if (sl.idx != (colour ? idx + 2 : idx) || sl.state != 0 || sl.wr > it - 2 || sl.rd >= it) return -40 - colour;
                     sl.state = 1;
                     sl.wr = it;
                 }
                 for (int t = 0; t < T; ++t)
                     rs_compute<MODEL, NWL2>(ct[buf], W.data(), plan, replica, sweep, key, t, tdB, tdS);
             }
-            // ---- pack
+            // ---- pack (after the arrival: may overlap the tasks and the unpacking of iteration it + 1 in other warps)
             if ((it << p.q_log2) < npacks) {
                 const int slot = it % RS_STAGES;
                 if (stage_group[slot] != it) return -50;  // the copy for this group was never issued
@@ -447,16 +454,18 @@ int rowstream_sweep(Image &im, const uint32_t *thr, uint64_t seed, uint32_t repl
                     if (sl.wr >= it || sl.rd >= it) return -60;  // somebody uses this slot in this very iteration
                     // what it held must be finished: a stored new row, a halo row, or nothing yet
                     if (sl.idx >= 0 && sl.state == 0 && !(colour == 1 && (sl.idx < 2 || sl.idx > n + 1))) return -61;
+                    // ... and stored already: the unpacking of iteration it + 1 may run beside this packing
+                    if (sl.idx >= 0 && sl.state == 1 && sl.rd <= sl.wr) return -62;
                     sl.idx = idx;
                     sl.state = 0;
                     sl.wr = it;
+                    sl.rd = -1;
                 }
                 for (int t = 0; t < T; ++t)
                     rs_pack<MODEL, NWL2>(pt[buf], stage.data() + (size_t)slot * T * 4, W.data(), t);
                 stage_packed[slot] = 1;
             }
             build_tables(it + 1, buf ^ 1);
-            if (int rc = issue_group(it + RS_STAGES)) return rc;
         }
     }
     for (size_t k = 0; k < dst.size(); ++k)
