@@ -25,11 +25,18 @@
 // are the recomputed halo rows, not stored), c1[j] = colour 1 of row a+j (j = 0 .. n-1).  c1[j] needs the NEW c0 of
 // rows a+j-1 .. a+j+1, i.e. c0[j], c0[j+1], c0[j+2]; c0[m] needs the OLD c1 of rows a+m-2 .. a+m, the last of which
 // c1[m-2] overwrites.  With Q row tasks per iteration (Q = threads / words per row) the order
-//       c0[0] .. c0[Q]   c0[Q+1] c1[0]   c0[Q+2] c1[1]   ...   c0[n+1] c1[n-Q]   c1[n-Q+1] .. c1[n-1]
-// keeps every such pair at least Q positions apart, so the tasks of one iteration are independent and read only
-// what earlier iterations (separated by the block barrier) left.  Packing runs ahead of that sequence by a fixed
-// number of iterations, unpacking and storing trails it by one.  Bit words live in two rings of RW rows (one per
-// colour); the emulation in tests/hostemu checks every read against what the ring slot holds at that time.
+//       c0[0] .. c0[2Q]   c0[2Q+1] c1[0]   c0[2Q+2] c1[1]   ...   c0[n+1] c1[n-2Q]   c1[n-2Q+1] .. c1[n-1]
+// keeps every such pair at least 2Q positions = TWO iterations apart.  That is what lets the block run without a
+// barrier in the usual sense: a warp starting iteration `it` waits only until every warp has finished iteration
+// it - 2 (an mbarrier per iteration parity, one arrival per warp), so the warps of a block may be a whole iteration
+// apart and the spread of the per-lane tail rounds of the Metropolis test -- which parked warps at a __syncthreads
+// for 12 % of their time -- is absorbed.  Everything obeys the same rule: nothing is read that was written less
+// than two iterations earlier (packing runs that far ahead of the sequence, the stores of finished rows trail it
+// by two), nothing is overwritten that was read less than two iterations earlier (ring size), a staging slot is
+// refilled two iterations after it was packed from, and the tables of an iteration are built two iterations
+// before it (by a different warp each time).  Bit words live in two rings of rs_ring_rows(Q) rows (one per colour);
+// the emulation in tests/hostemu checks every read and write against that rule, for what the ring slot holds at
+// that time.
 #pragma once
 #include "pmc_core.cuh"
 #include "pmc_pack.cuh"
@@ -43,26 +50,30 @@ namespace pmc {
 constexpr int RS_THREADS = PMC_RS_THREADS;
 constexpr int RS_STAGES = 2;   // staging slots for the bulk copies (one iteration's rows each)
 constexpr int RS_MAXQ = 64;    // row tasks per iteration: words per colour row >= RS_THREADS / 64
-#ifndef PMC_RS_TABLE_ENTRIES
-#define PMC_RS_TABLE_ENTRIES 160
-#endif
-constexpr int RS_TABLE_ENTRIES = PMC_RS_TABLE_ENTRIES;  // per-iteration tables kept for a whole piece if it has no more row-task slots
+constexpr int RS_TABLES = 4;   // iterations whose tables are kept: built two iterations ahead, read by warps up to one apart
 
 // launch-uniform schedule constants (kernel parameter: constant memory)
 struct RSParams {
     int lenX, nk, nw, nw_log2;
     int Q, q_log2;     // row tasks per iteration (a power of two)
-    int lead;          // c0 tasks before the first c1 task: Q + 1
+    int lead;          // c0 tasks before the first c1 task
     int prologue;      // iterations that only pack
     int rw;            // ring rows per colour
     int pieces;        // pieces per replica
 };
 
-__host__ __device__ constexpr int rs_ring_rows(int Q) { return 3 * Q + 4 + (Q + 1) / 2; }  // checked by the emulation in tests/hostemu
-// iterations that only pack: the rows a task reads must have been packed two iterations before it runs (a warp packs
-// after it has arrived at the barrier of an iteration, so only the packing of the iteration before last is complete)
-__host__ __device__ constexpr int rs_prologue(int Q) { return (2 * Q + 4 + Q - 1) / Q + 1; }
-__host__ __device__ inline int rs_min_rows(int Q) { return 2 * Q + 2; }  // smallest piece the task order is valid for
+// The schedule constants below were found by searching the smallest values for which no hazard occurs when the warps
+// of a block may be up to one whole iteration apart (see the kernel), and are checked for every geometry by the emulation
+// in tests/hostemu (which refuses a read of anything written less than two iterations earlier, and a write over anything
+// read less than two iterations earlier).
+// c0 tasks before the first c1 task: colour 1 of row j reads colour 0 of row j+1 from two iterations back
+__host__ __device__ constexpr int rs_lead(int Q) { return 2 * Q + 1; }
+// ring rows per colour
+__host__ __device__ constexpr int rs_ring_rows(int Q) { return (11 * Q + 1) / 2 + (Q < 4 ? 1 : 0); }
+// iterations that only pack: a task reads rows packed at least two iterations before it runs
+__host__ __device__ constexpr int rs_prologue(int Q) { return (2 * Q + 4 + Q - 1) / Q + 2; }
+__host__ __device__ constexpr int rs_min_rows(int Q) { return 4 * Q + 4; }  // smallest piece the task order is valid for
+constexpr int RS_LAG = 2;  // iterations between a task and the storing of its row (and between any write and a read of it)
 
 // false if the shape cannot be streamed with RS_THREADS threads
 __host__ inline bool rs_make_params(int lenX, int nk, int pieces, RSParams &p) {
@@ -77,7 +88,7 @@ __host__ inline bool rs_make_params(int lenX, int nk, int pieces, RSParams &p) {
     p.Q = RS_THREADS / nw;
     p.q_log2 = 0;
     while ((1 << p.q_log2) < p.Q) ++p.q_log2;
-    p.lead = p.Q + 1;
+    p.lead = rs_lead(p.Q);
     p.prologue = rs_prologue(p.Q);
     p.rw = rs_ring_rows(p.Q);
     p.pieces = pieces;
@@ -104,7 +115,7 @@ __host__ __device__ __forceinline__ int rs_wrap(int i, int lenX) { return i < 0 
 // position in the task sequence -> (colour, index): c0[idx] or c1[idx]; false beyond the end
 __host__ __device__ inline bool rs_task_index(const RSParams &p, int n, int pos, int &colour, int &idx) {
     if (pos < 0 || pos >= 2 * n + 2) return false;
-    const int L = p.lead;  // n >= 2Q + 2 > L
+    const int L = p.lead;  // n >= rs_min_rows(Q) > L
     if (pos < L) {
         colour = 0;
         idx = pos;
@@ -188,7 +199,7 @@ __host__ __device__ inline RSMove rs_build_pack(const RSParams &p, int n, int pp
     return m;
 }
 
-// the task at position pos was computed in the previous iteration: where its row goes
+// the task at position pos was computed RS_LAG iterations ago: where its row goes
 __host__ __device__ inline RSMove rs_build_unpack(const RSParams &p, int a, int n, int pos) {
     RSMove m = {(2 * p.rw) << p.nw_log2, -1};
     int colour, idx;
@@ -249,11 +260,10 @@ __device__ __forceinline__ void rs_compute(const RSCompute *tab, uint64_t *W, co
     const int w = t & (NW - 1);
     const RSCompute c = tab[t >> NWL2];
     const uint64_t S = W[c.own + w], U = W[c.ru + w], C = W[c.rc + w], D = W[c.rd + w];
-    uint64_t Sd;
-    if (c.flags & 8)
-        Sd = (C >> 1) | (W[c.rc + ((w + 1) & (NW - 1))] << 63);
-    else
-        Sd = (C << 1) | (W[c.rc + ((w - 1) & (NW - 1))] >> 63);
+    // the other same-row neighbour: site k+1 (bit 3 of flags) or k-1 -- one load of the word beside C, one funnel shift
+    const bool right = c.flags & 8;
+    const uint64_t nb = W[c.rc + ((w + (right ? 1 : NW - 1)) & (NW - 1))];
+    const uint64_t Sd = right ? ((C >> 1) | (nb << 63)) : ((C << 1) | (nb >> 63));
     int b, s2;
     const uint64_t Snew = update_word<MODEL>(S, U, D, C, Sd, (c.flags & 1) ? ~0ull : 0ull, plan, (uint32_t)(c.widx + w), greplica,
                                              2 * sweep + (uint64_t)((c.flags >> 2) & 1), key, b, s2);
@@ -324,15 +334,14 @@ __global__ void __launch_bounds__(RS_THREADS, 1024 / RS_THREADS)
                      int8_t *__restrict__ dst, uint64_t sweep, int *err) {
     constexpr int Q = RS_THREADS >> NWL2, QL2 = 9 - NWL2 + (RS_THREADS == 256 ? -1 : (RS_THREADS == 1024 ? 1 : 0));
     static_assert((1 << QL2) == Q && Q >= 1 && Q <= RS_MAXQ, "row tasks per iteration");
+    constexpr int NWARPS = RS_THREADS / 32;
     extern __shared__ __align__(128) unsigned char rs_smem[];
-    __shared__ __align__(8) uint64_t s_full[RS_STAGES];
-    __shared__ __align__(8) uint64_t s_done;  // one arrival per warp and iteration: the split block barrier
-    // tables of all iterations of the piece when they fit (built once, one entry per thread), else of three iterations
-    constexpr int TBL = RS_TABLE_ENTRIES > 3 * Q ? RS_TABLE_ENTRIES : 3 * Q;
-    __shared__ __align__(16) RSCompute s_ct[TBL];
-    __shared__ __align__(8) RSMove s_pt[TBL], s_ut[TBL];
+    __shared__ __align__(8) uint64_t s_full[RS_STAGES];  // the bulk copies of a staging slot have landed
+    __shared__ __align__(8) uint64_t s_done[2];          // every warp has finished an iteration (even / odd ones)
+    __shared__ __align__(16) RSCompute s_ct[RS_TABLES * Q];
+    __shared__ __align__(8) RSMove s_pt[RS_TABLES * Q], s_ut[RS_TABLES * Q];
     __shared__ RSBlock s_blk;
-    __shared__ int s_red[2][RS_THREADS / 32];
+    __shared__ int s_red[2][NWARPS];
     uint4 *const stage = reinterpret_cast<uint4 *>(rs_smem);
     uint64_t *const W = reinterpret_cast<uint64_t *>(rs_smem + (size_t)RS_STAGES * RS_THREADS * 64);
 
@@ -343,11 +352,11 @@ __global__ void __launch_bounds__(RS_THREADS, 1024 / RS_THREADS)
     p.nw_log2 = NWL2;
     p.Q = Q;
     p.q_log2 = QL2;
-    p.lead = Q + 1;
+    p.lead = rs_lead(Q);
     p.prologue = rs_prologue(Q);
     p.rw = rs_ring_rows(Q);
 
-    const int t = threadIdx.x, rep = blockIdx.y;
+    const int t = threadIdx.x, rep = blockIdx.y, warp = t >> 5;
     if (t == 0) {
         int a, n;
         rs_piece(p, blockIdx.x, a, n);
@@ -355,11 +364,12 @@ __global__ void __launch_bounds__(RS_THREADS, 1024 / RS_THREADS)
         s_blk.n = n;
         s_blk.ntasks = 2 * n + 2;
         s_blk.npacks = 2 * n + 6;
-        s_blk.niter = p.prologue + ((2 * n + 2 + Q - 1) >> QL2) + 1;
+        s_blk.niter = p.prologue + ((2 * n + 2 + Q - 1) >> QL2) + RS_LAG;
         s_blk.src_rep = src + (size_t)rep * 2 * p.lenX * p.nk;
         s_blk.dst16 = reinterpret_cast<uint4 *>(dst + (size_t)rep * 2 * p.lenX * p.nk);
         for (int s = 0; s < RS_STAGES; ++s) rs_mbar_init(&s_full[s], 1);
-        rs_mbar_init(&s_done, RS_THREADS / 32);
+        rs_mbar_init(&s_done[0], NWARPS);
+        rs_mbar_init(&s_done[1], NWARPS);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
@@ -367,45 +377,31 @@ __global__ void __launch_bounds__(RS_THREADS, 1024 / RS_THREADS)
     Plan<MODEL> plan;
     fetch_plan(L, rep, plan);
 
-    // rows of packing group g -> staging slot g % RS_STAGES (warp 0)
+    // rows of packing group g -> staging slot g % RS_STAGES (one warp; lane = threadIdx.x & 31)
     auto issue_group = [&](int g) {
-        const int first = g << QL2, npacks = s_blk.npacks;
+        const int first = g << QL2, npacks = s_blk.npacks, lane = t & 31;
         if (first >= npacks) return;
         const int nvalid = npacks - first < Q ? npacks - first : Q;
         uint64_t *bar = &s_full[g % RS_STAGES];
-        if (t == 0) rs_mbar_expect_tx(bar, (uint32_t)nvalid * (uint32_t)p.nk);
+        if (lane == 0) rs_mbar_expect_tx(bar, (uint32_t)nvalid * (uint32_t)p.nk);
         __syncwarp();
         unsigned char *slot = rs_smem + (size_t)(g % RS_STAGES) * RS_THREADS * 64;
-        for (int k = t; k < nvalid; k += 32) {
+        for (int k = lane; k < nvalid; k += 32) {
             const RSTask task = rs_pack_task(p, s_blk.a, s_blk.n, first + k);
             const int colour = (task.info >> 16) & 1;
             rs_bulk_load(slot + (size_t)k * p.nk, s_blk.src_rep + ((size_t)colour * p.lenX + task.row) * p.nk, (uint32_t)p.nk, bar);
         }
     };
-    // Tables.  A piece of few enough iterations gets all of them at once (one entry per thread, here); otherwise the
-    // tables of iteration it + 1 are built during iteration it by one lane per task, in the LAST warps of the block
-    // (warp 0 issues the copies), and three iterations' worth of entries rotate (a warp that has arrived at the barrier of
-    // iteration it - 1 may still be packing from that iteration's table while the builder is already in iteration it).
-    const bool all_tables = s_blk.niter * Q <= TBL;
-    auto build_entry = [&](int it, int k, int at) {
-        const int kc = it - p.prologue, a = s_blk.a, n = s_blk.n;
+    // tables of iteration `it`, entry k (one lane per row task)
+    auto build_entry = [&](int it, int k) {
+        const int kc = it - p.prologue, a = s_blk.a, n = s_blk.n, at = ((it % RS_TABLES) << QL2) + k;
         s_ct[at] = rs_build_compute(p, a, n, (kc << QL2) + k);
         s_pt[at] = rs_build_pack(p, n, (it << QL2) + k);
-        s_ut[at] = rs_build_unpack(p, a, n, ((kc - 1) << QL2) + k);
+        s_ut[at] = rs_build_unpack(p, a, n, ((kc - RS_LAG) << QL2) + k);
     };
-    auto build_tables = [&](int it) {
-        if (all_tables) return;
-        const int k = RS_THREADS - 1 - t;
-        if (k < Q) build_entry(it, k, ((it % 3) << QL2) + k);
-    };
-    auto table_base = [&](int it) { return all_tables ? it << QL2 : (it % 3) << QL2; };
-    if (all_tables) {
-        for (int e = t; e < s_blk.niter * Q; e += RS_THREADS) build_entry(e >> QL2, e & (Q - 1), e);
-    } else {
-        build_tables(0);
-    }
+    if (t < 2 * Q) build_entry(t >> QL2, t & (Q - 1));  // iterations 0 and 1
     __syncthreads();
-    if (t < 32)
+    if (warp == 0)
         for (int g = 0; g < RS_STAGES; ++g) issue_group(g);
 
     int dB = 0, dS = 0;
@@ -421,36 +417,32 @@ __global__ void __launch_bounds__(RS_THREADS, 1024 / RS_THREADS)
             }
         }
     };
-    // The block barrier of an iteration, split.  A warp ARRIVES when it has finished its share of the task sequence
-    // (what the other warps wait for), then packs rows for a later iteration -- nobody reads those before the
-    // barrier after next -- and only then WAITS for the slowest warp: the spread of the per-lane tail rounds between
-    // warps is absorbed by the packing instead of idling.  What follows the wait may read what any warp computed
-    // before its arrival.  A staging slot is free again once every warp has arrived for the iteration AFTER the one
-    // that packed from it (a warp packs after arriving), so the copies for group it + 1 are issued at the start of
-    // iteration it + 1 and have one compute phase to land.
-    auto arrive = [&]() {
-        __syncwarp();
-        if ((t & 31) == 0) rs_mbar_arrive(&s_done);
-    };
-    auto pack_group = [&](int it) {
-        if ((it << QL2) >= s_blk.npacks) return;
-        wait_on(&s_full[it % RS_STAGES], (uint32_t)(it / RS_STAGES) & 1u);
-        rs_pack<MODEL, NWL2>(s_pt + table_base(it), stage + (size_t)(it % RS_STAGES) * RS_THREADS * 4, W, t);
-    };
     const int niter = s_blk.niter, prologue = p.prologue;
 #pragma unroll 1
     for (int it = 0; it < niter; ++it) {
-        const int tb = table_base(it), kc = it - prologue;
-        if (it >= 2 && t < 32) issue_group(it);  // its slot was packed from in iteration it - 2: every warp is past that
+        const int tb = (it % RS_TABLES) << QL2, kc = it - prologue;
+        if (it >= 2) {
+            // every warp has finished iteration it - 2: what it computed and packed may be read, what it read may be
+            // overwritten, the staging slot it packed from may be refilled, the tables built during it are complete
+            wait_on(&s_done[it & 1], (uint32_t)((it - 2) >> 1) & 1u);
+            if (warp == (it + NWARPS / 2) % NWARPS) issue_group(it);
+        }
         if (kc >= 0) {
             rs_unpack<MODEL, NWL2>(s_ut + tb, W, s_blk.dst16, t);
             if ((kc << QL2) < s_blk.ntasks) rs_compute<MODEL, NWL2>(s_ct + tb, W, plan, greplica, sweep, L.key, t, dB, dS);
         }
-        build_tables(it + 1);
-        arrive();
-        pack_group(it);
-        wait_on(&s_done, (uint32_t)it & 1u);
+        if ((it << QL2) < s_blk.npacks) {
+            wait_on(&s_full[it % RS_STAGES], (uint32_t)(it / RS_STAGES) & 1u);
+            rs_pack<MODEL, NWL2>(s_pt + tb, stage + (size_t)(it % RS_STAGES) * RS_THREADS * 4, W, t);
+        }
+        {  // the tables of iteration it + 2: a different warp (two for Q = 64) every time, so that no warp is always behind
+            const int k = (((warp + NWARPS - it % NWARPS) % NWARPS) << 5) + (t & 31);
+            if (k < Q) build_entry(it + 2, k);
+        }
+        __syncwarp();
+        if ((t & 31) == 0) rs_mbar_arrive(&s_done[it & 1]);
     }
+    __syncthreads();
 
     // tracked observables: block sum, one atomic pair
     dB = __reduce_add_sync(0xFFFFFFFFu, dB);
@@ -463,7 +455,7 @@ __global__ void __launch_bounds__(RS_THREADS, 1024 / RS_THREADS)
     if (t < 2) {
         int v = 0;
 #pragma unroll
-        for (int k = 0; k < RS_THREADS / 32; ++k) v += s_red[t][k];
+        for (int k = 0; k < NWARPS; ++k) v += s_red[t][k];
         if (v) atomicAdd(L.tracked + 2 * (size_t)rep + t, (unsigned long long)(long long)v);
     }
 }

@@ -42,9 +42,9 @@ static const size_t PBATCH_AUTO_MIN_SITES = (size_t)128 * 128;
 static const size_t PBATCH_SINGLE_MIN_SITES = (size_t)128 * 128;
 // PYMC_KERNEL_AUTO runs the sweeps the resident kernels do not take (single-sweep calls, lattices beyond the chip) on the
 // row-streaming kernel K13 instead of the tiled one from this many sites (all replicas together) and this many words per
-// colour row on.  Measured (profiles/r2_rowstream_probe.json, ms per sweep K13 / tiled): 16384^2 0.1697 / 0.1760,
-// 16 x 4096^2 0.1732 / 0.1761, 8192^2 0.0499 / 0.0501; below that a piece per resident block is too short (4096^2 0.0226 /
-// 0.0169) and narrow rows put too many row tasks into one iteration (256 x 1024^2: 0.223 / 0.174).
+// colour row on.  Measured (profiles/r2_rowstream_probe.json, ms per sweep K13 / tiled): 16384^2 0.1592 / 0.1761,
+// 16 x 4096^2 0.1653 / 0.1761; below that the pieces (at least 4Q + 4 rows each) no longer fill two blocks per SM (8192^2
+// 0.059 / 0.050, 4096^2 0.034 / 0.017) and narrow rows put too many row tasks into one iteration (256 x 1024^2: 0.28 / 0.17).
 static const size_t ROWSTREAM_AUTO_MIN_SITES = (size_t)1 << 27;
 static const int ROWSTREAM_AUTO_MIN_NW = 32;
 #ifndef PMC_PERSIST_AUTO

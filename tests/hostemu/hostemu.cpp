@@ -332,10 +332,12 @@ namespace {
 
 // The row-streaming kernel's schedule and per-thread phases (pmc_rowstream.cuh) on the host: piece after piece,
 // iteration after iteration, thread after thread, with the bulk copies replaced by memcpy at the point where the kernel
-// issues them.  Besides the result (compared by the caller with the plain sweep) it checks what the sequential
-// order of the emulation would otherwise hide: every ring slot read holds the row the reader means, in the state it
-// needs (old / new), written in an EARLIER iteration; no slot is written in the iteration in which another task
-// reads it; a staging slot is refilled only after it has been packed.
+// issues them.  The warps of a block may be a whole iteration apart on the GPU (a warp starting iteration `it` has only
+// waited for every warp to finish iteration it - 2), so besides the result (compared by the caller with the plain sweep)
+// the emulation enforces the rule that makes that safe: every ring slot read holds the row the reader means, in the state
+// it needs (old / new), written at least TWO iterations earlier; no slot is written that was read or written less than two
+// iterations earlier; a row is stored exactly two iterations after it was computed and not overwritten before; a staging
+// slot is refilled two iterations after it was packed from.
 template <int MODEL, int NWL2>
 int rowstream_sweep(Image &im, const uint32_t *thr, uint64_t seed, uint32_t replica, uint64_t sweep, int pieces, long long *dB,
                     long long *dS) {
@@ -343,7 +345,6 @@ int rowstream_sweep(Image &im, const uint32_t *thr, uint64_t seed, uint32_t repl
     RSParams p;
     if (!rs_make_params(lenX, nk, pieces, p)) return -2;
     if (p.nw_log2 != NWL2) return -2;
-
     const int nw = p.nw, RW = p.rw, T = RS_THREADS;
     // colour-split int8 source and destination [2][lenX][nk]
     std::vector<int8_t> src((size_t)2 * lenX * nk), dst((size_t)2 * lenX * nk, 77);
@@ -361,30 +362,22 @@ int rowstream_sweep(Image &im, const uint32_t *thr, uint64_t seed, uint32_t repl
         rs_piece(p, piece, a, n);
         if (n < rs_min_rows(p.Q)) return -3;
         const int ntasks = 2 * n + 2, npacks = 2 * n + 6;
-        const int niter = p.prologue + ((ntasks + p.Q - 1) >> p.q_log2) + 1;
+        const int niter = p.prologue + ((ntasks + p.Q - 1) >> p.q_log2) + RS_LAG;
         std::vector<uint4> stage((size_t)RS_STAGES * T * 4);
-        std::vector<int> stage_group(RS_STAGES, -1), stage_packed(RS_STAGES, 1);
+        std::vector<int> stage_group(RS_STAGES, -1), stage_packed_at(RS_STAGES, -100);
         std::vector<uint64_t> W((size_t)(2 * RW + 1) * nw, 0xAAAAAAAAAAAAAAAAull);
         // per ring slot: index held, state (0 old, 1 new), iteration of the last write / of the last read by another task
         struct Slot {
-            int idx = -1000, state = -1, wr = -1, rd = -1;
+            int idx = -1000, state = -1, wr = -100, rd = -100;
         };
         std::vector<Slot> r0(RW), r1(RW);
-        RSCompute ct[2][RS_MAXQ];
-        RSMove pt[2][RS_MAXQ], ut[2][RS_MAXQ];
-        auto build_tables = [&](int it, int buf) {
-            const int kc = it - p.prologue;
-            for (int k = 0; k < p.Q; ++k) {
-                ct[buf][k] = rs_build_compute(p, a, n, (kc << p.q_log2) + k);
-                pt[buf][k] = rs_build_pack(p, n, (it << p.q_log2) + k);
-                ut[buf][k] = rs_build_unpack(p, a, n, ((kc - 1) << p.q_log2) + k);
-            }
-        };
-        auto issue_group = [&](int g) -> int {
+        RSCompute ct[RS_MAXQ];
+        RSMove pt[RS_MAXQ], ut[RS_MAXQ];
+        auto issue_group = [&](int g, int it) -> int {
             const int first = g << p.q_log2;
             if (first >= npacks) return 0;
             const int slot = g % RS_STAGES;
-            if (!stage_packed[slot]) return -10;  // refilled before it was packed
+            if (stage_group[slot] >= 0 && stage_packed_at[slot] > it - 2) return -10;  // refilled too early
             const int nvalid = npacks - first < p.Q ? npacks - first : p.Q;
             for (int k = 0; k < nvalid; ++k) {
                 const RSTask task = rs_pack_task(p, a, n, first + k);
@@ -393,42 +386,42 @@ int rowstream_sweep(Image &im, const uint32_t *thr, uint64_t seed, uint32_t repl
                        src.data() + ((size_t)colour * lenX + task.row) * nk, nk);
             }
             stage_group[slot] = g;
-            stage_packed[slot] = 0;
+            stage_packed_at[slot] = 1 << 30;  // not packed yet
             return 0;
         };
-        build_tables(0, 0);
         for (int g = 0; g < RS_STAGES; ++g)
-            if (int rc = issue_group(g)) return rc;
-        // A warp arrives at the barrier of an iteration after its share of the task sequence and packs AFTER that: when a
-        // warp starts iteration `it`, every warp has finished the tasks of it - 1 and the packing of it - 2, while the
-        // packing of it - 1 may still be going on in other warps.  So a task may only read packed rows written two
-        // iterations earlier, and a staging slot is refilled two iterations after it was packed from.
+            if (int rc = issue_group(g, -100)) return rc;
         for (int it = 0; it < niter; ++it) {
-            const int kc = it - p.prologue, buf = it & 1;
+            const int kc = it - p.prologue;
+            for (int k = 0; k < p.Q; ++k) {
+                ct[k] = rs_build_compute(p, a, n, (kc << p.q_log2) + k);
+                pt[k] = rs_build_pack(p, n, (it << p.q_log2) + k);
+                ut[k] = rs_build_unpack(p, a, n, ((kc - RS_LAG) << p.q_log2) + k);
+            }
             if (it >= 2)
-                if (int rc = issue_group(it)) return rc;
-            // ---- unpack of what the previous iteration computed
-            if (kc >= 1) {
+                if (int rc = issue_group(it, it)) return rc;
+            // ---- store what iteration it - RS_LAG computed
+            if (kc >= RS_LAG) {
                 for (int q = 0; q < p.Q; ++q) {
                     int colour, idx;
-                    if (!rs_task_index(p, n, ((kc - 1) << p.q_log2) + q, colour, idx)) continue;
+                    if (!rs_task_index(p, n, ((kc - RS_LAG) << p.q_log2) + q, colour, idx)) continue;
                     if (colour == 0 && (idx < 1 || idx > n)) continue;
                     Slot &sl = colour ? r1[(idx + 2) % p.rw] : r0[idx % p.rw];
-                    if (sl.idx != (colour ? idx + 2 : idx) || sl.state != 1 || sl.wr != it - 1) return -20;
+                    if (sl.idx != (colour ? idx + 2 : idx) || sl.state != 1 || sl.wr != it - RS_LAG) return -20;
                     sl.rd = it;
                 }
             }
             if (kc >= 0)
-                for (int t = 0; t < T; ++t) rs_unpack<MODEL, NWL2>(ut[buf], W.data(), reinterpret_cast<uint4 *>(dst.data()), t);
-            // ---- compute
+                for (int t = 0; t < T; ++t) rs_unpack<MODEL, NWL2>(ut, W.data(), reinterpret_cast<uint4 *>(dst.data()), t);
+            // ---- the tasks of this iteration
             if (kc >= 0 && (kc << p.q_log2) < ntasks) {
-                for (int q = 0; q < p.Q; ++q) {  // reads first (all tasks of the iteration run concurrently on the GPU)
+                for (int q = 0; q < p.Q; ++q) {  // reads first
                     int colour, idx;
                     if (!rs_task_index(p, n, (kc << p.q_log2) + q, colour, idx)) continue;
                     for (int d = 0; d < 3; ++d) {
-                        // c0[m] reads OLD c1h[m .. m+2] (packed: two iterations ago at the latest); c1[j] reads NEW c0[j .. j+2]
+                        // c0[m] reads OLD c1h[m .. m+2]; c1[j] reads NEW c0[j .. j+2]
                         Slot &sl = colour ? r0[(idx + d) % p.rw] : r1[(idx + d) % p.rw];
-                        if (sl.idx != idx + d || sl.state != (colour ? 1 : 0) || sl.wr > it - (colour ? 1 : 2)) return -30 - colour;
+                        if (sl.idx != idx + d || sl.state != (colour ? 1 : 0) || sl.wr > it - 2) return -30 - colour;
                         sl.rd = it;
                     }
                 }
@@ -436,14 +429,13 @@ int rowstream_sweep(Image &im, const uint32_t *thr, uint64_t seed, uint32_t repl
                     int colour, idx;
                     if (!rs_task_index(p, n, (kc << p.q_log2) + q, colour, idx)) continue;
                     Slot &sl = colour ? r1[(idx + 2) % p.rw] : r0[idx % p.rw];
-                    if (sl.idx != (colour ? idx + 2 : idx) || sl.state != 0 || sl.wr > it - 2 || sl.rd >= it) return -40 - colour;
+                    if (sl.idx != (colour ? idx + 2 : idx) || sl.state != 0 || sl.wr > it - 2 || sl.rd > it - 2) return -40 - colour;
                     sl.state = 1;
                     sl.wr = it;
                 }
-                for (int t = 0; t < T; ++t)
-                    rs_compute<MODEL, NWL2>(ct[buf], W.data(), plan, replica, sweep, key, t, tdB, tdS);
+                for (int t = 0; t < T; ++t) rs_compute<MODEL, NWL2>(ct, W.data(), plan, replica, sweep, key, t, tdB, tdS);
             }
-            // ---- pack (after the arrival: may overlap the tasks and the unpacking of iteration it + 1 in other warps)
+            // ---- pack
             if ((it << p.q_log2) < npacks) {
                 const int slot = it % RS_STAGES;
                 if (stage_group[slot] != it) return -50;  // the copy for this group was never issued
@@ -451,21 +443,18 @@ int rowstream_sweep(Image &im, const uint32_t *thr, uint64_t seed, uint32_t repl
                     int colour, idx;
                     if (!rs_pack_index(n, (it << p.q_log2) + q, colour, idx)) continue;
                     Slot &sl = colour ? r1[idx % p.rw] : r0[idx % p.rw];
-                    if (sl.wr >= it || sl.rd >= it) return -60;  // somebody uses this slot in this very iteration
+                    if (sl.wr > it - 2 || sl.rd > it - 2) return -60;  // still in use by a warp one iteration behind
                     // what it held must be finished: a stored new row, a halo row, or nothing yet
                     if (sl.idx >= 0 && sl.state == 0 && !(colour == 1 && (sl.idx < 2 || sl.idx > n + 1))) return -61;
-                    // ... and stored already: the unpacking of iteration it + 1 may run beside this packing
-                    if (sl.idx >= 0 && sl.state == 1 && sl.rd <= sl.wr) return -62;
+                    if (sl.idx >= 0 && sl.state == 1 && sl.rd < sl.wr + RS_LAG) return -62;  // ... and stored
                     sl.idx = idx;
                     sl.state = 0;
                     sl.wr = it;
-                    sl.rd = -1;
+                    sl.rd = -100;
                 }
-                for (int t = 0; t < T; ++t)
-                    rs_pack<MODEL, NWL2>(pt[buf], stage.data() + (size_t)slot * T * 4, W.data(), t);
-                stage_packed[slot] = 1;
+                for (int t = 0; t < T; ++t) rs_pack<MODEL, NWL2>(pt, stage.data() + (size_t)slot * T * 4, W.data(), t);
+                stage_packed_at[slot] = it;
             }
-            build_tables(it + 1, buf ^ 1);
         }
     }
     for (size_t k = 0; k < dst.size(); ++k)

@@ -44,8 +44,8 @@ def _run(model, shape, thr, kernel, nrep, nsweeps, seed=11, pieces=None):
     return out
 
 
-@pytest.mark.parametrize("nrep,shape,pieces", [(1, (130, 1024), 1), (1, (262, 1024), 2), (3, (140, 2048), 2), (1, (60, 16384), 3),
-                                               (2, (38, 4096), 1), (1, (36, 8192), 2), (1, (700, 2048), None)])
+@pytest.mark.parametrize("nrep,shape,pieces", [(1, (260, 1024), 1), (1, (526, 1024), 2), (3, (270, 2048), 2), (1, (60, 16384), 3),
+                                               (2, (70, 4096), 1), (1, (74, 8192), 2), (1, (700, 2048), None)])
 @pytest.mark.parametrize("model", [0, 1])
 def test_matches_two_pass_kernel_after_every_sweep(nrep, shape, pieces, model):
     from py_mc_b200 import _cabi
@@ -64,7 +64,7 @@ def test_matches_two_pass_kernel_after_every_sweep(nrep, shape, pieces, model):
 def test_against_the_oracle():
     from py_mc_b200 import _cabi
     from oracle import ising as o_ising
-    seed, shape = 20260611, (130, 1024)
+    seed, shape = 20260611, (260, 1024)
     thr = o_ising.threshold_table(-1.0, TC)
     lat = _cabi.Lattices(_cabi.MODEL_ISING, shape[0], shape[1], seed=seed, kernel=_cabi.KERNEL_ROWSTREAM)
     lat.init_random()

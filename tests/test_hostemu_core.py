@@ -144,21 +144,22 @@ def test_batch_resident_kernel_logic_matches_specification(core, nrep, shape, nb
 
 
 @pytest.mark.parametrize("shape,pieces", [
-    ((130, 1024), 1),    # 8 words per row, 64 row tasks per iteration: the smallest piece the task order allows
-    ((262, 1024), 2),    # two ragged pieces; the halo rows of one are the first / last rows of the other
-    ((70, 2048), 1),
-    ((38, 4096), 1),
-    ((56, 8192), 3),
-    ((10, 16384), 1),    # 128 words per row, 4 row tasks per iteration (the headline geometry), shortest piece
+    ((260, 1024), 1),    # 8 words per row, 64 row tasks per iteration: the smallest piece the task order allows
+    ((526, 1024), 2),    # two ragged pieces; the halo rows of one are the first / last rows of the other
+    ((132, 2048), 1),
+    ((68, 4096), 1),
+    ((110, 8192), 3),
+    ((20, 16384), 1),    # 128 words per row, 4 row tasks per iteration (the headline geometry), shortest piece
     ((62, 16384), 3),
     ((46, 16384), 2),
 ])
 def test_row_streaming_kernel_logic_matches_specification(core, shape, pieces):
     """pmc_rowstream.cuh piece after piece on the host: the task order (colour 1 of row j a fixed distance behind
     colour 0 of row j+1), the packing order running ahead of it, the ring of bit rows, the staging slots and the
-    per-iteration tables.  The emulation checks every read of a ring slot against what the slot holds at that time
-    and refuses a write into a slot another task of the same iteration reads (tests/hostemu/hostemu.cpp); the result
-    is compared with the numpy specification, sums included."""
+    per-iteration tables.  The warps of a block may be a whole iteration apart on the GPU, so the emulation checks
+    every read of a ring slot against what the slot holds at that time and refuses to read anything written, or to
+    overwrite anything read, less than two iterations earlier (tests/hostemu/hostemu.cpp); the result is compared
+    with the numpy specification, sums included."""
     seed, replica, J, kT = 91, 2, -1.0, 2.3
     ref = o_ising.init_config(seed, replica, *shape)
     cfg = ref.copy()
