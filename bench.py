@@ -699,6 +699,8 @@ def run_slab(args):
     clocks = sampler.stop()
     sl.check()
     b, m = sl.observables()
+    kname = sl.lat.sweep_kernel_for(args.steps)[1]
+    on_chip = kname == "pbatch_kernel"
     if rank == 0:
         nsites = L * L
         print(json.dumps({
@@ -706,10 +708,15 @@ def run_slab(args):
             "steps": args.steps, "warmup": args.warmup, "repeats": rep, "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": headline_config(args, world),
             "workload_detail": {"rows_per_gpu": L // world, "bond_sum": b, "magnetisation": m,
-                                "parallelism": "row slabs; halo rows stored into peer memory by the sweep kernel, neighbour "
-                                               "barrier inside the kernel, no NCCL in the timed region"},
-            "clocks": clocks, "gpu_launches": args.steps,
-            "roofline": roofline_block("sweep_fused_i8_kernel", 2.0 * nsites / world, ms / args.steps, False),
+                                "parallelism": ("row slabs kept in the shared memory of each GPU for all sweeps of a call; the first / last row "
+                                                "of every colour pass goes to the neighbouring GPUs as {data, pass number} packets stored "
+                                                "into their exchange buffers over NVLink: one launch per GPU, no NCCL, no host in the loop")
+                                               if on_chip else
+                                               ("row slabs; halo rows stored into peer memory by the sweep kernel, neighbour "
+                                                "barrier inside the kernel, no NCCL in the timed region")},
+            "clocks": clocks, "gpu_launches": 1 if on_chip else args.steps,
+            "roofline": roofline_block(kname, 2.0 * nsites / world * (args.steps if on_chip else 1),
+                                       ms if on_chip else ms / args.steps, on_chip),
         }), flush=True)
     grp.close()
 

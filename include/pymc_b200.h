@@ -195,12 +195,14 @@ int pymc_propose(pymc_handle *h, int replica, const int32_t *x, const int32_t *y
  *   [slab_index*lenX/nslabs, +lenX/nslabs) plus two halo rows on either side.  int8 layout, fused
  *   sweep kernel; needs (lenX/nslabs) % 32 == 0 and lenY % 1024 == 0.  The random stream is indexed by
  *   whole-lattice rows, so the union of the slabs follows exactly the single-GPU trajectory.
- * pymc_slab_ipc_export / pymc_slab_connect: each process exports three CUDA IPC handles (its two
- *   lattice buffers and its flag words, 3 x 64 bytes) and is given those of the slab above and below
- *   (periodic).  After that pymc_sweep stores the first/last two rows it computes straight into the
- *   neighbours' halo rows over NVLink from inside the sweep kernel, and a one-thread kernel per sweep
- *   does the neighbour barrier through the flag words (bounded wait: pymc_slab_status reports 1 if a
- *   neighbour never arrived).  All slabs must issue the same pymc_sweep calls.
+ * pymc_slab_ipc_export / pymc_slab_connect: each process exports four CUDA IPC handles (its two lattice buffers, its
+ *   flag words and the exchange buffer of the batch-resident kernel: 4 x 64 bytes) and is given those of the slab above
+ *   and below (periodic).  After that a pymc_sweep call of ONE sweep stores the first/last two rows it computes straight
+ *   into the neighbours' halo rows over NVLink from inside the tiled sweep kernel, with the neighbour barrier in the same
+ *   kernel (bounded wait: pymc_slab_status reports 1 if a neighbour never arrived); a call of TWO OR MORE sweeps keeps the
+ *   slab in the shared memory of the GPU for the whole call (pbatch_kernel) and hands the first / last row of every
+ *   colour pass to the neighbouring GPUs as {data, pass number} packets stored into their exchange buffers (peer
+ *   memory): one launch per GPU and call, no host and no NCCL in between.  All slabs must issue the same pymc_sweep calls.
  * pymc_upload_config / pymc_download_config move the owned rows only ((lenX/nslabs)*lenY sites);
  *   after uploads, every slab calls pymc_slab_push_halos once.  pymc_init_random needs no exchange.
  * pymc_reduce_observables / pymc_get_tracked return this slab's share: add them up over the slabs. */

@@ -393,12 +393,12 @@ class Lattices:
 
     # -- row slabs (one lattice over several GPUs)
     def slab_ipc_export(self):
-        buf = (C.c_char * 192)()
-        check(lib.pymc_slab_ipc_export(self._h, buf, 192))
+        buf = (C.c_char * 256)()
+        check(lib.pymc_slab_ipc_export(self._h, buf, 256))
         return bytes(buf)
 
     def slab_connect(self, up_handles, down_handles):
-        check(lib.pymc_slab_connect(self._h, C.c_char_p(up_handles), C.c_char_p(down_handles), 192))
+        check(lib.pymc_slab_connect(self._h, C.c_char_p(up_handles), C.c_char_p(down_handles), 256))
 
     def slab_connect_local(self, up, down):
         check(lib.pymc_slab_connect_local(self._h, up._h, down._h))

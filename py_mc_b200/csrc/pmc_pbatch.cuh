@@ -160,11 +160,15 @@ struct PBCtx {
     const int *segoff;           // [nseg] row-in-replica minus local row, per replica of this block
     const int *segstart;         // [nseg] first local row of each replica of this block (segstart[0] = 0)
     const uint32_t *splan;       // [nseg][PLAN_WORDS] plan row of each replica (its current temperature)
-    PBPacket *xbuf;              // [2 colours][nslots][nw] exchange buffer (global), zeroed before the launch
+    PBPacket *xbuf;              // [2 colours][nslots][nw] exchange buffer (global); pass numbers only ever grow
+    PBPacket *xbuf_up, *xbuf_dn; // where row 0 / the last row of the lattice is exported to: this buffer, or -- one lattice
+                                 // in row slabs over several GPUs -- the exchange buffer of the GPU above / below (peer memory)
+    unsigned int epoch;          // added to every pass number: launches never see each other's packets
+    int row0;                    // row of the whole lattice of local row 0 of replica 0 (random-stream index; slabs)
     unsigned int *abort_word;    // global: set when a wait has timed out
     int *err;
     int lenX, nw, nw_shift;      // nw_shift >= 0: nw is that power of two
-    int nslots, b;
+    int nslots, b, nblocks;
     uint32_t rep_offset;
     const PhiloxKey *key;        // round keys (in the kernel parameters: constant memory)
 };
@@ -192,13 +196,13 @@ __device__ __forceinline__ uint64_t pb_get(const PBPacket *p, unsigned int need,
 #ifdef __CUDA_ARCH__
     uint64_t a, b;
     asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
-    if ((unsigned int)(a >> 32) < need || (unsigned int)(b >> 32) < need) {
+    if ((int)((unsigned int)(a >> 32) - need) < 0 || (int)((unsigned int)(b >> 32) - need) < 0) {
         const long long t0 = clock64();
         unsigned int spins = 0;
         for (;;) {
             __nanosleep(20);
             asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
-            if ((unsigned int)(a >> 32) >= need && (unsigned int)(b >> 32) >= need) break;
+            if ((int)((unsigned int)(a >> 32) - need) >= 0 && (int)((unsigned int)(b >> 32) - need) >= 0) break;
             if ((++spins & 1023u) == 0) {
                 if (*(volatile unsigned int *)abort_word) break;
                 if (clock64() - t0 > 4000000000LL) {
@@ -212,7 +216,7 @@ __device__ __forceinline__ uint64_t pb_get(const PBPacket *p, unsigned int need,
     return (a & 0xFFFFFFFFull) | (b << 32);
 #else
     // the host drives the blocks in lock step: the packets must be there already
-    if ((unsigned int)(p->lo >> 32) < need || (unsigned int)(p->hi >> 32) < need) *err = 1;
+    if ((int)((unsigned int)(p->lo >> 32) - need) < 0 || (int)((unsigned int)(p->hi >> 32) - need) < 0) *err = 1;
     (void)abort_word;
     return (p->lo & 0xFFFFFFFFull) | (p->hi << 32);
 #endif
@@ -283,7 +287,13 @@ __device__ __forceinline__ void pb_neighbours(const PBGeom &g, int lenX, int lr,
 __device__ __forceinline__ uint64_t pb_row_word(const PBGeom &g, const PBCtx &c, int oc, int row, int w, unsigned int need) {
     if (row >= 0) return c.s[((size_t)oc * g.nrows + row) * c.nw + w];
     const int k = -1 - row;
-    return pb_get(c.xbuf + ((size_t)oc * c.nslots + g.imp_slot[k]) * c.nw + w, need, c.err, c.abort_word);
+    return pb_get(c.xbuf + ((size_t)oc * c.nslots + g.imp_slot[k]) * c.nw + w, c.epoch + need, c.err, c.abort_word);
+}
+
+// Where the word of export slot `slot` goes: the slots of a replica's row 0 / last row (what a block at the other end of
+// the replica reads) are those a neighbouring GPU reads when one lattice is cut into row slabs.
+__device__ __forceinline__ PBPacket *pb_export_buffer(const PBCtx &c, int slot, int B) {
+    return slot < 2 * B ? c.xbuf : (((slot - 2 * B) & 1) ? c.xbuf_dn : c.xbuf_up);
 }
 
 // One colour pass of one thread.  `events` = 1 + number of passes since the load: the pass number the packets of
@@ -328,13 +338,15 @@ __device__ __forceinline__ void pb_pass(const PBGeom &g, const PBCtx &c, int col
             Sd = (C << 1) | (so[w == 0 ? idx + nw - 1 : idx - 1] >> 63);
         const uint64_t U = pb_row_word(g, c, oc, up, w, events), D = pb_row_word(g, c, oc, dn, w, events);
         int dB, dS;  // unused: the sums are recomputed where they are needed (pb_reduce)
-        const uint64_t Snew = update_word<MODEL>(S, U, D, C, Sd, on ? ~0ull : 0ull, plan, (uint32_t)(i * nw + w),
+        const uint64_t Snew = update_word<MODEL>(S, U, D, C, Sd, on ? ~0ull : 0ull, plan, (uint32_t)((i + c.row0) * nw + w),
                                                  rep0 + (uint32_t)seg, step, *c.key, dB, dS);
         if (on) {
             sc[idx] = Snew;
             if (o < nexport)
                 for (int e = 0; e < g.nexp; ++e)
-                    if (g.exp_row[e] == lr) pb_put(c.xbuf + ((size_t)colour * c.nslots + g.exp_slot[e]) * nw + w, Snew, events + 1u);
+                    if (g.exp_row[e] == lr)
+                        pb_put(pb_export_buffer(c, g.exp_slot[e], c.nblocks) + ((size_t)colour * c.nslots + g.exp_slot[e]) * nw + w, Snew,
+                               c.epoch + events + 1u);
         }
     }
     if (T >= items) return;
@@ -387,7 +399,7 @@ __device__ __forceinline__ void pb_pass(const PBGeom &g, const PBCtx &c, int col
         else
             Sd = (C << 1) | (so[on ? o + left : 0] >> 63);
         int dB, dS;
-        const uint64_t Snew = update_word<MODEL>(S, so[ou], so[od], C, Sd, on ? ~0ull : 0ull, plan, (uint32_t)(i * nw + w),
+        const uint64_t Snew = update_word<MODEL>(S, so[ou], so[od], C, Sd, on ? ~0ull : 0ull, plan, (uint32_t)((i + c.row0) * nw + w),
                                                  rep0 + (uint32_t)seg, step, *c.key, dB, dS);
         if (on) sc[o] = Snew;
         if (strided) {
@@ -406,7 +418,8 @@ __device__ __forceinline__ void pb_publish_loaded(const PBGeom &g, const PBCtx &
     for (int k = t; k < 2 * g.nexp * c.nw; k += T) {
         const int colour = k / (g.nexp * c.nw), r = k - colour * g.nexp * c.nw;
         const int e = r / c.nw, w = r - e * c.nw;
-        pb_put(c.xbuf + ((size_t)colour * c.nslots + g.exp_slot[e]) * c.nw + w, c.s[((size_t)colour * g.nrows + g.exp_row[e]) * c.nw + w], 1u);
+        pb_put(pb_export_buffer(c, g.exp_slot[e], c.nblocks) + ((size_t)colour * c.nslots + g.exp_slot[e]) * c.nw + w,
+               c.s[((size_t)colour * g.nrows + g.exp_row[e]) * c.nw + w], c.epoch + 1u);
     }
 }
 
@@ -516,7 +529,10 @@ struct PBatchArgs {
     unsigned long long round0;     // the handle's exchange round at entry
     unsigned int *bar;             // [2] grid barrier arrivals and the abort word, zeroed by the host before the launch
     int *err;
-    PBPacket *xbuf;                // [2][nslots][nw], zeroed by the host before the launch (pass numbers start at 1)
+    PBPacket *xbuf;                // [2][nslots][nw]; zeroed once, pass numbers = epoch + 1, 2, ... grow from launch to launch
+    PBPacket *xbuf_up, *xbuf_dn;   // = xbuf, or the exchange buffers of the GPUs holding the slab above / below (CUDA IPC mappings)
+    unsigned int epoch;            // first pass number of this launch minus 1: the same on every GPU of a slab run
+    int row0;                      // slab: row of the whole lattice of my first owned row (0 otherwise)
     long long *esum;               // [2 parities][R][2] per-replica exact sums of an exchange, indexed by GLOBAL replica;
                                    // the local slice is zeroed by the host before the launch (blocks add deltas)
     // replicas spread over several GPUs (pymc_rx_connect): the all-gather of the energies is done by this kernel
@@ -567,7 +583,9 @@ __global__ void __launch_bounds__(PB_MAX_THREADS, 1) pbatch_kernel(const __grid_
     __shared__ long long s_acc[PB_MAXSEG * 2], s_prev[2][PB_MAXSEG * 2];
     __shared__ PBGeom s_geom;
     const int b = blockIdx.x, B = gridDim.x, t = threadIdx.x, T = blockDim.x;
-    const int lenX = L.lenX, nw = L.nw, nk = L.nk, nrep = L.nrep;
+    // rows of a replica held here: all of them, or -- one lattice in row slabs over several GPUs -- the owned rows of the
+    // local array (which carries halo rows for the per-sweep kernel: storage row = own_lo + row, lenS rows per colour)
+    const int lenX = L.own_hi - L.own_lo, lenS = L.lenX, row_lo = L.own_lo, nw = L.nw, nk = L.nk, nrep = L.nrep;
 
     if (t == 0) pb_geometry(b, B, nrep, lenX, s_geom);
     __syncthreads();
@@ -584,6 +602,11 @@ __global__ void __launch_bounds__(PB_MAX_THREADS, 1) pbatch_kernel(const __grid_
     c.segstart = s_segstart;
     c.splan = s_plan;
     c.xbuf = a.xbuf;
+    c.xbuf_up = a.xbuf_up;
+    c.xbuf_dn = a.xbuf_dn;
+    c.epoch = a.epoch;
+    c.row0 = a.row0;
+    c.nblocks = B;
     c.abort_word = a.bar + 1;
     c.err = a.err;
     c.lenX = lenX;
@@ -600,13 +623,13 @@ __global__ void __launch_bounds__(PB_MAX_THREADS, 1) pbatch_kernel(const __grid_
             for (int idx = t; idx < g.nrows * nw; idx += T) {
                 const int lr = idx / nw, w = idx - lr * nw;
                 const int gr = g.R0 + lr, rep = gr / lenX, i = gr - rep * lenX;
-                s_rows[((size_t)colour * g.nrows + lr) * nw + w] = L.bits[((size_t)(rep * 2 + colour) * lenX + i) * nw + w];
+                s_rows[((size_t)colour * g.nrows + lr) * nw + w] = L.bits[((size_t)(rep * 2 + colour) * lenS + row_lo + i) * nw + w];
             }
         } else {
             uint16_t *s16 = reinterpret_cast<uint16_t *>(s_rows + (size_t)colour * g.nrows * nw);
             for (int lr = t >> 5; lr < g.nrows; lr += T >> 5) {  // a warp takes one row at a time: 16-byte chunks, 4 per word
                 const int gr = g.R0 + lr, rep = gr / lenX, i = gr - rep * lenX;
-                const uint4 *src = reinterpret_cast<const uint4 *>(L.i8 + ((size_t)(rep * 2 + colour) * lenX + i) * nk);
+                const uint4 *src = reinterpret_cast<const uint4 *>(L.i8 + ((size_t)(rep * 2 + colour) * lenS + row_lo + i) * nk);
                 for (int cc = t & 31; cc < nw * 4; cc += 32) s16[lr * nw * 4 + cc] = (uint16_t)pack16<MODEL>(__ldg(src + cc));
             }
         }
@@ -759,13 +782,13 @@ __global__ void __launch_bounds__(PB_MAX_THREADS, 1) pbatch_kernel(const __grid_
             for (int idx = t; idx < g.nrows * nw; idx += T) {
                 const int lr = idx / nw, w = idx - lr * nw;
                 const int gr = g.R0 + lr, rep = gr / lenX, i = gr - rep * lenX;
-                L.bits[((size_t)(rep * 2 + colour) * lenX + i) * nw + w] = s_rows[((size_t)colour * g.nrows + lr) * nw + w];
+                L.bits[((size_t)(rep * 2 + colour) * lenS + row_lo + i) * nw + w] = s_rows[((size_t)colour * g.nrows + lr) * nw + w];
             }
         } else {
             const uint16_t *s16 = reinterpret_cast<const uint16_t *>(s_rows + (size_t)colour * g.nrows * nw);
             for (int lr = t >> 5; lr < g.nrows; lr += T >> 5) {
                 const int gr = g.R0 + lr, rep = gr / lenX, i = gr - rep * lenX;
-                uint4 *dst = reinterpret_cast<uint4 *>(L.i8 + ((size_t)(rep * 2 + colour) * lenX + i) * nk);
+                uint4 *dst = reinterpret_cast<uint4 *>(L.i8 + ((size_t)(rep * 2 + colour) * lenS + row_lo + i) * nk);
                 for (int cc = t & 31; cc < nw * 4; cc += 32) dst[cc] = unpack16<MODEL>(s16[lr * nw * 4 + cc]);
             }
         }

@@ -409,9 +409,10 @@ __global__ void __launch_bounds__(RS_THREADS, 1024 / RS_THREADS)
     int dB = 0, dS = 0;
     const uint32_t greplica = (uint32_t)(L.rep_offset + rep);
     auto wait_on = [&](uint64_t *bar, uint32_t parity) {
-        int tries = 0;
+        if (rs_mbar_try_wait(bar, parity)) return;
+        const long long t0 = clock64();
         while (!rs_mbar_try_wait(bar, parity)) {
-            if (++tries > 4000000) {  // each attempt sleeps in hardware; seconds in all: a copy never arrived / a warp never did
+            if (clock64() - t0 > 4000000000LL) {  // about two seconds: a copy never arrived / a warp never did
                 *err = 1;
                 break;
             }

@@ -719,6 +719,9 @@ struct pymc_handle {
     int rx_nranks, rx_rank;        // > 1 after pymc_rx_connect: the ladder is spread over that many GPUs
     long long *peer_esum[PB_MAXRANKS];       // CUDA IPC mappings of the other GPUs' pb_esum / pb_xflags
     unsigned int *peer_xflags[PB_MAXRANKS];
+    unsigned int pb_epoch;         // pass-number base of the last launch (grows by PB_EPOCH_STEP per launch)
+    PBPacket *peer_xbuf_up, *peer_xbuf_dn;   // slab mode: the neighbours' exchange buffers (CUDA IPC mappings, or mine)
+    bool slab_pbatch;              // slab handle whose calls of >= 2 sweeps run on K12 (connected through IPC, or a single slab)
     int32_t *pb_maps;              // [2 maps][2 parities][ntemps] replica <-> temperature maps of the kernel
     bool pb_attr[2];
     // K13 (pmc_rowstream.cuh): one sweep per launch with the rows streamed through shared memory (int8 layout)
@@ -733,6 +736,38 @@ struct pymc_handle {
     bool dirty;                    // configurations changed since the tracked observables were based
     uint64_t sweep_counter;
 };
+
+// K12 launch shape for `nrep` replicas of `lenX` rows each (lenX: the rows a replica has HERE -- the owned rows of a slab):
+// blocks, threads and dynamic shared memory into the handle; false if the kernel cannot take the shape.
+static bool plan_pbatch(pymc_handle *h, int nrep, int lenX, int sms, int smem, size_t *rows_bytes_out) {
+    int coop = 0;
+    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, h->p.device);
+    const long long NR = (long long)nrep * lenX;
+    const int blocks = NR < sms ? (int)NR : sms;
+    bool ok = coop && h->p.lenY % 128 == 0 && NR < (1ll << 31) / (h->nw > 0 ? h->nw : 1);
+    int max_rows = 0, max_x = 0;
+    for (int b = 0; ok && b < blocks; ++b) {
+        PBGeom g;
+        pb_geometry(b, blocks, nrep, lenX, g);
+        ok = g.nseg <= PB_MAXSEG;
+        if (g.nrows > max_rows) max_rows = g.nrows;
+        if (g.nxrow > max_x) max_x = g.nxrow;
+    }
+    const size_t rows_bytes = (size_t)16 * max_rows * h->nw;
+    ok = ok && rows_bytes + 2048 <= (size_t)smem;  // ~1.2 KiB of static shared memory ride along
+    const long long items = (long long)max_rows * h->nw;
+    const long long npass = (items + PB_MAX_THREADS - 1) / PB_MAX_THREADS;
+    long long threads = npass ? ((items + npass - 1) / npass + 31) / 32 * 32 : 32;
+    const long long need = ((long long)max_x * h->nw + 31) / 32 * 32;  // all export items sit in the first round
+    if (threads < need) threads = need;
+    if (threads < 64) threads = 64;
+    ok = ok && threads <= PB_MAX_THREADS;
+    h->pb_blocks = blocks;
+    h->pb_threads = (int)threads;
+    h->pb_smem = rows_bytes;
+    if (rows_bytes_out) *rows_bytes_out = rows_bytes;
+    return ok;
+}
 
 static Lat make_lat(const pymc_handle *h) {
     Lat L;
@@ -911,10 +946,12 @@ int pymc_destroy(pymc_handle *h) {
             cudaIpcCloseMemHandle(h->peer_up[0]);
             cudaIpcCloseMemHandle(h->peer_up[1]);
             cudaIpcCloseMemHandle(h->peer_up_flags);
+            if (h->peer_xbuf_up) cudaIpcCloseMemHandle(h->peer_xbuf_up);
             if (h->peer_dn[0] != h->peer_up[0]) {
                 cudaIpcCloseMemHandle(h->peer_dn[0]);
                 cudaIpcCloseMemHandle(h->peer_dn[1]);
                 cudaIpcCloseMemHandle(h->peer_dn_flags);
+                if (h->peer_xbuf_dn) cudaIpcCloseMemHandle(h->peer_xbuf_dn);
             }
         }
         if (h->ev0) cudaEventDestroy(h->ev0);
@@ -1019,28 +1056,8 @@ int pymc_create(const pymc_params *p, pymc_handle **out) {
         }
         // K12 (pmc_pbatch.cuh): the rows of ALL replicas cut into one piece per SM
         {
-            int coop = 0;
-            cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, p->device);
-            const long long NR = (long long)p->nreplicas * p->lenX;
-            const int blocks = NR < sms ? (int)NR : sms;
-            bool ok = coop && p->lenY % 128 == 0 && NR < (1ll << 31) / (h->nw > 0 ? h->nw : 1);
-            int max_rows = 0, max_x = 0;
-            for (int b = 0; ok && b < blocks; ++b) {
-                PBGeom g;
-                pb_geometry(b, blocks, p->nreplicas, p->lenX, g);
-                ok = g.nseg <= PB_MAXSEG;
-                if (g.nrows > max_rows) max_rows = g.nrows;
-                if (g.nxrow > max_x) max_x = g.nxrow;
-            }
-            const size_t rows_bytes = (size_t)16 * max_rows * h->nw;
-            ok = ok && rows_bytes + 2048 <= (size_t)smem;  // ~1.2 KiB of static shared memory ride along
-            const long long items = (long long)max_rows * h->nw;
-            const long long npass = (items + PB_MAX_THREADS - 1) / PB_MAX_THREADS;
-            long long threads = npass ? ((items + npass - 1) / npass + 31) / 32 * 32 : 32;
-            const long long need = ((long long)max_x * h->nw + 31) / 32 * 32;  // all export items sit in the first round
-            if (threads < need) threads = need;
-            if (threads < 64) threads = 64;
-            ok = ok && threads <= PB_MAX_THREADS;
+            size_t rows_bytes = 0;
+            const bool ok = plan_pbatch(h, p->nreplicas, p->lenX, sms, smem, &rows_bytes);
             if (p->kernel == PYMC_KERNEL_PBATCH && !ok) {
                 delete h;
                 return fail(PYMC_ERR_UNSUPPORTED,
@@ -1050,16 +1067,13 @@ int pymc_create(const pymc_params *p, pymc_handle **out) {
             }
             const char *off = getenv("PYMC_NO_PERSISTENT");
             const bool allowed = !(off && off[0] == '1');
-            // AUTO: one lattice of >= 2^20 sites, or a batch that the one-block-per-replica kernel does not already
-            // serve with several blocks per SM (small images, >= one replica per SM)
+            // AUTO: from a few rows on, except batches that the one-block-per-replica kernel already serves with several
+            // blocks per SM (small images, >= one replica per SM)
             const size_t sites = (size_t)p->nreplicas * p->lenX * p->lenY;
             const bool auto_ok = p->kernel == PYMC_KERNEL_AUTO && allowed && ok && !h->resident &&
                                  sites >= (p->nreplicas == 1 ? PBATCH_SINGLE_MIN_SITES : PBATCH_AUTO_MIN_SITES);
             h->pbatch = p->kernel == PYMC_KERNEL_PBATCH || auto_ok;
             if (h->pbatch && p->kernel == PYMC_KERNEL_AUTO) h->persist = h->resident_big = false;
-            h->pb_blocks = blocks;
-            h->pb_threads = (int)threads;
-            h->pb_smem = rows_bytes;
         }
         // K13 (pmc_rowstream.cuh): int8 sweeps one at a time, rows streamed through shared memory
         {
@@ -1398,6 +1412,23 @@ static int ensure_rx_exchange_buffers(pymc_handle *h) {
     return PYMC_OK;
 }
 
+// Pass numbers of K12's packets: every launch starts PB_EPOCH_STEP above the one before (a launch has at most 2 * 4096 + 2
+// passes), so the exchange buffer is zeroed once and never again -- which also means that a neighbouring GPU may store its
+// first packets here before this GPU has even launched.
+static const unsigned int PB_EPOCH_STEP = 16384;
+
+static int slab_refresh_halos(pymc_handle *h);
+
+static int ensure_pbatch_buffers(pymc_handle *h) {
+    if (!h->pb_sync) CUDA_TRY(cudaMalloc(&h->pb_sync, 2 * sizeof(unsigned int)));
+    if (!h->pb_xbuf) {
+        const size_t bytes = (size_t)2 * pb_nslots(h->pb_blocks, h->p.nreplicas) * h->nw * sizeof(PBPacket);
+        CUDA_TRY(cudaMalloc(&h->pb_xbuf, bytes));
+        CUDA_TRY(cudaMemset(h->pb_xbuf, 0, bytes));
+    }
+    return PYMC_OK;
+}
+
 // K12: nsweeps sweeps of every replica in one cooperative launch per <= 4096 sweeps; with xchg_every > 0 (single-GPU
 // replica exchange) an exchange after every xchg_every-th sweep, decided inside the kernel.  Returns
 // PYMC_ERR_UNSUPPORTED (and switches the handle back to the other kernels) if the device refuses the launch.
@@ -1416,9 +1447,9 @@ static int launch_pbatch(pymc_handle *h, int64_t nsweeps, int xchg_every, int *s
         h->pb_attr[m] = true;
     }
     const int B = h->pb_blocks, R = h->p.ntemps;
-    if (!h->pb_sync) {
-        CUDA_TRY(cudaMalloc(&h->pb_sync, 2 * sizeof(unsigned int)));
-        CUDA_TRY(cudaMalloc(&h->pb_xbuf, (size_t)2 * pb_nslots(B, h->p.nreplicas) * h->nw * sizeof(PBPacket)));
+    {
+        int rc = ensure_pbatch_buffers(h);
+        if (rc) return rc;
     }
     if (xchg_every > 0 && !h->pb_maps) CUDA_TRY(cudaMalloc(&h->pb_maps, (size_t)4 * R * sizeof(int32_t)));
     if (xchg_every > 0) {
@@ -1442,6 +1473,11 @@ static int launch_pbatch(pymc_handle *h, int64_t nsweeps, int xchg_every, int *s
         a.bar = h->pb_sync;
         a.err = h->persist_err;
         a.xbuf = h->pb_xbuf;
+        a.xbuf_up = h->slab ? h->peer_xbuf_up : h->pb_xbuf;
+        a.xbuf_dn = h->slab ? h->peer_xbuf_dn : h->pb_xbuf;
+        h->pb_epoch += PB_EPOCH_STEP;
+        a.epoch = h->pb_epoch;
+        a.row0 = h->slab ? h->slab_index * (h->own_hi - h->own_lo) : 0;
         a.esum = h->pb_esum;
         a.nranks = h->rx_nranks > 1 ? h->rx_nranks : 1;
         a.rank = h->rx_nranks > 1 ? h->rx_rank : 0;
@@ -1467,7 +1503,6 @@ static int launch_pbatch(pymc_handle *h, int64_t nsweeps, int xchg_every, int *s
             a.energies = h->energies;
         }
         CUDA_TRY(cudaMemsetAsync(h->pb_sync, 0, 2 * sizeof(unsigned int), h->stream));
-        CUDA_TRY(cudaMemsetAsync(h->pb_xbuf, 0, (size_t)2 * pb_nslots(B, h->p.nreplicas) * h->nw * sizeof(PBPacket), h->stream));
         CUDA_TRY(cudaMemsetAsync(h->reduced, 0, (size_t)h->p.nreplicas * 16, h->stream));
         if (xchg_every > 0)  // the blocks add deltas to the sums of MY replicas (other GPUs store theirs whole)
             for (int par = 0; par < 2; ++par)
@@ -1480,13 +1515,21 @@ static int launch_pbatch(pymc_handle *h, int64_t nsweeps, int xchg_every, int *s
             h->pbatch = false;  // nothing has run in this chunk: the caller falls back
             return fail(PYMC_ERR_UNSUPPORTED, "cooperative launch refused: %s", cudaGetErrorString(e));
         }
-        // the exact sums at the end of the launch are the new tracked values
-        CUDA_TRY(cudaMemcpyAsync(h->tracked, h->reduced, (size_t)h->p.nreplicas * 16, cudaMemcpyDeviceToDevice, h->stream));
+        if (h->slab) {
+            // The kernel keeps only the owned rows: bring the halo rows of the per-sweep kernel up to date (mine are written by
+            // the neighbours, as after an upload) and let the tracked sums be re-based in the convention of reduce_kernel (a
+            // slab's share of the boundary bonds differs between the two reductions; the sum over the slabs does not).
+            const int rc = slab_refresh_halos(h);
+            if (rc) return rc;
+        } else {
+            // the exact sums at the end of the launch are the new tracked values
+            CUDA_TRY(cudaMemcpyAsync(h->tracked, h->reduced, (size_t)h->p.nreplicas * 16, cudaMemcpyDeviceToDevice, h->stream));
+            h->dirty = false;
+        }
         if (nex & 1) {  // an odd number of exchanges leaves the current maps in the spare pair
             CUDA_TRY(cudaMemcpyAsync(h->rep_to_T, h->pb_maps, (size_t)R * 4, cudaMemcpyDeviceToDevice, h->stream));
             CUDA_TRY(cudaMemcpyAsync(h->T_to_rep, h->pb_maps + R, (size_t)R * 4, cudaMemcpyDeviceToDevice, h->stream));
         }
-        h->dirty = false;
         h->sweep_counter += chunk;
         h->rx_round += (uint64_t)nex;
         if (nex & 1) scheme ^= 1;
@@ -1560,7 +1603,7 @@ static int slab_sync_async(pymc_handle *h);
 static const char *sweep_kernel_for(const pymc_handle *h, int64_t nsweeps, int *launches_per_sweep) {
     int n = 2;
     const char *name;
-    if (h->pbatch && nsweeps >= 2 && !h->slab) {
+    if (h->pbatch && nsweeps >= 2 && (!h->slab || h->slab_pbatch)) {
         name = "pbatch_kernel";  // one cooperative launch per call of >= 2 sweeps (and per exchange cycle on one GPU)
         n = 1;
     } else if (h->resident || (h->resident_big && nsweeps >= 2)) {
@@ -1605,7 +1648,7 @@ int pymc_sweep(pymc_handle *h, int64_t nsweeps) {
     REQUIRE(nsweeps >= 0, PYMC_ERR_BADARG, "pymc_sweep: nsweeps %lld", (long long)nsweeps);
     REQUIRE(h->tables_set, PYMC_ERR_STATE, "pymc_sweep: call pymc_set_accept_tables first");
     REQUIRE(!h->slab || h->peer_up[0], PYMC_ERR_STATE, "pymc_sweep: connect the slab to its neighbours first");
-    if (h->pbatch && nsweeps >= 2 && !h->slab) {
+    if (h->pbatch && nsweeps >= 2 && (!h->slab || h->slab_pbatch)) {
         const int rc = launch_pbatch(h, nsweeps, 0, nullptr);
         if (rc != PYMC_ERR_UNSUPPORTED) return rc;
     }
@@ -2450,8 +2493,8 @@ int pymc_create_slab(const pymc_params *p, int slab_index, int nslabs, pymc_hand
     q.lenX = Xl + 4;  // two halo rows above and below the owned rows
     pymc_handle *h = nullptr;
     int rc = pymc_create(&q, &h);
-    if (rc == PYMC_OK) h->persist = h->pbatch = h->resident = h->resident_big = false;  // slabs run the fused kernel only
     if (rc) return rc;
+    h->persist = h->pbatch = h->resident = h->resident_big = h->rowstream = false;  // single sweeps: the tiled kernel
     h->slab = true;
     h->own_lo = 2;
     h->own_hi = Xl + 2;
@@ -2473,36 +2516,57 @@ int pymc_create_slab(const pymc_params *p, int slab_index, int nslabs, pymc_hand
     }
     h->buf[0] = h->i8;
     h->buf[1] = h->i8_alt;
+    // Calls of >= 2 sweeps keep the slab on chip (K12 on the owned rows; the first / last block exchange packets with the
+    // GPUs above / below through their exchange buffers).  Needs one replica, at least two blocks (the rows above row 0
+    // and below the last row must come through the exchange buffer, not from inside a block) and an even first row.
+    {
+        int sms = 0, smem = 0;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->p.device);
+        cudaDeviceGetAttribute(&smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->p.device);
+        const char *off = getenv("PYMC_NO_PERSISTENT");
+        h->pbatch = plan_pbatch(h, h->p.nreplicas, Xl, sms, smem, nullptr) && h->p.nreplicas == 1 && h->pb_blocks >= 2 &&
+                    (slab_index * Xl) % 2 == 0 && !(off && off[0] == '1');
+        if (h->pbatch && ensure_pbatch_buffers(h) != PYMC_OK) h->pbatch = false;
+    }
     if (nslabs == 1) {  // periodic onto myself: my own buffers are my neighbours' buffers
         h->peer_up[0] = h->peer_dn[0] = h->buf[0];
         h->peer_up[1] = h->peer_dn[1] = h->buf[1];
+        h->peer_xbuf_up = h->peer_xbuf_dn = h->pb_xbuf;
+        h->slab_pbatch = h->pbatch;
     }
     *out = h;
     return PYMC_OK;
 }
 
-// 3 x 64 bytes: CUDA IPC handles of buffer 0, buffer 1 and the flag words, to be handed to both neighbours
+// 4 x 64 bytes: CUDA IPC handles of buffer 0, buffer 1, the flag words and the exchange buffer of the batch-resident kernel
+// (zeros if this slab cannot run it), to be handed to both neighbours
 int pymc_slab_ipc_export(pymc_handle *h, void *handles, size_t nbytes) {
     ENTER(h);
-    REQUIRE(h->slab && handles && nbytes == 3 * sizeof(cudaIpcMemHandle_t), PYMC_ERR_BADARG,
-            "pymc_slab_ipc_export: need a slab handle and %zu bytes", 3 * sizeof(cudaIpcMemHandle_t));
+    REQUIRE(h->slab && handles && nbytes == 4 * sizeof(cudaIpcMemHandle_t), PYMC_ERR_BADARG,
+            "pymc_slab_ipc_export: need a slab handle and %zu bytes", 4 * sizeof(cudaIpcMemHandle_t));
     cudaIpcMemHandle_t *out = (cudaIpcMemHandle_t *)handles;
+    memset(out, 0, nbytes);
     CUDA_TRY(cudaIpcGetMemHandle(out + 0, h->buf[0]));
     CUDA_TRY(cudaIpcGetMemHandle(out + 1, h->buf[1]));
     CUDA_TRY(cudaIpcGetMemHandle(out + 2, h->flags));
+    if (h->pbatch && h->pb_xbuf) CUDA_TRY(cudaIpcGetMemHandle(out + 3, h->pb_xbuf));
     return PYMC_OK;
 }
 
 int pymc_slab_connect(pymc_handle *h, const void *up_handles, const void *dn_handles, size_t nbytes) {
     ENTER(h);
     REQUIRE(h->slab && h->nslabs > 1, PYMC_ERR_STATE, "pymc_slab_connect: only for slabs with neighbours");
-    REQUIRE(up_handles && dn_handles && nbytes == 3 * sizeof(cudaIpcMemHandle_t), PYMC_ERR_BADARG,
-            "pymc_slab_connect: need two sets of %zu bytes", 3 * sizeof(cudaIpcMemHandle_t));
+    REQUIRE(up_handles && dn_handles && nbytes == 4 * sizeof(cudaIpcMemHandle_t), PYMC_ERR_BADARG,
+            "pymc_slab_connect: need two sets of %zu bytes", 4 * sizeof(cudaIpcMemHandle_t));
     const cudaIpcMemHandle_t *up = (const cudaIpcMemHandle_t *)up_handles, *dn = (const cudaIpcMemHandle_t *)dn_handles;
-    void *pu[3], *pd[3];
-    for (int k = 0; k < 3; ++k) CUDA_TRY(cudaIpcOpenMemHandle(&pu[k], up[k], cudaIpcMemLazyEnablePeerAccess));
+    const cudaIpcMemHandle_t none = {};
+    // the exchange buffers are mapped only if all three slabs involved can run the batch-resident kernel
+    const bool xb = h->pbatch && memcmp(up + 3, &none, sizeof(none)) != 0 && memcmp(dn + 3, &none, sizeof(none)) != 0;
+    const int nh = xb ? 4 : 3;
+    void *pu[4] = {nullptr, nullptr, nullptr, nullptr}, *pd[4] = {nullptr, nullptr, nullptr, nullptr};
+    for (int k = 0; k < nh; ++k) CUDA_TRY(cudaIpcOpenMemHandle(&pu[k], up[k], cudaIpcMemLazyEnablePeerAccess));
     const bool same = memcmp(up, dn, nbytes) == 0;  // two slabs: the neighbour above is the neighbour below
-    for (int k = 0; k < 3; ++k) {
+    for (int k = 0; k < nh; ++k) {
         if (same)
             pd[k] = pu[k];
         else
@@ -2514,6 +2578,9 @@ int pymc_slab_connect(pymc_handle *h, const void *up_handles, const void *dn_han
     h->peer_dn[0] = (int8_t *)pd[0];
     h->peer_dn[1] = (int8_t *)pd[1];
     h->peer_dn_flags = (unsigned long long *)pd[2];
+    h->peer_xbuf_up = (PBPacket *)pu[3];
+    h->peer_xbuf_dn = (PBPacket *)pd[3];
+    h->slab_pbatch = xb;  // NOTE: every slab of the lattice must come to the same answer (same shape: they do)
     return PYMC_OK;
 }
 
@@ -2534,11 +2601,8 @@ int pymc_slab_connect_local(pymc_handle *h, pymc_handle *up, pymc_handle *down) 
     return PYMC_OK;
 }
 
-// After pymc_upload_config on every slab: make the halo rows consistent (collective over the neighbours).
-int pymc_slab_push_halos(pymc_handle *h) {
-    ENTER(h);
-    REQUIRE(h->slab, PYMC_ERR_STATE, "pymc_slab_push_halos: not a slab handle");
-    REQUIRE(h->nslabs == 1 || h->peer_up[0], PYMC_ERR_STATE, "pymc_slab_push_halos: call pymc_slab_connect first");
+// My first / last two owned rows into the neighbours' halo rows, then the neighbour barrier (collective over the neighbours).
+static int slab_refresh_halos(pymc_handle *h) {
     Lat L = make_lat(h);
     const int k = h->i8 == h->buf[0] ? 0 : 1;
     dim3 grid((h->nk / 16 + 127) / 128, 4, 2 * h->p.nreplicas);
@@ -2548,6 +2612,14 @@ int pymc_slab_push_halos(pymc_handle *h) {
     if (rc) return rc;
     h->dirty = true;
     return PYMC_OK;
+}
+
+// After pymc_upload_config on every slab: make the halo rows consistent (collective over the neighbours).
+int pymc_slab_push_halos(pymc_handle *h) {
+    ENTER(h);
+    REQUIRE(h->slab, PYMC_ERR_STATE, "pymc_slab_push_halos: not a slab handle");
+    REQUIRE(h->nslabs == 1 || h->peer_up[0], PYMC_ERR_STATE, "pymc_slab_push_halos: call pymc_slab_connect first");
+    return slab_refresh_halos(h);
 }
 
 // 0 = fine; 1 = a neighbour did not reach a barrier within the time limit (results are invalid)

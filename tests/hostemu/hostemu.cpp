@@ -265,7 +265,10 @@ int pbatch_sweeps(int8_t *imgs, int nrep, int lenX, int lenY, const uint32_t *th
         c.segoff = segoff[b].data();
         c.segstart = segstart[b].data();
         c.splan = splan[b].data();
-        c.xbuf = xbuf.data();
+        c.xbuf = c.xbuf_up = c.xbuf_dn = xbuf.data();
+        c.epoch = 4096u * 7u;  // any base: the pass numbers of a launch are relative to it
+        c.row0 = 0;
+        c.nblocks = B;
         c.abort_word = &abort_word;
         c.err = &err;
         c.lenX = lenX;

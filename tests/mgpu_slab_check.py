@@ -28,13 +28,19 @@ def main():
     from py_mc_b200.slab import SlabLattice
     ok = True
     thr = ising2D(-1.0)._pmc_thresholds(2.269185314213022)[None, :]
-    for (lenX, lenY, nsweeps, seed) in [(256, 1024, 9, 11), (1024, 2048, 5, 12)]:
+    # calls: single sweeps take the tiled kernel (halo rows stored into the neighbours' arrays), calls of two or more sweeps
+    # the batch-resident kernel (first / last rows to the neighbouring GPUs as packets); both, and mixtures, must give the
+    # whole-lattice trajectory
+    for (lenX, lenY, calls, seed) in [(256, 1024, (9,), 11), (1024, 2048, (5,), 12), (512, 1024, (1, 1, 3, 1, 2, 1), 13),
+                                       (2048, 4096, (2, 4), 14)]:
         if lenX % (32 * world):
             continue
+        nsweeps = sum(calls)
         sl = SlabLattice(_cabi.MODEL_ISING, lenX, lenY, seed, dist)
         sl.init_random()
         sl.set_accept_tables(thr)
-        sl.sweep(nsweeps)
+        for n in calls:
+            sl.sweep(n)
         sl.check()
         got = sl.gather()
         b, m = sl.observables()
@@ -48,7 +54,8 @@ def main():
             wb, wm = whole.tracked()
             good = np.array_equal(got, want) and (b, m) == (int(wb[0]), int(wm[0]))
             # upload path: continue from the downloaded state on the slabs
-            print("slab %dx%d over %d GPUs, %d sweeps: %s" % (lenX, lenY, world, nsweeps, "ok" if good else "MISMATCH"),
+            print("slab %dx%d over %d GPUs, calls %s (%s / %s): %s" % (lenX, lenY, world, calls, sl.lat.sweep_kernel_for(1)[1],
+                                                                     sl.lat.sweep_kernel_for(2)[1], "ok" if good else "MISMATCH"),
                   flush=True)
         flag = torch.tensor([1 if good else 0], device="cuda")
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)

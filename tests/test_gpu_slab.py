@@ -34,7 +34,7 @@ def test_slabs_follow_the_whole_lattice_trajectory(nslabs):
     for s in slabs:
         s.init_random()
         s.set_accept_tables(thr)
-        assert s.sweep_kernel_info() == (1, "sweep_fused_i8_kernel")
+        assert s.sweep_kernel_for(1) == (1, "sweep_fused_i8_kernel")
     # the hot start is a function of whole-lattice rows: the slabs together are the single-GPU start
     start = np.concatenate([s.download(0) for s in slabs])
     assert np.array_equal(start, o_ising.init_config(seed, 0, *shape))
@@ -48,6 +48,31 @@ def test_slabs_follow_the_whole_lattice_trajectory(nslabs):
     assert (b, m) == (int(wb[0]), int(wm[0]))
     rb = sum(int(s.reduce_observables()[0][0]) for s in slabs)
     assert rb == o_ising.bond_sum(want)
+
+
+@pytest.mark.parametrize("shape", [(128, 1024), (2048, 2048)])
+def test_single_slab_calls_of_several_sweeps_stay_on_chip(shape):
+    """One slab over the whole lattice (its neighbours are itself): calls of two or more sweeps run on the batch-resident
+    kernel with the rows above row 0 / below the last row travelling through the exchange buffer like between GPUs; the
+    halo rows of the tiled kernel are refreshed afterwards, so single-sweep calls can follow.  Same trajectory and sums as
+    the plain lattice.  (Real neighbours over CUDA IPC: tests/mgpu_slab_check.py.)"""
+    from py_mc_b200 import _cabi
+    seed, calls = 77, (3, 1, 4, 1, 1, 2)
+    thr = o_ising.threshold_table(-1.0, 2.3)[1][None, :]
+    want, (wb, wm) = _whole(shape, seed, thr, sum(calls))
+    s = _cabi.Lattices(_cabi.MODEL_ISING, shape[0], shape[1], seed=seed, layout=_cabi.LAYOUT_INT8, slab=(0, 1))
+    s.init_random()
+    s.set_accept_tables(thr)
+    assert s.sweep_kernel_for(2) == (1, "pbatch_kernel") and s.sweep_kernel_for(1) == (1, "sweep_fused_i8_kernel")
+    for n in calls:
+        s.sweep(n)
+    assert s.slab_status() == 0
+    assert np.array_equal(s.download(0), want)
+    b, m = s.tracked()
+    assert (int(b[0]), int(m[0])) == (int(wb[0]), int(wm[0]))
+    rb, rm = s.reduce_observables()
+    assert (int(rb[0]), int(rm[0])) == (int(wb[0]), int(wm[0]))
+    s.close()
 
 
 def test_upload_then_push_halos():
