@@ -2,9 +2,11 @@
 
 No counterpart in the reference (it has no domain decomposition).  One process per GPU, started with
 ``torchrun``; process g owns rows ``[g*lenX/G, (g+1)*lenX/G)`` of the lattice.  ``torch.distributed`` is
-used once, to hand each process the CUDA IPC handles of its two neighbours' buffers; after that the
-sweep kernel itself stores the boundary rows into the neighbours' halo rows (peer memory) and a one-thread
-kernel per sweep synchronises neighbours through flag words -- no NCCL call and no host involvement per sweep.
+used once, to hand each process the CUDA IPC handles of its two neighbours' buffers.  After that a call of two
+or more sweeps keeps every slab in the shared memory of its GPU for the whole call and hands the first / last row
+of every colour pass to the neighbouring GPUs as packets stored into their memory over NVLink (one launch per GPU);
+a call of a single sweep stores the boundary rows into the neighbours' halo rows from inside the tiled sweep kernel,
+which also carries the neighbour barrier -- no NCCL call and no host involvement per sweep either way.
 The random stream is indexed by whole-lattice rows, so the result is bit-identical to the single-GPU run.
 """
 import os
