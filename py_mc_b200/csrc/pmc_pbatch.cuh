@@ -165,6 +165,7 @@ struct PBCtx {
                                  // in row slabs over several GPUs -- the exchange buffer of the GPU above / below (peer memory)
     unsigned int epoch;          // added to every pass number: launches never see each other's packets
     int row0;                    // row of the whole lattice of local row 0 of replica 0 (random-stream index; slabs)
+    long long wait_cycles;       // how long a reader waits for a packet before it gives up (longer when other GPUs feed me)
     unsigned int *abort_word;    // global: set when a wait has timed out
     int *err;
     int lenX, nw, nw_shift;      // nw_shift >= 0: nw is that power of two
@@ -190,9 +191,10 @@ __device__ __forceinline__ void pb_put(PBPacket *p, uint64_t v, unsigned int ev)
 }
 
 // Load the word whose packets carry pass number `need` (or a later one: see the header).  The poll backs off and is
-// bounded: after about two seconds *err is raised, and so is the abort word in device memory that lets every other
-// waiter of the launch give up at once.
-__device__ __forceinline__ uint64_t pb_get(const PBPacket *p, unsigned int need, int *err, unsigned int *abort_word) {
+// bounded: after about two seconds (ten when the rows of another GPU are awaited) *err is raised, and so is the abort word
+// in device memory that lets every other waiter of the launch give up at once.
+__device__ __forceinline__ uint64_t pb_get(const PBPacket *p, unsigned int need, int *err, unsigned int *abort_word,
+                                           long long wait_cycles) {
 #ifdef __CUDA_ARCH__
     uint64_t a, b;
     asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
@@ -205,7 +207,7 @@ __device__ __forceinline__ uint64_t pb_get(const PBPacket *p, unsigned int need,
             if ((int)((unsigned int)(a >> 32) - need) >= 0 && (int)((unsigned int)(b >> 32) - need) >= 0) break;
             if ((++spins & 1023u) == 0) {
                 if (*(volatile unsigned int *)abort_word) break;
-                if (clock64() - t0 > 4000000000LL) {
+                if (clock64() - t0 > wait_cycles) {
                     *(volatile unsigned int *)abort_word = 1u;
                     *err = 1;
                     break;
@@ -218,6 +220,7 @@ __device__ __forceinline__ uint64_t pb_get(const PBPacket *p, unsigned int need,
     // the host drives the blocks in lock step: the packets must be there already
     if ((int)((unsigned int)(p->lo >> 32) - need) < 0 || (int)((unsigned int)(p->hi >> 32) - need) < 0) *err = 1;
     (void)abort_word;
+    (void)wait_cycles;
     return (p->lo & 0xFFFFFFFFull) | (p->hi << 32);
 #endif
 }
@@ -287,7 +290,7 @@ __device__ __forceinline__ void pb_neighbours(const PBGeom &g, int lenX, int lr,
 __device__ __forceinline__ uint64_t pb_row_word(const PBGeom &g, const PBCtx &c, int oc, int row, int w, unsigned int need) {
     if (row >= 0) return c.s[((size_t)oc * g.nrows + row) * c.nw + w];
     const int k = -1 - row;
-    return pb_get(c.xbuf + ((size_t)oc * c.nslots + g.imp_slot[k]) * c.nw + w, c.epoch + need, c.err, c.abort_word);
+    return pb_get(c.xbuf + ((size_t)oc * c.nslots + g.imp_slot[k]) * c.nw + w, c.epoch + need, c.err, c.abort_word, c.wait_cycles);
 }
 
 // Where the word of export slot `slot` goes: the slots of a replica's row 0 / last row (what a block at the other end of
@@ -606,6 +609,7 @@ __global__ void __launch_bounds__(PB_MAX_THREADS, 1) pbatch_kernel(const __grid_
     c.xbuf_dn = a.xbuf_dn;
     c.epoch = a.epoch;
     c.row0 = a.row0;
+    c.wait_cycles = a.xbuf_up != a.xbuf ? 20000000000LL : 4000000000LL;  // neighbours on other GPUs may launch later
     c.nblocks = B;
     c.abort_word = a.bar + 1;
     c.err = a.err;

@@ -268,6 +268,7 @@ int pbatch_sweeps(int8_t *imgs, int nrep, int lenX, int lenY, const uint32_t *th
         c.xbuf = c.xbuf_up = c.xbuf_dn = xbuf.data();
         c.epoch = 4096u * 7u;  // any base: the pass numbers of a launch are relative to it
         c.row0 = 0;
+        c.wait_cycles = 0;
         c.nblocks = B;
         c.abort_word = &abort_word;
         c.err = &err;
