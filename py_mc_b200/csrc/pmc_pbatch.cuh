@@ -293,6 +293,60 @@ __device__ __forceinline__ uint64_t pb_row_word(const PBGeom &g, const PBCtx &c,
     return pb_get(c.xbuf + ((size_t)oc * c.nslots + g.imp_slot[k]) * c.nw + w, c.epoch + need, c.err, c.abort_word, c.wait_cycles);
 }
 
+// What a thread works out about its items that does not change from pass to pass: the first-round item (general path)
+// and where its later rounds start.  Kept in shared memory when there is room (32 bytes per thread: every launch shape except
+// the ones that fill the shared memory with rows, where a pass has so many rounds that the set-up does not matter); with a
+// few rows per block a pass is two or three rounds long and this set-up was a tenth of its instructions.
+struct PBI4 {
+    int x, y, z, w;
+};
+struct PBItems {
+    int idx, i, up, dn;     // first round: word index in the block (lr * nw + w), row in the replica, rows above / below
+    int lr, w, seg, on;     // ... its local row, word column, replica segment; on = 0: no item (thread beyond the items)
+    int lr2, w2, xk2;       // later rounds: local row and word column of the second item, export rows already skipped
+};
+
+__device__ __forceinline__ void pb_items_first(const PBGeom &g, const PBCtx &c, int t, PBItems &it) {
+    const int nw = c.nw, items = g.nrows * nw;
+    it.on = t < items;
+    const int o = it.on ? t : items - 1;
+    pb_locate(g, c, o, true, it.lr, it.w, it.seg, it.i);
+    pb_neighbours(g, c.lenX, it.lr, it.i, it.up, it.dn);
+    it.idx = it.lr * nw + it.w;
+}
+__device__ __forceinline__ void pb_items_later(const PBGeom &g, const PBCtx &c, int t, int T, PBItems &it) {
+    const int nw = c.nw, ro = (T + t) / nw;
+    it.w2 = (T + t) - ro * nw;
+    it.lr2 = ro - g.nxrow;  // rank among the rows that are not export rows -> row: skip over the export rows
+    it.xk2 = 0;
+    while (it.xk2 < g.nxrow && it.lr2 >= g.xrow[it.xk2]) {
+        ++it.lr2;
+        ++it.xk2;
+    }
+}
+__device__ __forceinline__ void pb_items(const PBGeom &g, const PBCtx &c, int t, int T, PBItems &it) {
+    pb_items_first(g, c, t, it);
+    pb_items_later(g, c, t, T, it);
+}
+__device__ __forceinline__ void pb_items_store(const PBItems &it, PBI4 *ca, PBI4 *cb, int t) {
+    ca[t] = PBI4{it.idx, it.i, it.up, it.dn};
+    cb[t] = PBI4{it.lr | (it.on << 30), it.w | (it.seg << 16), it.lr2, it.w2 | (it.xk2 << 16)};
+}
+__device__ __forceinline__ void pb_items_load(PBItems &it, const PBI4 *ca, const PBI4 *cb, int t) {
+    const PBI4 a = ca[t], b = cb[t];
+    it.idx = a.x;
+    it.i = a.y;
+    it.up = a.z;
+    it.dn = a.w;
+    it.lr = b.x & 0x3FFFFFFF;
+    it.on = (b.x >> 30) & 1;
+    it.w = b.y & 0xFFFF;
+    it.seg = b.y >> 16;
+    it.lr2 = b.z;
+    it.w2 = b.w & 0xFFFF;
+    it.xk2 = b.w >> 16;
+}
+
 // Where the word of export slot `slot` goes: the slots of a replica's row 0 / last row (what a block at the other end of
 // the replica reads) are those a neighbouring GPU reads when one lattice is cut into row slabs.
 __device__ __forceinline__ PBPacket *pb_export_buffer(const PBCtx &c, int slot, int B) {
@@ -311,28 +365,37 @@ __device__ __forceinline__ PBPacket *pb_export_buffer(const PBCtx &c, int slot, 
 // instead of being recomputed.  (Measured alternatives, slower: recomputing the row from the ordinal per item; the
 // natural order with the export items pulled forward by their owners -- with few words per row those owners' warps do
 // a whole extra item.)
-template <int MODEL>
+template <int MODEL, bool KEEP, bool SLAB>
 __device__ __forceinline__ void pb_pass(const PBGeom &g, const PBCtx &c, int colour, uint64_t step, unsigned int events, int t,
-                                        int T) {
+                                        int T, Plan<MODEL> &kept_plan, int &kept_cur, const PBI4 *ca, const PBI4 *cb) {
     // block-uniform values out of shared memory once: the stores of the loop could alias them for all the compiler knows
     const int nrows = g.nrows, nxrow = g.nxrow, nseg = g.nseg, nw = c.nw, lenX = c.lenX;
     const int oc = colour ^ 1, items = nrows * nw, nexport = nxrow * nw;
     uint64_t *const sc = c.s + (size_t)colour * items;
     const uint64_t *const so = c.s + (size_t)oc * items;
     const uint32_t rep0 = c.rep_offset + (uint32_t)g.rep_first;
-    Plan<MODEL> plan;
-    int cur;
+    // KEEP (launch shapes with room in shared memory: few rows per block, two or three rounds per pass): the per-thread
+    // item data comes from shared memory, and the Ising plan (9 registers) with the replica segment it belongs to (-1:
+    // none) lives across passes in the caller (the lattice-gas plan, 25 registers, would spill there).  Otherwise everything
+    // is worked out per pass, the later rounds' starting point only after the first round (registers).
+    Plan<MODEL> pass_plan;
+    int pass_cur = -1;
+    Plan<MODEL> &plan = (KEEP && MODEL == MODEL_ISING) ? kept_plan : pass_plan;
+    int &cur = (KEEP && MODEL == MODEL_ISING) ? kept_cur : pass_cur;
+    PBItems f;
+    if (KEEP)
+        pb_items_load(f, ca, cb, t);
+    else
+        pb_items_first(g, c, t, f);
 
     // ---- first round: general path -----------------------------------------------------------------------
     {
-        const bool on = t < items;
-        const int o = on ? t : items - 1;
-        int lr, w, seg, i, up, dn;
-        pb_locate(g, c, o, true, lr, w, seg, i);
-        pb_neighbours(g, lenX, lr, i, up, dn);
-        plan.init(SmemRow{c.splan + seg * PLAN_WORDS});
-        cur = seg;
-        const int idx = lr * nw + w;
+        const bool on = f.on;
+        const int lr = f.lr, w = f.w, seg = f.seg, i = f.i, up = f.up, dn = f.dn, idx = f.idx;
+        if (seg != cur) {
+            plan.init(SmemRow{c.splan + seg * PLAN_WORDS});
+            cur = seg;
+        }
         const uint64_t S = sc[idx], C = so[idx];
         uint64_t Sd;
         if ((i + colour) & 1)
@@ -341,15 +404,15 @@ __device__ __forceinline__ void pb_pass(const PBGeom &g, const PBCtx &c, int col
             Sd = (C << 1) | (so[w == 0 ? idx + nw - 1 : idx - 1] >> 63);
         const uint64_t U = pb_row_word(g, c, oc, up, w, events), D = pb_row_word(g, c, oc, dn, w, events);
         int dB, dS;  // unused: the sums are recomputed where they are needed (pb_reduce)
-        const uint64_t Snew = update_word<MODEL>(S, U, D, C, Sd, on ? ~0ull : 0ull, plan, (uint32_t)((i + c.row0) * nw + w),
+        const uint64_t Snew = update_word<MODEL>(S, U, D, C, Sd, on ? ~0ull : 0ull, plan, (uint32_t)((SLAB ? i + c.row0 : i) * nw + w),
                                                  rep0 + (uint32_t)seg, step, *c.key, dB, dS);
         if (on) {
             sc[idx] = Snew;
-            if (o < nexport)
+            if (t < nexport)
                 for (int e = 0; e < g.nexp; ++e)
                     if (g.exp_row[e] == lr)
-                        pb_put(pb_export_buffer(c, g.exp_slot[e], c.nblocks) + ((size_t)colour * c.nslots + g.exp_slot[e]) * nw + w, Snew,
-                               c.epoch + events + 1u);
+                        pb_put((SLAB ? pb_export_buffer(c, g.exp_slot[e], c.nblocks) : c.xbuf) + ((size_t)colour * c.nslots + g.exp_slot[e]) * nw + w,
+                               Snew, c.epoch + events + 1u);
         }
     }
     if (T >= items) return;
@@ -358,19 +421,10 @@ __device__ __forceinline__ void pb_pass(const PBGeom &g, const PBCtx &c, int col
     const bool strided = T % nw == 0;  // then a thread keeps its word column and moves down T / nw ordinal rows per round
     const int dr = strided ? T / nw : 0;
     const int wrap = (lenX - 1) * nw;  // from row 0 of a replica to its last row
-    int lr, w, left, right, xk = 0, xn;  // xn: the next export row at or below which lr has not yet been moved past
-    {
-        const int ro = (T + t) / nw;
-        w = (T + t) - ro * nw;
-        lr = ro - nxrow;  // rank among the rows that are not export rows -> row: skip over the export rows
-        while (xk < nxrow && lr >= g.xrow[xk]) {
-            ++lr;
-            ++xk;
-        }
-        xn = xk < nxrow ? g.xrow[xk] : 0x7FFFFFFF;
-        left = w == 0 ? nw - 1 : -1;
-        right = w == nw - 1 ? 1 - nw : 1;
-    }
+    if (!KEEP) pb_items_later(g, c, t, T, f);
+    int lr = f.lr2, w = f.w2, xk = f.xk2;
+    int xn = xk < nxrow ? g.xrow[xk] : 0x7FFFFFFF;  // the next export row at or below which lr has not yet been moved past
+    int left = w == 0 ? nw - 1 : -1, right = w == nw - 1 ? 1 - nw : 1;
     int seg = 0, seg_end = nseg > 1 ? c.segstart[1] : 0x7FFFFFFF, ioff = c.segoff[0];
 #pragma unroll 1
     for (int base = T; base < items; base += T) {  // whole warps stay in the loop: the update votes
@@ -402,8 +456,8 @@ __device__ __forceinline__ void pb_pass(const PBGeom &g, const PBCtx &c, int col
         else
             Sd = (C << 1) | (so[on ? o + left : 0] >> 63);
         int dB, dS;
-        const uint64_t Snew = update_word<MODEL>(S, so[ou], so[od], C, Sd, on ? ~0ull : 0ull, plan, (uint32_t)((i + c.row0) * nw + w),
-                                                 rep0 + (uint32_t)seg, step, *c.key, dB, dS);
+        const uint64_t Snew = update_word<MODEL>(S, so[ou], so[od], C, Sd, on ? ~0ull : 0ull, plan,
+                                                 (uint32_t)((SLAB ? i + c.row0 : i) * nw + w), rep0 + (uint32_t)seg, step, *c.key, dB, dS);
         if (on) sc[o] = Snew;
         if (strided) {
             lr += dr;
@@ -536,6 +590,7 @@ struct PBatchArgs {
     PBPacket *xbuf_up, *xbuf_dn;   // = xbuf, or the exchange buffers of the GPUs holding the slab above / below (CUDA IPC mappings)
     unsigned int epoch;            // first pass number of this launch minus 1: the same on every GPU of a slab run
     int row0;                      // slab: row of the whole lattice of my first owned row (0 otherwise)
+    int cache_off;                 // KEEP instantiation: byte offset behind the rows of 32 bytes per thread of item data
     long long *esum;               // [2 parities][R][2] per-replica exact sums of an exchange, indexed by GLOBAL replica;
                                    // the local slice is zeroed by the host before the launch (blocks add deltas)
     // replicas spread over several GPUs (pymc_rx_connect): the all-gather of the energies is done by this kernel
@@ -578,7 +633,9 @@ __device__ __forceinline__ void pb_grid_barrier(unsigned int *counter, unsigned 
 
 // grid = B blocks (<= number of SMs, cooperative launch: all resident), block = multiple of 32 threads with
 // 4 * nw <= threads, dynamic shared memory = 2 * (largest nrows) * nw * 8 bytes.
-template <int MODEL, int LAYOUT, class LatT>
+// SLAB: one lattice in row slabs over several GPUs -- the owned rows of the local array are the "replica", row 0 / the last row
+// are exported into the exchange buffers of the GPUs above / below, the random stream is indexed by whole-lattice rows.
+template <int MODEL, int LAYOUT, bool KEEP, bool SLAB, class LatT>
 __global__ void __launch_bounds__(PB_MAX_THREADS, 1) pbatch_kernel(const __grid_constant__ LatT L, const __grid_constant__ PBatchArgs a) {
     extern __shared__ __align__(16) uint64_t s_rows[];
     __shared__ uint32_t s_plan[PB_MAXSEG * PLAN_WORDS];
@@ -649,13 +706,24 @@ __global__ void __launch_bounds__(PB_MAX_THREADS, 1) pbatch_kernel(const __grid_
     pb_publish_loaded(g, c, t, T);
     __syncthreads();
 
+    // pass-invariant per-thread item data in shared memory behind the rows, if the host found room for it
+    PBI4 *const ca = KEEP ? reinterpret_cast<PBI4 *>(reinterpret_cast<unsigned char *>(s_rows) + a.cache_off) : nullptr;
+    PBI4 *const cb = KEEP ? ca + T : nullptr;
+    if (KEEP) {
+        PBItems f;
+        pb_items(g, c, t, T, f);
+        pb_items_store(f, ca, cb, t);  // read back by this thread only
+    }
+    Plan<MODEL> plan;
+    int plan_seg = -1;
+
     unsigned int events = 1, arrivals = 0;
     int scheme = a.scheme0, cur = 0;
     unsigned long long round = a.round0;
     for (long long sw = 0; sw < a.nsweeps; ++sw) {
 #pragma unroll 1
         for (int colour = 0; colour < 2; ++colour) {
-            pb_pass<MODEL>(g, c, colour, 2 * (a.sweep0 + sw) + colour, events, t, T);
+            pb_pass<MODEL, KEEP, SLAB>(g, c, colour, 2 * (a.sweep0 + sw) + colour, events, t, T, plan, plan_seg, ca, cb);
             ++events;
             __syncthreads();
         }
@@ -770,6 +838,7 @@ __global__ void __launch_bounds__(PB_MAX_THREADS, 1) pbatch_kernel(const __grid_
             }
             __syncthreads();
             load_plans();
+            plan_seg = -1;  // the plan rows have changed
             __syncthreads();
             cur = nxt;
             scheme ^= 1;

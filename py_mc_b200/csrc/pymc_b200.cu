@@ -712,6 +712,7 @@ struct pymc_handle {
     bool pbatch;                   // calls of >= 2 sweeps (and single-GPU exchange cycles) run on the batch kernel
     int pb_blocks, pb_threads;
     size_t pb_smem;
+    int pb_cache_off;              // byte offset of the per-thread item data behind the rows in shared memory (0: none)
     unsigned int *pb_sync;         // [2] grid-barrier counter + abort word (zeroed per launch)
     PBPacket *pb_xbuf;             // [2][2*blocks + 2*nrep][nw] rows exchanged between blocks, as packets (zeroed per launch)
     long long *pb_esum;            // [2 parities][ntemps][2] exact sums per GLOBAL replica at an exchange
@@ -765,6 +766,13 @@ static bool plan_pbatch(pymc_handle *h, int nrep, int lenX, int sms, int smem, s
     h->pb_blocks = blocks;
     h->pb_threads = (int)threads;
     h->pb_smem = rows_bytes;
+    // 32 bytes per thread of pass-invariant item data behind the rows, where the rows leave room (pmc_pbatch.cuh: PBItems)
+    h->pb_cache_off = 0;
+    if (ok && rows_bytes > 0 && rows_bytes + (size_t)threads * 32 + 2048 <= (size_t)smem && max_rows < (1 << 29) / (h->nw > 0 ? h->nw : 1) &&
+        h->nw < 65536) {
+        h->pb_cache_off = (int)rows_bytes;
+        h->pb_smem = rows_bytes + (size_t)threads * 32;
+    }
     if (rows_bytes_out) *rows_bytes_out = rows_bytes;
     return ok;
 }
@@ -1437,10 +1445,16 @@ static int launch_pbatch(pymc_handle *h, int64_t nsweeps, int xchg_every, int *s
     if (nsweeps <= 0) return PYMC_OK;
     const int m = h->p.model == PYMC_MODEL_ISING ? 0 : 1;
     const void *fn;
-    if (h->p.layout == PYMC_LAYOUT_INT8)
-        fn = m ? (const void *)pbatch_kernel<MODEL_LATGAS, PYMC_LAYOUT_INT8, Lat> : (const void *)pbatch_kernel<MODEL_ISING, PYMC_LAYOUT_INT8, Lat>;
+    const bool keep = h->pb_cache_off > 0;  // room in shared memory for the per-thread item data: the KEEP instantiation
+#define PB_FN(MOD, LAY, SLB) \
+    (keep ? (const void *)pbatch_kernel<MOD, LAY, true, SLB, Lat> : (const void *)pbatch_kernel<MOD, LAY, false, SLB, Lat>)
+    if (h->slab)  // slabs are int8
+        fn = m ? PB_FN(MODEL_LATGAS, PYMC_LAYOUT_INT8, true) : PB_FN(MODEL_ISING, PYMC_LAYOUT_INT8, true);
+    else if (h->p.layout == PYMC_LAYOUT_INT8)
+        fn = m ? PB_FN(MODEL_LATGAS, PYMC_LAYOUT_INT8, false) : PB_FN(MODEL_ISING, PYMC_LAYOUT_INT8, false);
     else
-        fn = m ? (const void *)pbatch_kernel<MODEL_LATGAS, PYMC_LAYOUT_BITS, Lat> : (const void *)pbatch_kernel<MODEL_ISING, PYMC_LAYOUT_BITS, Lat>;
+        fn = m ? PB_FN(MODEL_LATGAS, PYMC_LAYOUT_BITS, false) : PB_FN(MODEL_ISING, PYMC_LAYOUT_BITS, false);
+#undef PB_FN
     if (!h->pb_attr[m]) {
         if (h->pb_smem > 48 * 1024)
             CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->pb_smem));
@@ -1478,6 +1492,7 @@ static int launch_pbatch(pymc_handle *h, int64_t nsweeps, int xchg_every, int *s
         h->pb_epoch += PB_EPOCH_STEP;
         a.epoch = h->pb_epoch;
         a.row0 = h->slab ? h->slab_index * (h->own_hi - h->own_lo) : 0;
+        a.cache_off = h->pb_cache_off;
         a.esum = h->pb_esum;
         a.nranks = h->rx_nranks > 1 ? h->rx_nranks : 1;
         a.rank = h->rx_nranks > 1 ? h->rx_rank : 0;

@@ -282,13 +282,30 @@ int pbatch_sweeps(int8_t *imgs, int nrep, int lenX, int lenY, const uint32_t *th
         c.rep_offset = rep_offset;
         c.key = &keys;
     }
+    std::vector<std::vector<PBI4>> cache_a(B, std::vector<PBI4>(T)), cache_b(B, std::vector<PBI4>(T));
     for (int b = 0; b < B; ++b)
-        for (int t = 0; t < T; ++t) pb_publish_loaded(geo[b], ctx[b], t, T);
+        for (int t = 0; t < T; ++t) {
+            pb_publish_loaded(geo[b], ctx[b], t, T);
+            PBItems f;
+            pb_items(geo[b], ctx[b], t, T, f);
+            pb_items_store(f, cache_a[b].data(), cache_b[b].data(), t);
+        }
     unsigned int events = 1;
     for (int sw = 0; sw < nsweeps; ++sw)
         for (int colour = 0; colour < 2; ++colour) {
             for (int b = 0; b < B; ++b)
-                for (int t = 0; t < T; ++t) pb_pass<MODEL>(geo[b], ctx[b], colour, 2 * (sweep0 + sw) + colour, events, t, T);
+                for (int t = 0; t < T; ++t) {
+                    // with the per-thread item data cached (as the kernel does when shared memory has room) in even
+                    // blocks, recomputed in odd ones; the plan is set up afresh for every call here
+                    Plan<MODEL> plan;
+                    int plan_seg = -1;
+                    if ((b & 1) == 0)
+                        pb_pass<MODEL, true, false>(geo[b], ctx[b], colour, 2 * (sweep0 + sw) + colour, events, t, T, plan, plan_seg,
+                                             cache_a[b].data(), cache_b[b].data());
+                    else
+                        pb_pass<MODEL, false, false>(geo[b], ctx[b], colour, 2 * (sweep0 + sw) + colour, events, t, T, plan, plan_seg,
+                                              nullptr, nullptr);
+                }
             ++events;
         }
     for (int r = 0; r < 2 * nrep; ++r) sums[r] = 0;
