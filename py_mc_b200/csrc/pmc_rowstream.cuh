@@ -11,13 +11,14 @@
 // instructions per 64-site word against 547 for the bit-packed kernel, 47 % of the HBM roofline).  Here a block owns
 // a PIECE of whole rows of one replica and walks down it:
 //   * rows arrive in shared memory by bulk asynchronous copies (cp.async.bulk + mbarrier: one instruction per row
-//     from one thread, no per-thread address arithmetic, no registers held across the latency), two stages deep;
+//     from one lane, no per-thread address arithmetic, no registers held across the latency), two staging slots;
 //   * every thread packs 64 bytes to bits, updates one 64-site word and unpacks one per iteration; full-width rows
 //     wrap onto themselves, so there is no halo in y at all, and in x a piece recomputes ONE extra row of colour 0
 //     at either end (2 row updates per piece instead of a ring per tile);
 //   * colour 1 of row j follows colour 0 of row j+1 at a fixed distance in one task sequence, so both colours are
-//     done in one pass over the data with one block barrier per iteration: every site is read once and written
-//     once per sweep (2 B per attempt), out of place (the handle ping-pongs two buffers).
+//     done in one pass over the data: every site is read once and written once per sweep (2 B per attempt), out
+//     of place (the handle ping-pongs two buffers); the warps of a block synchronise through mbarriers, two
+//     iterations back (below), not at a block barrier.
 // Random-stream indexing is that of every other sweep kernel (word = row * nw + w, replica, step = 2*sweep +
 // colour), so the trajectory is identical.
 //
