@@ -280,7 +280,8 @@ int pymc_rx_exchange(pymc_handle *h, int xcscheme);
 int pymc_rx_cycle(pymc_handle *h, int64_t ncycles, int64_t sweeps_per_exchange, int first_scheme);
 /* The ladder spread over several GPUs with the exchange inside the sweep kernel (replaces the Send/Recv of one double
  * per pair and the Allgather of mc_mpi.py:106-138 by stores into peer memory over NVLink; no host, no NCCL in the loop).
- * pymc_rx_ipc_export  two CUDA IPC handles of this GPU (2 x 64 bytes): its per-replica sums and its delivery flags.
+ * pymc_rx_ipc_export  two CUDA IPC handles of this GPU (2 x 64 bytes): the array the other GPUs store the sums of their
+ *                     replicas into as {data, round} packets, and a spare word array.
  * pymc_rx_connect     all_handles = the exports of all GPUs in rank order (nranks x 128 bytes).  Needs the block
  *                     partition rank g <-> replicas [g*R/G, (g+1)*R/G) and the batch-resident kernel.
  * Afterwards pymc_rx_cycle works on the partitioned handle: ONE launch per GPU for all sweeps and exchanges of the call;

@@ -562,12 +562,29 @@ __device__ __forceinline__ void pb_reduce(const PBGeom &g, const PBCtx &c, unsig
 // esum[global replica][2] = exact bond sum and second observable of every replica at this exchange.  The energy is
 // evaluated like rx_energy_kernel (no FMA contraction) so that it equals the host expression J*B + (Eads-mu)*N bit
 // for bit.
-__device__ __forceinline__ double pb_energy(const long long *esum, int r, double c_bond, double c_second) {
+// The sums of a replica on another GPU arrive as packets (xpk, pass number = exchange round + 1: what pb_get waits for);
+// xpk == nullptr: all replicas are here.
+struct PBRemote {
+    const PBPacket *xpk;  // [R][2] of this round's parity, or nullptr
+    unsigned int need;
+    int own_lo, own_hi;   // my replicas: [own_lo, own_hi)
+    int *err;
+    unsigned int *abort_word;
+};
+__device__ __forceinline__ double pb_energy(const long long *esum, const PBRemote &rm, int r, double c_bond, double c_second) {
 #ifdef __CUDA_ARCH__
-    const long long Bs = __ldcg(esum + 2 * r), Ss = __ldcg(esum + 2 * r + 1);
+    long long Bs, Ss;
+    if (rm.xpk && (r < rm.own_lo || r >= rm.own_hi)) {
+        Bs = (long long)pb_get(rm.xpk + 2 * r, rm.need, rm.err, rm.abort_word, 20000000000LL);  // ten seconds: another GPU
+        Ss = (long long)pb_get(rm.xpk + 2 * r + 1, rm.need, rm.err, rm.abort_word, 20000000000LL);
+    } else {
+        Bs = __ldcg(esum + 2 * r);
+        Ss = __ldcg(esum + 2 * r + 1);
+    }
     double e = __dmul_rn(c_bond, (double)Bs);
     if (c_second != 0.0) e = __dadd_rn(e, __dmul_rn((double)Ss, c_second));
 #else
+    (void)rm;
     const long long Bs = esum[2 * r], Ss = esum[2 * r + 1];
     double e = c_bond * (double)Bs;
     if (c_second != 0.0) e = e + (double)Ss * c_second;
@@ -595,9 +612,8 @@ struct PBatchArgs {
                                    // the local slice is zeroed by the host before the launch (blocks add deltas)
     // replicas spread over several GPUs (pymc_rx_connect): the all-gather of the energies is done by this kernel
     int nranks, rank;              // 1, 0 on a single GPU
-    long long *peer_esum[PB_MAXRANKS];    // the other GPUs' esum arrays (CUDA IPC mappings); [rank] unused
-    unsigned int *xflags;                 // [nranks] mine: xflags[g] = exchanges whose sums GPU g has delivered here
-    unsigned int *peer_xflags[PB_MAXRANKS];
+    PBPacket *xpk;                        // [2 parities][R][2] mine: the sums of the other GPUs' replicas arrive here as packets
+    PBPacket *peer_xpk[PB_MAXRANKS];      // the other GPUs' xpk arrays (CUDA IPC mappings); [rank] unused
     unsigned long long *out;       // [nrep][2] zeroed by the host: the exact sums at the end of the launch
     const double *betas;
     double c_bond, c_second;
@@ -746,43 +762,31 @@ __global__ void __launch_bounds__(PB_MAX_THREADS, 1) pbatch_kernel(const __grid_
             }
             arrivals += (unsigned int)B;
             pb_grid_barrier(a.bar, arrivals, a.err);  // the sums of all replicas of this GPU are complete
+            PBRemote rm;
+            rm.xpk = nullptr;
             if (a.nranks > 1) {
                 // All-gather over NVLink, written by hand: block 0 stores the sums of my replicas straight into every other
-                // GPU's array (peer memory), then raises my flag over there; every block waits until all other GPUs have
-                // delivered theirs here.  Flags carry the exchange round (the same number on every GPU, never reset).
+                // GPU's packet array (peer memory) as {32 data bits, exchange round + 1} packets -- the round rides in the
+                // same atomic 8-byte store as the data, so there is no fence, no separate flag and no second trip over
+                // NVLink; whoever needs the sums of a replica of another GPU (pb_energy) repeats the load of its packets
+                // from local memory until they carry this round.  (First form: plain stores, __threadfence_system, a flag
+                // per GPU: two dependent NVLink trips and two system-scope fences per exchange.)
                 const unsigned int xr = (unsigned int)round + 1u;
                 if (b == 0) {
                     for (int k = t; k < 2 * nrep * a.nranks; k += T) {
                         const int peer = k / (2 * nrep), j = k - peer * 2 * nrep;
                         if (peer != a.rank) {
                             const size_t at = (size_t)par * R * 2 + 2 * (size_t)L.rep_offset + j;
-                            a.peer_esum[peer][at] = __ldcg(a.esum + at);
+                            pb_put(a.peer_xpk[peer] + at, (uint64_t)__ldcg(a.esum + at), xr);
                         }
                     }
-                    __threadfence_system();
-                    __syncthreads();
-                    if (t < a.nranks && t != a.rank) {
-                        __threadfence_system();
-                        *(volatile unsigned int *)(a.peer_xflags[t] + a.rank) = xr;
-                    }
                 }
-                if (t < a.nranks && t != a.rank) {
-                    const long long t0 = clock64();
-                    unsigned int spins = 0;
-                    while (*(volatile unsigned int *)(a.xflags + t) < xr) {
-                        __nanosleep(64);
-                        if ((++spins & 1023u) == 0) {
-                            if (*(volatile unsigned int *)(a.bar + 1)) break;
-                            if (clock64() - t0 > 20000000000LL) {  // ten seconds: the other GPU is not running this exchange
-                                *(volatile unsigned int *)(a.bar + 1) = 1u;
-                                *a.err = 1;
-                                break;
-                            }
-                        }
-                    }
-                    __threadfence_system();
-                }
-                __syncthreads();
+                rm.xpk = a.xpk + (size_t)par * R * 2;
+                rm.need = xr;
+                rm.own_lo = (int)L.rep_offset;
+                rm.own_hi = (int)L.rep_offset + nrep;
+                rm.err = a.err;
+                rm.abort_word = a.bar + 1;
             }
             // ---- the pair decisions of Xtrial (py_mc/mc_mpi.py:102-140) ---------------------------------------------
             // A decision is a pure function of (pair, round, the two energies): every block works out the pairs its own
@@ -792,8 +796,8 @@ __global__ void __launch_bounds__(PB_MAX_THREADS, 1) pbatch_kernel(const __grid_
             auto decide = [&](int tl, int &r_lo, int &r_hi) -> bool {  // pair (tl, tl + 1) of temperature indices
                 r_lo = t2r[tl];
                 r_hi = t2r[tl + 1];
-                const double e_lo = pb_energy(es, r_lo, a.c_bond, a.c_second);
-                const double e_hi = pb_energy(es, r_hi, a.c_bond, a.c_second);
+                const double e_lo = pb_energy(es, rm, r_lo, a.c_bond, a.c_second);
+                const double e_hi = pb_energy(es, rm, r_hi, a.c_bond, a.c_second);
                 const double delta = __dmul_rn(__dsub_rn(a.betas[tl + 1], a.betas[tl]), __dsub_rn(e_lo, e_hi));
                 if (delta < 0.0) return true;
                 const uint4 o = philox4x32_10((uint32_t)tl, 0u, (uint32_t)round, ctr3(DOMAIN_RX, 0, round), L.key);
@@ -819,7 +823,7 @@ __global__ void __launch_bounds__(PB_MAX_THREADS, 1) pbatch_kernel(const __grid_
                         a.rep_to_T[nxt][r] = tt;
                     }
                 }
-                for (int r = t; r < R; r += T) a.energies[r] = pb_energy(es, r, a.c_bond, a.c_second);
+                for (int r = t; r < R; r += T) a.energies[r] = pb_energy(es, rm, r, a.c_bond, a.c_second);
                 const int g_first = (int)L.rep_offset + g.rep_first;
                 for (int p = t; 2 * p + scheme + 1 < R; p += T) {
                     const int tl = 2 * p + scheme;

@@ -718,8 +718,9 @@ struct pymc_handle {
     long long *pb_esum;            // [2 parities][ntemps][2] exact sums per GLOBAL replica at an exchange
     unsigned int *pb_xflags;       // [PB_MAXRANKS] exchange rounds whose sums each other GPU has delivered here
     int rx_nranks, rx_rank;        // > 1 after pymc_rx_connect: the ladder is spread over that many GPUs
-    long long *peer_esum[PB_MAXRANKS];       // CUDA IPC mappings of the other GPUs' pb_esum / pb_xflags
-    unsigned int *peer_xflags[PB_MAXRANKS];
+    PBPacket *pb_xpk;              // [2 parities][ntemps][2] packets: the sums of the other GPUs' replicas arrive here
+    PBPacket *peer_xpk[PB_MAXRANKS];         // CUDA IPC mappings of the other GPUs' pb_xpk
+    unsigned int *peer_xflags[PB_MAXRANKS];  // ... and pb_xflags (kept for the layout of the exported handles; unused)
     unsigned int pb_epoch;         // pass-number base of the last launch (grows by PB_EPOCH_STEP per launch)
     PBPacket *peer_xbuf_up, *peer_xbuf_dn;   // slab mode: the neighbours' exchange buffers (CUDA IPC mappings, or mine)
     bool slab_pbatch;              // slab handle whose calls of >= 2 sweeps run on K12 (connected through IPC, or a single slab)
@@ -929,9 +930,10 @@ int pymc_destroy(pymc_handle *h) {
         cudaFree(h->pb_xbuf);
         for (int g = 0; g < h->rx_nranks; ++g)
             if (g != h->rx_rank) {
-                if (h->peer_esum[g]) cudaIpcCloseMemHandle(h->peer_esum[g]);
+                if (h->peer_xpk[g]) cudaIpcCloseMemHandle(h->peer_xpk[g]);
                 if (h->peer_xflags[g]) cudaIpcCloseMemHandle(h->peer_xflags[g]);
             }
+        cudaFree(h->pb_xpk);
         cudaFree(h->pb_esum);
         cudaFree(h->pb_xflags);
         cudaFree(h->pb_maps);
@@ -1417,6 +1419,11 @@ static int ensure_rx_exchange_buffers(pymc_handle *h) {
         CUDA_TRY(cudaMalloc(&h->pb_xflags, PB_MAXRANKS * sizeof(unsigned int)));
         CUDA_TRY(cudaMemset(h->pb_xflags, 0, PB_MAXRANKS * sizeof(unsigned int)));
     }
+    if (!h->pb_xpk) {
+        const size_t bytes = (size_t)2 * h->p.ntemps * 2 * sizeof(PBPacket);
+        CUDA_TRY(cudaMalloc(&h->pb_xpk, bytes));
+        CUDA_TRY(cudaMemset(h->pb_xpk, 0, bytes));
+    }
     return PYMC_OK;
 }
 
@@ -1496,11 +1503,8 @@ static int launch_pbatch(pymc_handle *h, int64_t nsweeps, int xchg_every, int *s
         a.esum = h->pb_esum;
         a.nranks = h->rx_nranks > 1 ? h->rx_nranks : 1;
         a.rank = h->rx_nranks > 1 ? h->rx_rank : 0;
-        a.xflags = h->pb_xflags;
-        for (int g = 0; g < a.nranks; ++g) {
-            a.peer_esum[g] = h->peer_esum[g];
-            a.peer_xflags[g] = h->peer_xflags[g];
-        }
+        a.xpk = h->pb_xpk;
+        for (int g = 0; g < a.nranks; ++g) a.peer_xpk[g] = h->peer_xpk[g];
         a.out = h->reduced;
         a.ntemps = R;
         a.rep_to_T[0] = h->rep_to_T;
@@ -1989,7 +1993,7 @@ int pymc_rx_ipc_export(pymc_handle *h, void *handles, size_t nbytes) {
     int rc = ensure_rx_exchange_buffers(h);
     if (rc) return rc;
     cudaIpcMemHandle_t *out = (cudaIpcMemHandle_t *)handles;
-    CUDA_TRY(cudaIpcGetMemHandle(out + 0, h->pb_esum));
+    CUDA_TRY(cudaIpcGetMemHandle(out + 0, h->pb_xpk));
     CUDA_TRY(cudaIpcGetMemHandle(out + 1, h->pb_xflags));
     return PYMC_OK;
 }
@@ -2010,7 +2014,7 @@ int pymc_rx_connect(pymc_handle *h, const void *all_handles, size_t nbytes, int 
         void *p0 = nullptr, *p1 = nullptr;
         CUDA_TRY(cudaIpcOpenMemHandle(&p0, hd[2 * g + 0], cudaIpcMemLazyEnablePeerAccess));
         CUDA_TRY(cudaIpcOpenMemHandle(&p1, hd[2 * g + 1], cudaIpcMemLazyEnablePeerAccess));
-        h->peer_esum[g] = (long long *)p0;
+        h->peer_xpk[g] = (PBPacket *)p0;
         h->peer_xflags[g] = (unsigned int *)p1;
     }
     h->rx_nranks = nranks;
@@ -2048,10 +2052,10 @@ int pymc_rx_get_round(pymc_handle *h, uint64_t *round) {
 
 int pymc_rx_set_round(pymc_handle *h, uint64_t round) {
     REQUIRE(h, PYMC_ERR_BADARG, "pymc_rx_set_round: null handle");
-    if (h->pb_xflags && round < h->rx_round) {  // the delivery flags count rounds: start them again (do this on every GPU,
-        DeviceGuard guard(h->p.device);        // then synchronise the processes, before the next pymc_rx_cycle)
+    if (h->pb_xpk && round < h->rx_round) {  // the packets of other GPUs carry rounds: start them again (do this on every GPU,
+        DeviceGuard guard(h->p.device);     // then synchronise the processes, before the next pymc_rx_cycle)
         CUDA_TRY(cudaStreamSynchronize(h->stream));
-        CUDA_TRY(cudaMemset(h->pb_xflags, 0, PB_MAXRANKS * sizeof(unsigned int)));
+        CUDA_TRY(cudaMemset(h->pb_xpk, 0, (size_t)2 * h->p.ntemps * 2 * sizeof(PBPacket)));
     }
     h->rx_round = round;
     return PYMC_OK;
