@@ -286,7 +286,7 @@ int pymc_rx_cycle(pymc_handle *h, int64_t ncycles, int64_t sweeps_per_exchange, 
  *                     partition rank g <-> replicas [g*R/G, (g+1)*R/G) and the batch-resident kernel.
  * Afterwards pymc_rx_cycle works on the partitioned handle: ONE launch per GPU for all sweeps and exchanges of the call;
  * every GPU must make the same calls.  A GPU that waits ten seconds for another one raises the handle's error
- * (see pymc_synchronize).  pymc_rx_set_round to an earlier round restarts the delivery flags: call it on every GPU
+ * (see pymc_synchronize).  pymc_rx_set_round to an earlier round clears the packet array (packets carry the round): call it on every GPU
  * and synchronise the processes before the next cycle. */
 int pymc_rx_ipc_export(pymc_handle *h, void *handles, size_t nbytes);
 int pymc_rx_connect(pymc_handle *h, const void *all_handles, size_t nbytes, int nranks, int rank);

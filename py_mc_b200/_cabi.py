@@ -475,7 +475,7 @@ class Lattices:
         check(lib.pymc_rx_exchange(self._h, int(xcscheme)))
 
     def rx_ipc_export(self):
-        """128 bytes: CUDA IPC handles of this GPU's per-replica sums and delivery flags (in-kernel exchange)."""
+        """128 bytes: CUDA IPC handles of the array the other GPUs store their replicas' sums into (in-kernel exchange)."""
         buf = (C.c_char * 128)()
         check(lib.pymc_rx_ipc_export(self._h, buf, 128))
         return bytes(buf)
