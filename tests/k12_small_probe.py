@@ -1,3 +1,4 @@
+"""GPU probe (not a pytest file): us per sweep of R replicas of 1024 x 1024 on the batch-resident kernel, 400 sweeps per call."""
 import sys, os
 sys.path.insert(0, os.getcwd())
 import numpy as np
