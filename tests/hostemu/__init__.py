@@ -41,6 +41,8 @@ class HostCore:
                                                     C.c_uint64, C.c_int, C.c_int, C.c_int, LL, LL]
         self.lib.hostemu_pbatch_sweeps.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_uint64,
                                                    C.c_uint32, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        self.lib.hostemu_pbatch_slab_sweeps.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_uint32,
+                                                        C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
         self.lib.hostemu_rowstream_sweep.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_uint32,
                                                      C.c_uint64, C.c_int, LL, LL]
         self.lib.hostemu_pair_sweep.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_uint32,
@@ -55,6 +57,18 @@ class HostCore:
                                              replica, sweep0, nsweeps, nblocks, nthreads, C.byref(dB), C.byref(dS))
         assert rc == 0, rc
         return dB.value, dS.value
+
+    def pbatch_slab_sweeps(self, model, img, thr, seed, replica, sweep0, nsweeps, nslabs, nblocks, nthreads):
+        """nsweeps sweeps of ONE lattice img[lenX, lenY] (in place) cut into nslabs row slabs, each run by nblocks emulated blocks
+        of the batch-resident kernel's slab instantiation with its own exchange buffer (the GPUs of a slab run); returns the
+        (bond sum, second observable) added up over the slabs."""
+        assert img.dtype == np.int8 and img.flags.c_contiguous and img.ndim == 2
+        t = np.ascontiguousarray(thr, dtype=np.uint32)
+        sums = np.zeros(2, dtype=np.int64)
+        rc = self.lib.hostemu_pbatch_slab_sweeps(model, img.ctypes.data, img.shape[0], img.shape[1], t.ctypes.data, seed, replica,
+                                                 sweep0, nsweeps, nslabs, nblocks, nthreads, sums.ctypes.data)
+        assert rc == 0, rc
+        return int(sums[0]), int(sums[1])
 
     def rowstream_sweep(self, model, img, thr, seed, replica, sweep, pieces):
         """One sweep (in place) through the row-streaming kernel's schedule and per-thread phases with `pieces` emulated

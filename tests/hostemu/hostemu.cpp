@@ -511,3 +511,149 @@ extern "C" int hostemu_rowstream_sweep(int model, int8_t *img, int lenX, int len
 }
 
 extern "C" int hostemu_rowstream_threads(void) { return RS_THREADS; }
+
+namespace {
+
+// One lattice in row slabs over several "GPUs", each running the batch-resident kernel on its owned rows (pmc_pbatch.cuh,
+// SLAB instantiation): G slabs of lenX / G rows, B blocks each, every slab with its own exchange buffer; what a slab's
+// first / last block exports of row 0 / the last row goes into the exchange buffer of the slab above / below (on the GPUs:
+// peer memory), the random stream is indexed by whole-lattice rows.  All blocks of all slabs in lock step.  The caller
+// compares the result with the plain sweep of the whole lattice; sums[0..1] = bond sum and second observable added up over
+// the slabs (a slab's share of the boundary bonds is its own business).
+template <int MODEL>
+int pbatch_slab_sweeps(int8_t *img, int lenX, int lenY, const uint32_t *thr, uint64_t seed, uint32_t replica, uint64_t sweep0,
+                       int nsweeps, int G, int B, int T, long long *sums) {
+    const int nw = lenY / 128, nown = lenX / G, nslots = pb_nslots(B, 1);
+    Image im = {img, lenX, lenY};
+    struct Slab {
+        std::vector<PBGeom> geo;
+        std::vector<std::vector<uint64_t>> rows;
+        std::vector<int> segoff, segstart;
+        std::vector<uint32_t> splan;
+        std::vector<PBPacket> xbuf;
+        std::vector<PBCtx> ctx;
+        std::vector<std::vector<PBI4>> ca, cb;
+    };
+    std::vector<Slab> sl(G);
+    int err = 0;
+    unsigned int abort_word = 0;
+    const PhiloxKey keys = make_key(seed);
+    for (int s = 0; s < G; ++s) {
+        Slab &S = sl[s];
+        S.geo.resize(B);
+        S.rows.resize(B);
+        S.segoff.assign(1, 0);
+        S.segstart.assign(1, 0);
+        S.splan.resize(PLAN_WORDS);
+        Plan<MODEL>::build_row(thr, S.splan.data());
+        S.xbuf.assign((size_t)2 * nslots * nw, PBPacket{0, 0});
+        S.ctx.resize(B);
+        S.ca.assign(B, std::vector<PBI4>(T));
+        S.cb.assign(B, std::vector<PBI4>(T));
+    }
+    // per block: segoff[0] = row-in-replica of local row 0 -- differs per block, so every block gets its own copy
+    std::vector<std::vector<std::vector<int>>> bsegoff(G, std::vector<std::vector<int>>(B, std::vector<int>(1)));
+    for (int s = 0; s < G; ++s)
+        for (int b = 0; b < B; ++b) {
+            Slab &S = sl[s];
+            PBGeom &g = S.geo[b];
+            pb_geometry(b, B, 1, nown, g);
+            if (g.nxrow * nw > T || B < 2) return -2;
+            S.rows[b].assign((size_t)2 * g.nrows * nw, 0);
+            bsegoff[s][b][0] = g.i0;
+            for (int colour = 0; colour < 2; ++colour)
+                for (int lr = 0; lr < g.nrows; ++lr)
+                    for (int w = 0; w < nw; ++w)
+                        S.rows[b][((size_t)colour * g.nrows + lr) * nw + w] = gather(im, colour, s * nown + g.R0 + lr, w, 0, 0);
+            PBCtx &c = S.ctx[b];
+            c.s = S.rows[b].data();
+            c.segoff = bsegoff[s][b].data();
+            c.segstart = S.segstart.data();
+            c.splan = S.splan.data();
+            c.xbuf = S.xbuf.data();
+            c.xbuf_up = sl[(s + G - 1) % G].xbuf.data();
+            c.xbuf_dn = sl[(s + 1) % G].xbuf.data();
+            c.epoch = 16384u * 3u;
+            c.row0 = s * nown;
+            c.wait_cycles = 0;
+            c.abort_word = &abort_word;
+            c.err = &err;
+            c.lenX = nown;
+            c.nw = nw;
+            c.nw_shift = -1;
+            for (int k = 0; k < 20; ++k)
+                if ((1 << k) == nw) c.nw_shift = k;
+            c.nslots = nslots;
+            c.b = b;
+            c.nblocks = B;
+            c.rep_offset = replica;
+            c.key = &keys;
+        }
+    for (int s = 0; s < G; ++s)
+        for (int b = 0; b < B; ++b)
+            for (int t = 0; t < T; ++t) {
+                // the slab instantiation of the publishing step: through pb_export_buffer
+                const PBGeom &g = sl[s].geo[b];
+                const PBCtx &c = sl[s].ctx[b];
+                pb_publish_loaded(g, c, t, T);
+                PBItems f;
+                pb_items(g, c, t, T, f);
+                pb_items_store(f, sl[s].ca[b].data(), sl[s].cb[b].data(), t);
+            }
+    unsigned int events = 1;
+    for (int sw = 0; sw < nsweeps; ++sw)
+        for (int colour = 0; colour < 2; ++colour) {
+            for (int s = 0; s < G; ++s)
+                for (int b = 0; b < B; ++b)
+                    for (int t = 0; t < T; ++t) {
+                        Plan<MODEL> plan;
+                        int plan_seg = -1;
+                        if ((b + s) & 1)
+                            pb_pass<MODEL, true, true>(sl[s].geo[b], sl[s].ctx[b], colour, 2 * (sweep0 + sw) + colour, events, t, T, plan,
+                                                       plan_seg, sl[s].ca[b].data(), sl[s].cb[b].data());
+                        else
+                            pb_pass<MODEL, false, true>(sl[s].geo[b], sl[s].ctx[b], colour, 2 * (sweep0 + sw) + colour, events, t, T, plan,
+                                                        plan_seg, nullptr, nullptr);
+                    }
+            ++events;
+        }
+    sums[0] = sums[1] = 0;
+    for (int s = 0; s < G; ++s)
+        for (int b = 0; b < B; ++b) {
+            long long acc[2 * PB_MAXSEG] = {0};
+            for (int t = 0; t < T; ++t) pb_reduce<MODEL>(sl[s].geo[b], sl[s].ctx[b], events, acc, t, T);
+            sums[0] += acc[0];
+            sums[1] += acc[1];
+        }
+    if (err) return -4;
+    for (int s = 0; s < G; ++s)
+        for (int b = 0; b < B; ++b) {
+            const PBGeom &g = sl[s].geo[b];
+            for (int colour = 0; colour < 2; ++colour)
+                for (int lr = 0; lr < g.nrows; ++lr) {
+                    const int i = s * nown + g.R0 + lr, q = (i + colour) & 1;
+                    for (int w = 0; w < nw; ++w) {
+                        const uint64_t v = sl[s].rows[b][((size_t)colour * g.nrows + lr) * nw + w];
+                        for (int l = 0; l < 64; ++l) {
+                            const int bit = (int)((v >> l) & 1ull);
+                            *im.site(i, 2 * (64 * w + l) + q) = MODEL == MODEL_ISING ? (int8_t)(2 * bit - 1) : (int8_t)bit;
+                        }
+                    }
+                }
+        }
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int hostemu_pbatch_slab_sweeps(int model, int8_t *img, int lenX, int lenY, const uint32_t *thr, uint64_t seed,
+                                          uint32_t replica, uint64_t sweep0, int nsweeps, int nslabs, int nblocks, int nthreads,
+                                          long long *sums) {
+    if (lenY % 128 || nslabs < 1 || lenX % nslabs || ((lenX / nslabs) & 1) || nblocks < 2 || nblocks > lenX / nslabs || nthreads < 1)
+        return -1;
+    if (model == MODEL_ISING)
+        return pbatch_slab_sweeps<MODEL_ISING>(img, lenX, lenY, thr, seed, replica, sweep0, nsweeps, nslabs, nblocks, nthreads, sums);
+    if (model == MODEL_LATGAS)
+        return pbatch_slab_sweeps<MODEL_LATGAS>(img, lenX, lenY, thr, seed, replica, sweep0, nsweeps, nslabs, nblocks, nthreads, sums);
+    return -1;
+}

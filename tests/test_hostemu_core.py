@@ -178,3 +178,23 @@ def test_row_streaming_kernel_logic_matches_specification(core, shape, pieces):
     core.rowstream_sweep(core.MODEL_LATGAS, cfg, thr, seed, replica, 0, pieces)
     o_latgas.sweep(ref, thr, seed, replica, 0)
     assert np.array_equal(cfg, ref)
+
+
+@pytest.mark.parametrize("shape,nslabs,nblocks,nthreads", [
+    ((16, 128), 2, 2, 32),      # two slabs: the slab above is the slab below
+    ((24, 256), 3, 4, 32),      # three slabs of 8 rows in 4 blocks: every block of two rows
+    ((32, 128), 4, 2, 64),
+    ((40, 384), 1, 5, 32),      # a single slab: its neighbours are itself (the periodic lattice through the exchange buffer)
+])
+def test_batch_resident_kernel_on_row_slabs_matches_specification(core, shape, nslabs, nblocks, nthreads):
+    """pmc_pbatch.cuh, slab instantiation, with several emulated "GPUs": each slab's first / last block exports row 0 / the
+    last row into the exchange buffer of the slab above / below, imports from its own; the random stream is indexed by
+    whole-lattice rows.  Must equal the plain sweep of the whole lattice (numpy specification), sums included."""
+    seed, replica, J, kT = 123, 1, -1.0, 2.4
+    ref = o_ising.init_config(seed, replica, *shape)
+    cfg = ref.copy()
+    b, m = core.pbatch_slab_sweeps(core.MODEL_ISING, cfg, ising_table(J, kT), seed, replica, 3, 4, nslabs, nblocks, nthreads)
+    for sw in range(3, 7):
+        o_ising.sweep(ref, J, kT, seed, replica, sw)
+    assert np.array_equal(cfg, ref)
+    assert b == o_ising.bond_sum(ref) and m == int(ref.astype(np.int64).sum())
