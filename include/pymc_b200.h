@@ -78,7 +78,7 @@ typedef struct {
     int32_t device;            /* CUDA device ordinal */
     int32_t model;             /* pymc_model */
     int32_t layout;            /* pymc_layout */
-    int32_t lenX, lenY;        /* lattice edges (config[x][y], y contiguous); both even */
+    int32_t lenX, lenY;        /* lattice edges (config[x][y], y contiguous); both even; at most 2^34 sites per replica (a slab handle: per slab) */
     int32_t nreplicas;         /* replicas held by this handle (this GPU) */
     int32_t replica_offset;    /* global index of local replica 0 (multi-GPU partition) */
     int32_t nreplicas_global;  /* replicas over all GPUs (== nreplicas on one GPU) */

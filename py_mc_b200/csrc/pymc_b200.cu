@@ -998,6 +998,13 @@ int pymc_create(const pymc_params *p, pymc_handle **out) {
     CUDA_TRY(cudaGetDeviceCount(&ndev));
     REQUIRE(p->device >= 0 && p->device < ndev, PYMC_ERR_BADARG, "pymc_create: device %d of %d", p->device, ndev);
 
+    // 32-bit indices: words of one colour of one replica (all sweep kernels) and 16-byte chunks of the natural image (the
+    // upload / download kernels count lenX * lenY / 16 of them in an int): 2^34 sites per replica, 131072 x 131072
+    REQUIRE((uint64_t)p->lenX * (uint64_t)((p->lenY / 2 + 63) / 64) <= (1ull << 27) && (uint64_t)p->lenX * p->lenY <= (1ull << 34),
+            PYMC_ERR_UNSUPPORTED, "pymc_create: lattice too large (%d x %d; at most 2^34 sites per replica)", p->lenX, p->lenY);
+    REQUIRE(p->kernel >= PYMC_KERNEL_AUTO && p->kernel <= PYMC_KERNEL_ROWSTREAM, PYMC_ERR_BADARG, "pymc_create: kernel %d",
+            p->kernel);
+
     pymc_handle *h = new (std::nothrow) pymc_handle();
     REQUIRE(h, PYMC_ERR_BADARG, "pymc_create: out of host memory");
     memset(h, 0, sizeof(*h));
@@ -1005,9 +1012,6 @@ int pymc_create(const pymc_params *p, pymc_handle **out) {
     h->nk = p->lenY / 2;
     h->nw = (h->nk + 63) / 64;
     h->nclass = p->model == PYMC_MODEL_ISING ? PYMC_NCLASS_ISING : PYMC_NCLASS_LATGAS;
-    REQUIRE((uint64_t)p->lenX * h->nw < (1ull << 31), PYMC_ERR_UNSUPPORTED, "pymc_create: lattice too large");
-    REQUIRE(p->kernel >= PYMC_KERNEL_AUTO && p->kernel <= PYMC_KERNEL_ROWSTREAM, PYMC_ERR_BADARG, "pymc_create: kernel %d",
-            p->kernel);
 
     DeviceGuard guard(p->device);
     int rc = PYMC_OK;
@@ -2507,6 +2511,9 @@ int pymc_create_slab(const pymc_params *p, int slab_index, int nslabs, pymc_hand
     // slab_push_halos_kernel puts 2 * nreplicas colour planes into gridDim.z (limit 65535)
     REQUIRE(p->nreplicas <= 32767, PYMC_ERR_UNSUPPORTED, "pymc_create_slab: at most 32767 replicas per slab handle (got %d)",
             p->nreplicas);
+    // the random streams are keyed by the word index in the WHOLE lattice, a 32-bit number
+    REQUIRE((uint64_t)p->lenX * (uint64_t)(p->lenY / 128) < (1ull << 31), PYMC_ERR_UNSUPPORTED,
+            "pymc_create_slab: lattice too large (%d x %d over all slabs; at most 2^38 sites)", p->lenX, p->lenY);
     const int Xl = p->lenX / nslabs;
     pymc_params q = *p;
     q.lenX = Xl + 4;  // two halo rows above and below the owned rows

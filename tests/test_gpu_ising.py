@@ -50,6 +50,8 @@ def test_unsupported_shapes_fail_loudly():
         c.Lattices(c.MODEL_ISING, 5, 8)
     with pytest.raises(c.PymcError, match="128"):
         c.Lattices(c.MODEL_ISING, 8, 64, layout=BITS)
+    with pytest.raises(c.PymcError, match="too large"):  # 2^35 sites: past the 32-bit chunk index of the upload kernels
+        c.Lattices(c.MODEL_ISING, 262144, 131072)
     lat = c.Lattices(c.MODEL_ISING, 8, 8)
     with pytest.raises(c.PymcError, match="set_accept_tables"):
         lat.sweep(1)
